@@ -1,0 +1,91 @@
+"""Layer modules backed by this package's sm_100a kernels.
+
+Each class subclasses its ``torch.nn`` namesake (same constructor, same parameters, same
+``state_dict`` keys) and overrides ``forward``: fp32 CUDA tensors go to the native kernels in
+``ops.functional`` (channels-last/NHWC internally); anything else (CPU tensors in the unit
+tests, unsupported dtypes) uses the stock implementation.  Layers covered are the ones the
+reference's models use: Conv2d/ReLU/MaxPool2d/Linear/CrossEntropyLoss (launch_dist.py:9-41,58)
+and BatchNorm2d/AdaptiveAvgPool2d for the torchvision ResNets (example_launch.py:26).
+"""
+from __future__ import annotations
+
+import torch
+import torch.nn as tnn
+
+
+def _native(x):
+    return x.is_cuda and x.dtype == torch.float32
+
+
+def _pair(v):
+    return tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+
+
+class Conv2d(tnn.Conv2d):
+    def forward(self, x):
+        if (_native(x) and self.groups == 1 and _pair(self.dilation) == (1, 1) and self.padding_mode == "zeros"
+                and not isinstance(self.padding, str) and self.stride[0] == self.stride[1] and self.padding[0] == self.padding[1]
+                and self.kernel_size[0] == self.kernel_size[1]):
+            from ..ops import functional as NF
+
+            return NF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0])
+        return super().forward(x)
+
+
+class ReLU(tnn.ReLU):
+    def forward(self, x):
+        if _native(x):
+            from ..ops import functional as NF
+
+            return NF.relu(x)
+        return super().forward(x)
+
+
+class MaxPool2d(tnn.MaxPool2d):
+    def forward(self, x):
+        k, s, p = _pair(self.kernel_size), _pair(self.stride if self.stride is not None else self.kernel_size), _pair(self.padding)
+        if (_native(x) and k[0] == k[1] and s[0] == s[1] and p[0] == p[1] and _pair(self.dilation) == (1, 1)
+                and not self.ceil_mode and not self.return_indices):
+            from ..ops import functional as NF
+
+            return NF.max_pool2d(x, k[0], s[0], p[0])
+        return super().forward(x)
+
+
+class Linear(tnn.Linear):
+    def forward(self, x):
+        if _native(x) and x.dim() == 2:
+            from ..ops import functional as NF
+
+            return NF.linear(x, self.weight, self.bias)
+        return super().forward(x)
+
+
+class CrossEntropyLoss(tnn.CrossEntropyLoss):
+    def forward(self, logits, target):
+        if (_native(logits) and logits.dim() == 2 and target.dtype == torch.int64 and self.weight is None
+                and self.reduction == "mean" and self.label_smoothing == 0.0 and self.ignore_index == -100):
+            from ..ops import functional as NF
+
+            return NF.cross_entropy(logits, target)
+        return super().forward(logits, target)
+
+
+class BatchNorm2d(tnn.BatchNorm2d):
+    def forward(self, x):
+        if _native(x) and self.affine and self.track_running_stats and self.momentum is not None:
+            from ..ops import functional as NF
+
+            if self.training and self.num_batches_tracked is not None:
+                self.num_batches_tracked.add_(1)
+            return NF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum, self.eps)
+        return super().forward(x)
+
+
+class AdaptiveAvgPool2d(tnn.AdaptiveAvgPool2d):
+    def forward(self, x):
+        if _native(x) and _pair(self.output_size) == (1, 1):
+            from ..ops import functional as NF
+
+            return NF.global_avg_pool(x)
+        return super().forward(x)

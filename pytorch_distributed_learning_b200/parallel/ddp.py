@@ -1,0 +1,372 @@
+"""DistributedDataParallel: replica-per-process data parallelism with bucketed gradient averaging.
+
+Call shape kept from the reference: ``DistributedDataParallel(model, device_ids=[g],
+output_device=g)`` (launch_dist.py:61, example_mp.py:53, example_launch.py:29) and
+``DistributedDataParallel(model, device_ids=[g])`` (mpspawn_dist.py:68).
+
+What happens, B200-first rather than a mirror of torch's reducer:
+  * constructor: parameter shapes are checked across ranks, then rank 0's parameters and
+    buffers are broadcast so every replica starts identical (the reference relies on this:
+    its ResNet scripts never seed);
+  * gradients live in ONE flat arena laid out bucket by bucket in reverse registration order
+    (≈ the order backward produces them).  On GPUs the arena is *symmetric memory*: the same
+    offsets on every rank, mapped into every peer, so the allreduce kernel reads the peers'
+    buckets straight over NVLink -- there is no copy-out, ``param.grad`` becomes a view of the
+    averaged arena;
+  * a bucket is launched on a side stream the moment its last gradient arrives (autograd
+    post-accumulate hooks), so communication overlaps the rest of backward;
+  * if the parameters belong to this package's ``optim.SGD`` the averaging kernel also applies
+    the SGD update (fused 1/W scale + weight decay + momentum + nesterov), and
+    ``optimizer.step()`` only waits for the side stream;
+  * the first backward records the real gradient arrival order; if it differs from the assumed
+    one the buckets are rebuilt once, with rank 0's order, before the second forward.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import weakref
+from contextlib import contextmanager
+
+import torch
+import torch.nn as nn
+from torch.autograd import Variable
+
+from .. import _lib
+from . import distributed as dist
+
+_MiB = 1024 * 1024
+_ALIGN_ELEMS = 4  # every parameter starts on a 16-byte boundary inside the arena (float4 access)
+
+
+def compute_bucket_assignment_by_size(sizes_bytes, limits, kinds=None):
+    """C++ bucket assignment (csrc/host/bucket.cpp). Returns list[list[int]] of tensor indices."""
+    n = len(sizes_bytes)
+    if n == 0:
+        return []
+    sizes = (ctypes.c_int64 * n)(*[int(s) for s in sizes_bytes])
+    kind_arr = (ctypes.c_int32 * n)(*([int(k) for k in kinds] if kinds is not None else [0] * n))
+    lim = (ctypes.c_int64 * len(limits))(*[int(x) for x in limits])
+    out = (ctypes.c_int32 * n)()
+    nb = _lib.host().pdl_bucket_assign(sizes, kind_arr, n, lim, len(limits), out)
+    buckets = [[] for _ in range(nb)]
+    for i in range(n):
+        buckets[out[i]].append(i)
+    return buckets
+
+
+class _Bucket:
+    __slots__ = ("index", "param_ids", "offset", "numel", "pending", "launched", "fused_group", "ready_event", "done_event", "grads")
+
+    def __init__(self, index, param_ids, offset, numel):
+        self.index, self.param_ids, self.offset, self.numel = index, param_ids, offset, numel
+        self.pending, self.launched = len(param_ids), False
+        self.fused_group = None
+        self.ready_event = self.done_event = None
+        self.grads = {}
+
+
+def _align(n, a=_ALIGN_ELEMS):
+    return (n + a - 1) // a * a
+
+
+class DistributedDataParallel(nn.Module):
+    def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True, process_group=None,
+                 bucket_cap_mb=25, find_unused_parameters=False, check_reduction=False, gradient_as_bucket_view=True,
+                 static_graph=False, algorithm=None, first_bucket_mb=1):
+        super().__init__()
+        self.process_group = process_group if process_group is not None else dist._default()
+        params = [(n, p) for n, p in module.named_parameters() if p.requires_grad]
+        if not params:
+            raise RuntimeError("DistributedDataParallel is not needed when a module doesn't have any parameter that requires a gradient.")
+        devices = {p.device for _, p in params}
+        if len(devices) != 1:
+            raise ValueError("DistributedDataParallel requires all parameters of the module on one device, got %s" % sorted(map(str, devices)))
+        self.device = next(iter(devices))
+        if self.device.type == "cuda":
+            if device_ids is not None:
+                if len(device_ids) != 1:
+                    raise ValueError("device_ids can only be None or contain a single element.")
+                dev = device_ids[0]
+                dev_index = dev.index if isinstance(dev, torch.device) else int(dev)
+                if dev_index != self.device.index:
+                    raise ValueError("device_ids=[%d] but the module's parameters live on %s" % (dev_index, self.device))
+            self.device_ids = [self.device.index]
+            if output_device is None:
+                output_device = self.device.index
+            self.output_device = output_device.index if isinstance(output_device, torch.device) else int(output_device)
+        else:
+            if device_ids or output_device is not None:
+                raise ValueError("device_ids and output_device must be None for a CPU module")
+            self.device_ids, self.output_device = None, None
+        self.module = module
+        self.dim = dim
+        self.broadcast_buffers = broadcast_buffers
+        self.find_unused_parameters = find_unused_parameters
+        self.bucket_bytes_cap = int(bucket_cap_mb * _MiB)
+        self.first_bucket_bytes = int(first_bucket_mb * _MiB)
+        self.algorithm = algorithm or os.environ.get("PDL_ALGO") or None
+        self.require_backward_grad_sync = True
+        self._param_names = [n for n, _ in params]
+        self._params = [p for _, p in params]
+        self._world = self.process_group.size()
+        self._iteration = 0
+        self._arrival = []
+        self._rebuilt = False
+        self._callback_queued = False
+        self._stats = {"buckets_launched": 0, "fused_buckets": 0, "rebuilds": 0}
+
+        self._verify_params_across_processes()
+        self._sync_module_states()
+        self._backend = self.process_group.make_reducer_backend(self.device) if hasattr(self.process_group, "make_reducer_backend") else _CpuReducerBackend(self.process_group)
+        self._build_buckets(list(reversed(range(len(self._params)))))
+        self._hook_handles = [p.register_post_accumulate_grad_hook(self._make_hook(i)) for i, p in enumerate(self._params)]
+
+    # ------------------------------------------------------------------ construction
+    def _verify_params_across_processes(self):
+        meta = [(n, tuple(p.shape), str(p.dtype)) for n, p in zip(self._param_names, self._params)]
+        everyone = self.process_group.allgather_object(meta)
+        for r, other in enumerate(everyone):
+            if other != everyone[0]:
+                raise RuntimeError("DDP expects the same model on every rank: rank %d's parameter list differs from rank 0's "
+                                   "(%d vs %d tensors, first mismatch: %s)" %
+                                   (r, len(other), len(everyone[0]), next((a for a, b in zip(other, everyone[0]) if a != b), "length")))
+
+    def _sync_module_states(self, chunk_bytes=250 * _MiB):
+        tensors = [p.data for p in self.module.parameters()] + [b for b in self.module.buffers()]
+        self._broadcast_coalesced(tensors, chunk_bytes)
+
+    def _broadcast_coalesced(self, tensors, chunk_bytes=250 * _MiB):
+        by_dtype = {}
+        for t in tensors:
+            by_dtype.setdefault(t.dtype, []).append(t)
+        for dtype, group in by_dtype.items():
+            chunk, size = [], 0
+            for t in group + [None]:
+                if t is None or (chunk and size + t.numel() * t.element_size() > chunk_bytes):
+                    if chunk:
+                        flat = torch.cat([c.reshape(-1) for c in chunk])
+                        self.process_group.broadcast(flat, 0)
+                        off = 0
+                        for c in chunk:
+                            c.copy_(flat[off:off + c.numel()].view_as(c))
+                            off += c.numel()
+                    chunk, size = [], 0
+                if t is not None:
+                    chunk.append(t)
+                    size += t.numel() * t.element_size()
+
+    def _build_buckets(self, order):
+        """order: parameter indices in expected gradient-arrival order."""
+        ps = self._params
+        dtypes = sorted({p.dtype for p in ps}, key=str)
+        if len(dtypes) != 1:
+            raise NotImplementedError("DistributedDataParallel: mixed parameter dtypes %s are not supported; cast the model to one dtype" % dtypes)
+        self._dtype = dtypes[0]
+        sizes = [ps[i].numel() * ps[i].element_size() for i in order]
+        assignment = compute_bucket_assignment_by_size(sizes, [self.first_bucket_bytes, self.bucket_bytes_cap])
+        self._buckets, self._bucket_of, self._offset_of = [], {}, {}
+        off = 0
+        for b, members in enumerate(assignment):
+            start = off
+            ids = [order[j] for j in members]
+            for i in ids:
+                self._bucket_of[i] = b
+                self._offset_of[i] = off
+                off = _align(off + ps[i].numel())
+            self._buckets.append(_Bucket(b, ids, start, off - start))
+        self._total = off
+        self._backend.allocate(self._total, self._dtype, self.device, [(bk.offset, bk.numel) for bk in self._buckets])
+        g_in, g_avg = self._backend.g_in, self._backend.g_avg
+        self._in_views = [g_in[self._offset_of[i]:self._offset_of[i] + p.numel()].view_as(p) for i, p in enumerate(ps)]
+        self._avg_views = [g_avg[self._offset_of[i]:self._offset_of[i] + p.numel()].view_as(p) for i, p in enumerate(ps)]
+        self._order = list(order)
+        self._next_bucket = 0
+        self._fused_checked = False
+
+    def bucket_sizes_bytes(self):
+        """Unpadded bytes per bucket (what the reference's stack would put on the wire)."""
+        return [sum(self._params[i].numel() * self._params[i].element_size() for i in bk.param_ids) for bk in self._buckets]
+
+    # ------------------------------------------------------------------ forward
+    def forward(self, *inputs, **kwargs):
+        if torch.is_grad_enabled() and self.require_backward_grad_sync:
+            self._maybe_rebuild_buckets()
+            self._prepare_for_backward()
+        if self.broadcast_buffers and self.require_backward_grad_sync:
+            bufs = list(self.module.buffers())
+            if bufs and self._world > 1:
+                self._broadcast_coalesced(bufs)
+        if self.device.type == "cuda":
+            inputs = tuple(self._to_device(x) for x in inputs)
+            kwargs = {k: self._to_device(v) for k, v in kwargs.items()}
+        return self.module(*inputs, **kwargs)
+
+    def _to_device(self, x):
+        if isinstance(x, torch.Tensor) and x.device != self.device:
+            return x.to(self.device, non_blocking=True)
+        return x
+
+    def _prepare_for_backward(self):
+        for bk in self._buckets:
+            bk.pending, bk.launched = len(bk.param_ids), False
+            bk.grads.clear()
+        self._next_bucket = 0
+        self._callback_queued = False
+        if self._iteration == 0:
+            self._arrival = []
+
+    def _maybe_rebuild_buckets(self):
+        if self._rebuilt or self._iteration != 1:
+            return
+        self._rebuilt = True
+        seen = list(dict.fromkeys(self._arrival))
+        seen += [i for i in self._order if i not in set(seen)]
+        order = self.process_group.broadcast_object(seen, 0)
+        if order != self._order:
+            self._stats["rebuilds"] += 1
+            old_avg = [v.clone() for v in self._avg_views]
+            self._build_buckets(order)
+            for i, p in enumerate(self._params):  # keep any grads the user still holds valid
+                self._avg_views[i].copy_(old_avg[i])
+                if p.grad is not None:
+                    p.grad = self._avg_views[i]
+
+    # ------------------------------------------------------------------ backward
+    def _make_hook(self, i):
+        ref = weakref.ref(self)
+
+        def hook(param):
+            self_ = ref()
+            if self_ is not None:
+                self_._on_grad_ready(i, param)
+
+        return hook
+
+    def _on_grad_ready(self, i, param):
+        if not self.require_backward_grad_sync:
+            return
+        if not self._callback_queued:
+            self._callback_queued = True
+            Variable._execution_engine.queue_callback(self._finalize_backward)
+        if self._iteration == 0:
+            self._arrival.append(i)
+        bk = self._buckets[self._bucket_of[i]]
+        if i in bk.grads:
+            raise RuntimeError("parameter %r received a second gradient in one backward pass; DDP reduces each parameter once per "
+                               "iteration (use no_sync() for gradient accumulation)" % self._param_names[i])
+        bk.grads[i] = param.grad
+        bk.pending -= 1
+        if bk.pending == 0:
+            self._launch_ready_buckets()
+
+    def _launch_ready_buckets(self):
+        while self._next_bucket < len(self._buckets) and self._buckets[self._next_bucket].pending == 0:
+            self._launch_bucket(self._buckets[self._next_bucket])
+            self._next_bucket += 1
+
+    def _launch_bucket(self, bk):
+        srcs, dsts = [], []
+        for i in bk.param_ids:
+            g = bk.grads.get(i)
+            view = self._in_views[i]
+            if g is None:  # parameter took no part in this backward: contributes zeros
+                view.zero_()
+            elif g.data_ptr() != view.data_ptr():
+                srcs.append(g)
+                dsts.append(view)
+        if dsts:
+            torch._foreach_copy_(dsts, srcs)
+        if not self._fused_checked:
+            self._resolve_fused_optimizers()
+        self._backend.reduce_bucket(bk, self._world, self.algorithm)
+        for i in bk.param_ids:
+            self._params[i].grad = self._avg_views[i]
+        bk.launched = True
+        bk.grads.clear()
+        self._stats["buckets_launched"] += 1
+        if bk.fused_group is not None:
+            self._stats["fused_buckets"] += 1
+
+    def _finalize_backward(self):
+        self._callback_queued = False
+        if not self.require_backward_grad_sync:
+            return
+        if self._next_bucket < len(self._buckets):
+            # some parameters produced no gradient this iteration: they contribute zeros
+            for bk in self._buckets[self._next_bucket:]:
+                bk.pending = 0
+            self._launch_ready_buckets()
+        self._backend.finish(self._buckets)
+        self._iteration += 1
+
+    # ------------------------------------------------------------------ fused optimizer
+    def _resolve_fused_optimizers(self):
+        """Look up (lazily: the optimizer may be created before or after the wrap, reference
+        launch_dist.py:59-61 vs example_launch.py:29,64) which buckets can take the fused update."""
+        self._fused_checked = True
+        if not self._backend.supports_fused_sgd:
+            return
+        from ..optim.sgd import lookup_optimizer
+
+        for bk in self._buckets:
+            owners = {lookup_optimizer(self._params[i]) for i in bk.param_ids}
+            if len(owners) != 1:
+                continue
+            owner = next(iter(owners))
+            if owner is None:
+                continue
+            opt, group = owner
+            if opt.attach_bucket(self, bk, [self._params[i] for i in bk.param_ids], [self._offset_of[i] for i in bk.param_ids], group):
+                bk.fused_group = (opt, group)
+
+    # ------------------------------------------------------------------ API parity
+    @contextmanager
+    def no_sync(self):
+        """Skip gradient averaging inside the block (local accumulation into ``.grad``)."""
+        old = self.require_backward_grad_sync
+        self.require_backward_grad_sync = False
+        try:
+            yield
+        finally:
+            self.require_backward_grad_sync = old
+
+    def get_step_stats(self):
+        stats = dict(self._stats)
+        stats["bucket_bytes"] = self.bucket_sizes_bytes()
+        stats["iterations"] = self._iteration
+        stats.update(self._backend.stats())
+        return stats
+
+    def state_dict(self, *args, **kwargs):
+        return super().state_dict(*args, **kwargs)
+
+    def train(self, mode=True):
+        super().train(mode)
+        return self
+
+
+class _CpuReducerBackend:
+    """Reducer data plane for the CPU ("gloo") group: in-place allreduce, then scale by 1/W."""
+
+    supports_fused_sgd = False
+
+    def __init__(self, pg):
+        self.pg = pg
+        self.g_in = self.g_avg = None
+
+    def allocate(self, total, dtype, device, bucket_ranges):
+        self.g_in = torch.zeros(total, dtype=dtype, device=device)
+        self.g_avg = self.g_in
+
+    def reduce_bucket(self, bk, world, algorithm):
+        flat = self.g_in[bk.offset:bk.offset + bk.numel]
+        if world > 1:
+            self.pg.allreduce(flat, dist.ReduceOp.SUM)
+            flat.mul_(1.0 / world)
+
+    def finish(self, buckets):
+        pass
+
+    def stats(self):
+        return {"backend": "cpu"}

@@ -1,0 +1,71 @@
+import os
+import subprocess
+import sys
+import time
+
+import pytest
+
+import _workers
+import pytorch_distributed_learning_b200 as pdl
+from pytorch_distributed_learning_b200 import launch
+from pytorch_distributed_learning_b200.parallel.spawn import ProcessExitedException, ProcessRaisedException
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_spawn_runs_every_rank(tmp_path):
+    assert pdl.multiprocessing.spawn(_workers.ok_worker, args=(str(tmp_path),), nprocs=3) is None
+    assert sorted(os.listdir(tmp_path)) == ["ok0", "ok1", "ok2"]
+
+
+def test_spawn_propagates_child_exception_and_kills_siblings(tmp_path):
+    t0 = time.time()
+    with pytest.raises(ProcessRaisedException, match="boom from rank 1") as ei:
+        pdl.multiprocessing.spawn(_workers.failing, args=(str(tmp_path),), nprocs=2)
+    assert ei.value.error_index == 1
+    assert time.time() - t0 < 45  # the sleeping sibling was terminated, not waited for
+    assert not os.path.exists(tmp_path / "survivor")
+
+
+def test_spawn_reports_exit_code():
+    with pytest.raises(ProcessExitedException) as ei:
+        pdl.multiprocessing.spawn(_workers.exiting, nprocs=2)
+    assert ei.value.exit_code == 7 and ei.value.error_index == 0
+
+
+def test_spawn_nonblocking_context(tmp_path):
+    ctx = pdl.multiprocessing.spawn(_workers.ok_worker, args=(str(tmp_path),), nprocs=2, join=False)
+    assert len(ctx.pids()) == 2
+    while not ctx.join():
+        pass
+
+
+def test_launch_env_contract():
+    env = launch.worker_env({}, node_rank=1, local_rank=2, nproc=4, nnodes=2, master_addr="10.0.0.9", master_port=8888)
+    assert env == {"RANK": "6", "LOCAL_RANK": "2", "WORLD_SIZE": "8", "LOCAL_WORLD_SIZE": "4", "GROUP_RANK": "1",
+                   "MASTER_ADDR": "10.0.0.9", "MASTER_PORT": "8888", "OMP_NUM_THREADS": "1"}
+    args = launch.build_parser().parse_args(["--nproc_per_node=2", "--nnodes=1", "--node_rank=0", "--master_addr=127.0.0.1",
+                                             "--master_port=1234", "train.py", "--epochs", "3"])
+    assert launch.worker_cmd(args, 1)[-4:] == ["train.py", "--epochs", "3", "--local-rank=1"]
+    args = launch.build_parser().parse_args(["--use_env", "train.py"])
+    assert launch.worker_cmd(args, 0)[-1] == "train.py"
+
+
+def test_launch_end_to_end(tmp_path):
+    script = tmp_path / "w.py"
+    script.write_text(
+        "import os,sys\n"
+        "open(os.path.join(%r, 'r'+os.environ['RANK']), 'w').write(' '.join([os.environ['LOCAL_RANK'], os.environ['WORLD_SIZE'], sys.argv[-1]]))\n" % str(tmp_path))
+    rc = subprocess.run([sys.executable, "-m", "pytorch_distributed_learning_b200.launch", "--nproc_per_node=2", "--master_port=29411",
+                         str(script)], cwd=ROOT, timeout=120).returncode
+    assert rc == 0
+    assert (tmp_path / "r0").read_text() == "0 2 --local-rank=0" and (tmp_path / "r1").read_text() == "1 2 --local-rank=1"
+
+
+def test_launch_failure_stops_the_job(tmp_path):
+    script = tmp_path / "f.py"
+    script.write_text("import os,sys,time\nif os.environ['RANK']=='1': sys.exit(3)\ntime.sleep(60)\n")
+    t0 = time.time()
+    rc = subprocess.run([sys.executable, "-m", "pytorch_distributed_learning_b200.launch", "--nproc_per_node=2", "--use_env", str(script)],
+                        cwd=ROOT, timeout=120).returncode
+    assert rc == 3 and time.time() - t0 < 45
