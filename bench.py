@@ -1,0 +1,294 @@
+#!/usr/bin/env python
+"""Headline benchmark: images/sec of the reference's DDP training step on N B200s of one node.
+
+    python bench.py --gpus 1 --steps 200 --warmup 20
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port P bench.py --gpus 8 ...
+    python bench.py --impl reference ...        # the unmodified reference model on stock torch DDP + NCCL
+
+Config (BASELINE.json): MNIST-shaped ConvNet (reference launch_dist.py), synthetic 1x28x28 data,
+batch 100 per rank, SGD lr 1e-4, fp32 storage.  ``--model resnet50`` / ``--batch`` select the other
+BASELINE configs.  Timing: W warm-up steps, then exactly K steps between barrier+synchronize,
+CUDA events on the launching stream, max over ranks.  Inputs rotate through a pool of distinct
+batches larger than the 126 MB L2, so no step finds its batch in cache.  ``value`` is the
+device-resident-input number; ``e2e`` repeats it through the public API with a pinned-host H2D
+copy of each batch and a D2H read of each loss inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import socket
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+L2_BYTES = 126 * 1024 * 1024
+
+
+def parse_args():
+    p = argparse.ArgumentParser()
+    p.add_argument("--gpus", type=int, default=1)
+    p.add_argument("--steps", type=int, default=200)
+    p.add_argument("--warmup", type=int, default=20)
+    p.add_argument("--impl", choices=["ours", "reference"], default="ours")
+    p.add_argument("--model", choices=["convnet", "resnet18", "resnet50"], default="convnet")
+    p.add_argument("--batch", type=int, default=None, help="per-rank batch (default: 100 ConvNet, 128 ResNet-18, 64 ResNet-50)")
+    p.add_argument("--eager", action="store_true", help="ours: run the reference-style eager loop instead of the graphed TrainStep")
+    p.add_argument("--algorithm", default=None, help="ours: force an allreduce variant (oneshot|twoshot|ring|nvls)")
+    p.add_argument("--local-rank", "--local_rank", type=int, default=None)
+    return p.parse_args()
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons for one GPU while the timed region runs."""
+
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._read, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 6:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = float(r[1])
+            except ValueError:
+                continue
+            for name, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def ensure_reference_tree():
+    """baseline/_ref holds an unmodified copy of the reference (it has no setup.py, so `pip install
+    --target baseline/_ref /root/reference` cannot work -- see DESIGN.md); copy the scripts verbatim."""
+    dst = os.path.join(ROOT, "baseline", "_ref")
+    src = "/root/reference"
+    if not os.path.exists(os.path.join(dst, "launch_dist.py")) and os.path.isdir(src):
+        import shutil
+
+        os.makedirs(dst, exist_ok=True)
+        for f in os.listdir(src):
+            if os.path.isfile(os.path.join(src, f)):
+                shutil.copy2(os.path.join(src, f), os.path.join(dst, f))
+    return dst if os.path.exists(os.path.join(dst, "launch_dist.py")) else None
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        ref_dir = ensure_reference_tree()
+        if ref_dir is None:
+            print(json.dumps({"impl": "reference", "unavailable": "baseline/_ref is empty and /root/reference is not mounted on this box"}))
+            return 0
+    import torch
+
+    if not torch.cuda.is_available():
+        print(json.dumps({"impl": args.impl, "unavailable": "no CUDA device visible"}))
+        return 0
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", str(rank)))
+    if "MASTER_ADDR" not in os.environ:
+        os.environ["MASTER_ADDR"] = "127.0.0.1"
+        os.environ["MASTER_PORT"] = str(free_port())
+        os.environ["RANK"], os.environ["WORLD_SIZE"], os.environ["LOCAL_RANK"] = str(rank), str(world), str(local_rank)
+    if world != args.gpus and rank == 0:
+        sys.stderr.write("bench: --gpus %d but WORLD_SIZE=%d (launch with torch.distributed.run for N>1); using WORLD_SIZE\n" % (args.gpus, world))
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    batch = args.batch or {"convnet": 100, "resnet18": 128, "resnet50": 64}[args.model]
+    shape = {"convnet": (1, 28, 28), "resnet18": (3, 32, 32), "resnet50": (3, 224, 224)}[args.model]
+    classes = {"convnet": 10, "resnet18": 10, "resnet50": 1000}[args.model]
+    opt_kw = dict(lr=1e-4) if args.model == "convnet" else dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)
+
+    # ---------------- model + DDP + step function ----------------
+    kernels_per_step = 0
+    if args.impl == "reference":
+        import torch.distributed as tdist
+        import torch.nn as tnn
+
+        sys.path.insert(0, ref_dir)
+        tdist.init_process_group(backend="nccl", device_id=dev)
+        torch.manual_seed(0)
+        if args.model == "convnet":
+            import launch_dist as ref_script  # the reference file itself; its __main__ block is not executed
+
+            model = ref_script.ConvNet().to(dev)
+        else:
+            import torchvision
+
+            model = getattr(torchvision.models, args.model)(num_classes=classes).to(dev)
+        criterion = tnn.CrossEntropyLoss().cuda(local_rank)
+        optimizer = torch.optim.SGD(model.parameters(), **opt_kw)
+        model = tnn.parallel.DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank)
+
+        def step_fn(images, labels):  # loop body of launch_dist.py:82-92
+            images = images.cuda(non_blocking=True)
+            labels = labels.cuda(non_blocking=True)
+            outputs = model(images)
+            loss = criterion(outputs, labels)
+            optimizer.zero_grad()
+            loss.backward()
+            optimizer.step()
+            return loss
+
+        def barrier():
+            tdist.barrier()
+
+        def gather_max(v):
+            t = torch.tensor([v], dtype=torch.float64, device=dev)
+            tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
+            return float(t.item())
+
+        def shutdown():
+            tdist.destroy_process_group()
+        parallelism, mode = "dp%d (torch DDP + NCCL)" % world, "eager"
+    else:
+        import pytorch_distributed_learning_b200 as pdl
+
+        dist = pdl.distributed
+        dist.init_process_group(backend="nccl")
+        torch.manual_seed(0)
+        model = (pdl.models.ConvNet() if args.model == "convnet" else getattr(pdl.models, args.model)(num_classes=classes)).to(dev)
+        criterion = pdl.nn.CrossEntropyLoss().cuda(local_rank)
+        optimizer = pdl.optim.SGD(model.parameters(), **opt_kw)
+        model = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank, algorithm=args.algorithm)
+        train_step = pdl.TrainStep(model, criterion, optimizer, use_graph=not args.eager)
+        step_fn = train_step
+
+        def barrier():
+            torch.cuda.synchronize()
+            dist.barrier()
+
+        def gather_max(v):
+            return max(dist._default().allgather_object(float(v)))
+
+        def shutdown():
+            dist.destroy_process_group()
+        parallelism = "dp%d (P2P NVLink allreduce fused with SGD)" % world
+        mode = "cuda-graph" if train_step.graphed else "eager"
+
+    # ---------------- synthetic data: pool larger than L2 ----------------
+    per_batch = batch * (shape[0] * shape[1] * shape[2]) * 4
+    pool = max(4, min(1024, L2_BYTES // per_batch + 2))
+    g = torch.Generator().manual_seed(1234 + rank)
+    host_x = [torch.randn((batch,) + shape, generator=g).pin_memory() for _ in range(pool)]
+    host_y = [torch.randint(0, classes, (batch,), generator=g).pin_memory() for _ in range(pool)]
+    dev_pool = min(pool, max(4, (8 << 30) // per_batch))
+    dev_x = [t.to(dev) for t in host_x[:dev_pool]]
+    dev_y = [t.to(dev) for t in host_y[:dev_pool]]
+
+    # ---------------- device-timed run (inputs resident on the GPU) ----------------
+    for i in range(max(3, args.warmup)):
+        step_fn(dev_x[i % dev_pool], dev_y[i % dev_pool])
+    if args.impl == "ours":
+        kernels_per_step = train_step.kernels_per_step() or 0
+    barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t_wall0 = time.perf_counter()
+    start.record()
+    for i in range(args.steps):
+        step_fn(dev_x[i % dev_pool], dev_y[i % dev_pool])
+    stop.record()
+    torch.cuda.synchronize()
+    barrier()
+    wall_ms = (time.perf_counter() - t_wall0) * 1e3
+    dev_ms = start.elapsed_time(stop)
+    clocks = sampler.stop()
+    dev_ms = gather_max(dev_ms)
+    wall_ms = gather_max(wall_ms)
+
+    # ---------------- end to end: pinned host batch -> H2D -> step -> loss D2H, every step ----------------
+    for i in range(3):
+        float(step_fn(host_x[i % pool], host_y[i % pool]).item())
+    barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    loss_sum = 0.0
+    for i in range(args.steps):
+        loss_sum += float(step_fn(host_x[i % pool], host_y[i % pool]).item())
+    e1.record()
+    torch.cuda.synchronize()
+    barrier()
+    e2e_ms = gather_max(e0.elapsed_time(e1))
+
+    stats = {}
+    if args.impl == "ours":
+        try:
+            stats = model.get_step_stats()
+        except Exception:
+            stats = {}
+    if rank == 0:
+        global_batch = batch * world
+        out = {
+            "metric": "images/sec", "value": global_batch * args.steps / (dev_ms / 1e3), "unit": "images/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "fp32", "data": "synthetic", "impl": args.impl,
+            "config": {"model": {"convnet": "ConvNet (reference launch_dist.py, MNIST-shaped 1x28x28)", "resnet18": "ResNet-18 (3x32x32, 10 classes)",
+                                 "resnet50": "ResNet-50 (3x224x224)"}[args.model],
+                       "global_batch": global_batch, "per_gpu_batch": batch, "seq_len": None, "parallelism": parallelism, "optimizer": "SGD %s" % opt_kw,
+                       "execution": mode, "l2_policy": "inputs rotate through a pool of %d distinct batches (%.0f MB > 126 MB L2)" % (dev_pool, dev_pool * per_batch / 1e6),
+                       "weights": "random init", "timing": "CUDA events, max over ranks; wall %.3f ms/step" % (wall_ms / args.steps)},
+            "clocks": clocks,
+            "e2e": {"value": global_batch * args.steps / (e2e_ms / 1e3), "unit": "images/s", "ms_per_step": e2e_ms / args.steps,
+                    "h2d_bytes_per_step": per_batch + batch * 8, "d2h_bytes_per_step": 4, "mean_loss": loss_sum / args.steps},
+            "gpu_launches": int(kernels_per_step * args.steps) if args.impl == "ours" else None,
+        }
+        if stats:
+            out["config"]["allreduce"] = stats.get("algorithms")
+            if "exposed_comm_ms" in stats:
+                out["exposed_comm_ms_per_step"] = stats["exposed_comm_ms"]
+        print(json.dumps(out))
+        sys.stdout.flush()
+    shutdown()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

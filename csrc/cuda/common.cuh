@@ -1,0 +1,46 @@
+// Shared helpers for the sm_100a kernel library (plain C ABI, loaded with ctypes).
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <cstdio>
+
+#define PDL_API extern "C" __attribute__((visibility("default")))
+
+// Every entry point returns 0 on success or a negative/CUDA error code; the message is kept
+// in a thread-local buffer readable through pdl_last_error().
+void pdl_set_error(const char* fmt, ...);
+
+#define PDL_CUDA_CHECK(expr)                                                                  \
+  do {                                                                                        \
+    cudaError_t _e = (expr);                                                                  \
+    if (_e != cudaSuccess) {                                                                  \
+      pdl_set_error("%s failed at %s:%d: %s", #expr, __FILE__, __LINE__, cudaGetErrorString(_e)); \
+      return static_cast<int>(_e);                                                            \
+    }                                                                                         \
+  } while (0)
+
+#define PDL_LAUNCH_CHECK() PDL_CUDA_CHECK(cudaGetLastError())
+
+static inline int pdl_ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
+
+struct SgdHyper {  // lives in device memory so a captured CUDA graph sees LR-schedule changes
+  float lr;
+  float momentum;
+  float dampening;
+  float weight_decay;
+  int nesterov;
+  int first_step;  // 1 until the first update has run (momentum buffer := gradient)
+  int pad0, pad1;
+};
+
+// One SGD update, identical to the rule the reference's optimizer applies
+// (launch_dist.py:59 plain SGD; example_launch.py:64-70 momentum+wd+nesterov).
+__device__ __forceinline__ float sgd_update(float p, float g, float* m_inout, const SgdHyper& h, bool has_momentum) {
+  g = fmaf(h.weight_decay, p, g);
+  if (has_momentum) {
+    float buf = h.first_step ? g : fmaf(h.momentum, *m_inout, (1.0f - h.dampening) * g);
+    *m_inout = buf;
+    g = h.nesterov ? fmaf(h.momentum, buf, g) : buf;
+  }
+  return fmaf(-h.lr, g, p);
+}

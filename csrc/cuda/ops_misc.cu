@@ -1,0 +1,267 @@
+// Element-wise / pooling / linear / loss kernels (NHWC fp32) for the reference's models:
+//   ReLU, MaxPool2d incl. the overlapping 2/1 window (launch_dist.py:17-27), Linear 2048->10 in
+//   strict fp32 (launch_dist.py:32; the reference's cuBLAS sgemm is not TF32), CrossEntropyLoss
+//   mean-reduced with integer targets (launch_dist.py:58), ResNet's residual add+ReLU and
+//   global average pool.  Pool backward is gather-style (each input looks at the <=ceil(k/s)^2
+//   windows that contain it), so overlapping windows need no atomics and stay deterministic.
+#include "igemm_simt.cuh"
+
+#include <cfloat>
+
+namespace {
+
+constexpr int kThreads = 256;
+
+__global__ void relu_fwd_kernel(const float4* __restrict__ x, float4* __restrict__ y, long long n4) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i < n4) {
+    float4 v = x[i];
+    y[i] = make_float4(fmaxf(v.x, 0.f), fmaxf(v.y, 0.f), fmaxf(v.z, 0.f), fmaxf(v.w, 0.f));
+  }
+}
+__global__ void relu_fwd_tail(const float* __restrict__ x, float* __restrict__ y, long long from, long long n) {
+  long long i = from + blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i < n) y[i] = fmaxf(x[i], 0.f);
+}
+__global__ void relu_bwd_kernel(const float* __restrict__ y, const float* __restrict__ dy, float* __restrict__ dx, long long n) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i < n) dx[i] = y[i] > 0.f ? dy[i] : 0.f;
+}
+__global__ void add_relu_fwd_kernel(const float* __restrict__ a, const float* __restrict__ b, float* __restrict__ y, long long n) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i < n) y[i] = fmaxf(a[i] + b[i], 0.f);
+}
+
+// y[n,p,q,c] = max over the window; idx = r*k+s of the FIRST maximum in scan order (torch's tie rule).
+__global__ void maxpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ idx, int N, int H, int W, int C,
+                                   int k, int stride, int pad, int P, int Q) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  long long total = static_cast<long long>(N) * P * Q * C;
+  if (i >= total) return;
+  int c = i % C;
+  long long t = i / C;
+  int q = t % Q; t /= Q;
+  int p = t % P;
+  int n = static_cast<int>(t / P);
+  float best = -INFINITY;
+  int arg = -1;
+  for (int r = 0; r < k; ++r) {
+    int h = p * stride - pad + r;
+    if (h < 0 || h >= H) continue;
+    for (int s = 0; s < k; ++s) {
+      int w = q * stride - pad + s;
+      if (w < 0 || w >= W) continue;
+      float v = x[((static_cast<long long>(n) * H + h) * W + w) * C + c];
+      if (arg < 0 || v > best || v != v) { best = v; arg = r * k + s; }  // first max wins; NaN propagates
+    }
+  }
+  y[i] = best;
+  idx[i] = static_cast<uint8_t>(arg);
+}
+
+// dx[n,h,w,c] = sum of dy over the windows whose argmax is (h,w).  If relu_out != nullptr the ReLU
+// that preceded the pool is folded in: windows whose pooled value is <= 0 pass no gradient.
+__global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* __restrict__ idx, const float* __restrict__ pooled,
+                                   float* __restrict__ dx, int N, int H, int W, int C, int k, int stride, int pad, int P, int Q, int fuse_relu) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  long long total = static_cast<long long>(N) * H * W * C;
+  if (i >= total) return;
+  int c = i % C;
+  long long t = i / C;
+  int w = t % W; t /= W;
+  int h = t % H;
+  int n = static_cast<int>(t / H);
+  float acc = 0.f;
+  for (int r = 0; r < k; ++r) {
+    int ph = h + pad - r;
+    if (ph < 0 || ph % stride) continue;
+    int p = ph / stride;
+    if (p >= P) continue;
+    for (int s = 0; s < k; ++s) {
+      int qw = w + pad - s;
+      if (qw < 0 || qw % stride) continue;
+      int q = qw / stride;
+      if (q >= Q) continue;
+      long long o = ((static_cast<long long>(n) * P + p) * Q + q) * C + c;
+      if (idx[o] == r * k + s && (!fuse_relu || pooled[o] > 0.f)) acc += dy[o];
+    }
+  }
+  dx[i] = acc;
+}
+
+__global__ void global_avgpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, int N, int HW, int C) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= N * C) return;
+  int c = i % C, n = i / C;
+  float acc = 0.f;
+  for (int j = 0; j < HW; ++j) acc += x[(static_cast<long long>(n) * HW + j) * C + c];
+  y[i] = acc / HW;
+}
+__global__ void global_avgpool_bwd_kernel(const float* __restrict__ dy, float* __restrict__ dx, int N, int HW, int C) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i >= static_cast<long long>(N) * HW * C) return;
+  int c = i % C;
+  int n = static_cast<int>(i / (static_cast<long long>(HW) * C));
+  dx[i] = dy[n * C + c] / HW;
+}
+
+// Layout change at the flatten boundary: the reference flattens NCHW (x.view(-1, 128*4*4),
+// launch_dist.py:39) while activations here are NHWC.  to_nchw=1: y[n][c][hw] = x[n][hw][c].
+__global__ void permute_nhwc_nchw_kernel(const float* __restrict__ x, float* __restrict__ y, int N, int HW, int C, int to_nchw) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i >= static_cast<long long>(N) * HW * C) return;
+  int per = HW * C;
+  int n = static_cast<int>(i / per), j = static_cast<int>(i % per);
+  if (to_nchw) { int c = j / HW, hw = j % HW; y[i] = x[static_cast<long long>(n) * per + hw * C + c]; }
+  else { int hw = j / C, c = j % C; y[i] = x[static_cast<long long>(n) * per + c * HW + hw]; }
+}
+
+// ---- Linear (strict fp32) via the SIMT GEMM ----
+struct RowMajorA { const float* a; int ld; __device__ float operator()(int m, int k) const { return a[static_cast<long long>(m) * ld + k]; } };
+struct ColOfRowMajorB { const float* b; int ld; __device__ float operator()(int k, int n) const { return b[static_cast<long long>(n) * ld + k]; } };
+struct RowMajorB { const float* b; int ld; __device__ float operator()(int k, int n) const { return b[static_cast<long long>(k) * ld + n]; } };
+struct TransA { const float* a; int ld; __device__ float operator()(int m, int k) const { return a[static_cast<long long>(k) * ld + m]; } };
+struct StoreBias {
+  float* c; const float* bias; int ld;
+  __device__ void operator()(int m, int n, float v, int) const { c[static_cast<long long>(m) * ld + n] = v + (bias ? bias[n] : 0.f); }
+};
+struct OnesColB {  // B(k, n) = x[k][n] for n < cols, 1 for the extra bias column
+  const float* b; int ld; int cols;
+  __device__ float operator()(int k, int n) const { return n < cols ? b[static_cast<long long>(k) * ld + n] : 1.0f; }
+};
+struct StoreWgrad {
+  float* dw; float* db; int cols;
+  __device__ void operator()(int m, int n, float v, int) const {
+    if (n < cols) dw[static_cast<long long>(m) * cols + n] = v;
+    else if (db) db[m] = v;
+  }
+};
+
+// ---- CrossEntropy: one warp per row; last CTA reduces the per-row losses in index order ----
+__device__ unsigned int g_ce_done_counter = 0;
+
+__global__ void __launch_bounds__(kThreads) cross_entropy_kernel(const float* __restrict__ logits, const long long* __restrict__ target, int N,
+                                                                 int C, float* __restrict__ row_loss, float* __restrict__ loss,
+                                                                 float* __restrict__ dlogits, const float* __restrict__ grad_scale) {
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  const int row = blockIdx.x * (kThreads / 32) + warp;
+  if (row < N) {
+    const float* x = logits + static_cast<long long>(row) * C;
+    float mx = -FLT_MAX;
+    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, x[c]);
+    for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+    float sum = 0.f;
+    for (int c = lane; c < C; c += 32) sum += expf(x[c] - mx);
+    for (int o = 16; o; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+    const float lse = logf(sum) + mx;
+    const int tgt = static_cast<int>(target[row]);
+    if (lane == 0) row_loss[row] = lse - x[tgt];
+    if (dlogits) {
+      const float g = (grad_scale ? *grad_scale : 1.0f) / N;
+      for (int c = lane; c < C; c += 32) dlogits[static_cast<long long>(row) * C + c] = (expf(x[c] - lse) - (c == tgt ? 1.f : 0.f)) * g;
+    }
+  }
+  __shared__ bool is_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    unsigned int done = atomicAdd(&g_ce_done_counter, 1u);
+    is_last = done == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    __shared__ float part[kThreads];
+    float acc = 0.f;
+    // fixed partition + fixed tree => the same bits every run
+    int per = (N + kThreads - 1) / kThreads, lo = threadIdx.x * per, hi = min(N, lo + per);
+    for (int i = lo; i < hi; ++i) acc += __ldcg(row_loss + i);
+    part[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = kThreads / 2; s; s >>= 1) {
+      if (threadIdx.x < s) part[threadIdx.x] += part[threadIdx.x + s];
+      __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+      *loss = part[0] / N;
+      g_ce_done_counter = 0;
+    }
+  }
+}
+
+int launch_1d(long long n) { return pdl_ceil_div(n, kThreads); }
+
+}  // namespace
+
+PDL_API int pdl_relu_fwd(const float* x, float* y, long long n, cudaStream_t stream) {
+  bool vec = ((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0;
+  long long n4 = vec ? n / 4 : 0;
+  if (n4) relu_fwd_kernel<<<launch_1d(n4), kThreads, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), n4);
+  if (n4 * 4 < n) relu_fwd_tail<<<launch_1d(n - n4 * 4), kThreads, 0, stream>>>(x, y, n4 * 4, n);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+PDL_API int pdl_relu_bwd(const float* y, const float* dy, float* dx, long long n, cudaStream_t stream) {
+  if (n) relu_bwd_kernel<<<launch_1d(n), kThreads, 0, stream>>>(y, dy, dx, n);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+PDL_API int pdl_add_relu_fwd(const float* a, const float* b, float* y, long long n, cudaStream_t stream) {
+  if (n) add_relu_fwd_kernel<<<launch_1d(n), kThreads, 0, stream>>>(a, b, y, n);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+PDL_API int pdl_maxpool_fwd(const float* x, float* y, uint8_t* idx, int N, int H, int W, int C, int k, int stride, int pad, cudaStream_t stream) {
+  int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
+  long long total = static_cast<long long>(N) * P * Q * C;
+  if (total) maxpool_fwd_kernel<<<launch_1d(total), kThreads, 0, stream>>>(x, y, idx, N, H, W, C, k, stride, pad, P, Q);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+PDL_API int pdl_maxpool_bwd(const float* dy, const uint8_t* idx, const float* pooled, float* dx, int N, int H, int W, int C, int k, int stride,
+                            int pad, int fuse_relu, cudaStream_t stream) {
+  int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
+  long long total = static_cast<long long>(N) * H * W * C;
+  if (total) maxpool_bwd_kernel<<<launch_1d(total), kThreads, 0, stream>>>(dy, idx, pooled, dx, N, H, W, C, k, stride, pad, P, Q, fuse_relu);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+PDL_API int pdl_global_avgpool_fwd(const float* x, float* y, int N, int HW, int C, cudaStream_t stream) {
+  global_avgpool_fwd_kernel<<<launch_1d(static_cast<long long>(N) * C), kThreads, 0, stream>>>(x, y, N, HW, C);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+PDL_API int pdl_global_avgpool_bwd(const float* dy, float* dx, int N, int HW, int C, cudaStream_t stream) {
+  global_avgpool_bwd_kernel<<<launch_1d(static_cast<long long>(N) * HW * C), kThreads, 0, stream>>>(dy, dx, N, HW, C);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+PDL_API int pdl_permute_nhwc_nchw(const float* x, float* y, int N, int HW, int C, int to_nchw, cudaStream_t stream) {
+  long long total = static_cast<long long>(N) * HW * C;
+  if (total) permute_nhwc_nchw_kernel<<<launch_1d(total), kThreads, 0, stream>>>(x, y, N, HW, C, to_nchw);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// y[M,N] = x[M,K] * w[N,K]^T + b
+PDL_API int pdl_linear_fwd(const float* x, const float* w, const float* b, float* y, int M, int N, int K, cudaStream_t stream) {
+  return simt::launch(M, N, K, 1, RowMajorA{x, K}, ColOfRowMajorB{w, K}, StoreBias{y, b, N}, stream);
+}
+// dx[M,K] = dy[M,N] * w[N,K]
+PDL_API int pdl_linear_dgrad(const float* dy, const float* w, float* dx, int M, int N, int K, cudaStream_t stream) {
+  return simt::launch(M, K, N, 1, RowMajorA{dy, N}, RowMajorB{w, K}, StoreBias{dx, nullptr, K}, stream);
+}
+// dw[N,K] = dy[M,N]^T * x[M,K];  db[N] = column sums of dy (folded in as one extra GEMM column)
+PDL_API int pdl_linear_wgrad(const float* x, const float* dy, float* dw, float* db, int M, int N, int K, cudaStream_t stream) {
+  return simt::launch(N, K + (db ? 1 : 0), M, 1, TransA{dy, N}, OnesColB{x, K, K}, StoreWgrad{dw, db, K}, stream);
+}
+
+// loss (scalar, mean over rows) and, if dlogits != nullptr, d loss / d logits * (*grad_scale or 1).
+PDL_API int pdl_cross_entropy(const float* logits, const long long* target, int N, int C, float* row_loss, float* loss, float* dlogits,
+                              const float* grad_scale, cudaStream_t stream) {
+  int blocks = pdl_ceil_div(N, kThreads / 32);
+  cross_entropy_kernel<<<blocks, kThreads, 0, stream>>>(logits, target, N, C, row_loss, loss, dlogits, grad_scale);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}

@@ -1,0 +1,70 @@
+"""ctypes signatures of libpdl_cuda.so (mirrors include/pdl_b200.h)."""
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_longlong, c_uint64, c_void_p
+
+P = c_void_p
+I = c_int
+LL = c_longlong
+F = c_float
+
+
+def declare(L):
+    def sig(name, args, res=c_int):
+        fn = getattr(L, name)
+        fn.argtypes = args
+        fn.restype = res
+
+    sig("pdl_last_error", [], c_char_p)
+    sig("pdl_cuda_device_count", [])
+    # symmetric memory
+    sig("pdl_symm_multicast_supported", [I])
+    sig("pdl_symm_begin", [I, I, I, c_uint64, c_char_p, I, POINTER(P)])
+    sig("pdl_symm_exchange", [P])
+    sig("pdl_symm_multicast_ready", [P])
+    sig("pdl_symm_bind_multicast", [P, I])
+    sig("pdl_symm_bytes", [P], c_uint64)
+    sig("pdl_symm_ptr", [P, I], P)
+    sig("pdl_symm_mc_ptr", [P], P)
+    sig("pdl_symm_dev_ptrs", [P], P)
+    sig("pdl_symm_destroy", [P])
+    # collectives
+    sig("pdl_comm_state_bytes", [])
+    sig("pdl_signal_pad_bytes", [])
+    sig("pdl_comm_max_blocks", [])
+    sig("pdl_comm_max_channels", [])
+    sig("pdl_sgd_hyper_bytes", [])
+    sig("pdl_allreduce_blocks", [LL, I, I])
+    sig("pdl_allreduce_launch", [I, I, I, I, LL, P, P, P, P, P, P, P, P, P, P, I, c_double, c_double, P])
+    sig("pdl_allreduce_emulated", [I, I, LL, P, P, P, P, P, P, P, P, I, P])
+    sig("pdl_pull_launch", [I, I, I, I, LL, P, P, P, P, I, c_double, P])
+    # optimizer
+    sig("pdl_sgd_chunk_elems", [])
+    sig("pdl_multi_tensor_sgd", [P, P, I, I, F, F, F, F, I, I, P])
+    # convolution (CUDA-core fallback / oracle)
+    sig("pdl_conv2d_fwd_simt", [P, P, P, P, I, I, I, I, I, I, I, I, I, I, P])
+    sig("pdl_conv2d_dgrad_simt", [P, P, P, I, I, I, I, I, I, I, I, I, P])
+    sig("pdl_conv2d_wgrad_scratch_bytes", [I, I, I, I, I, I, I, I, I], LL)
+    sig("pdl_conv2d_wgrad_simt", [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P])
+    # element-wise / pooling / linear / loss
+    sig("pdl_relu_fwd", [P, P, LL, P])
+    sig("pdl_relu_bwd", [P, P, P, LL, P])
+    sig("pdl_add_relu_fwd", [P, P, P, LL, P])
+    sig("pdl_maxpool_fwd", [P, P, P, I, I, I, I, I, I, I, P])
+    sig("pdl_maxpool_bwd", [P, P, P, P, I, I, I, I, I, I, I, I, P])
+    sig("pdl_global_avgpool_fwd", [P, P, I, I, I, P])
+    sig("pdl_global_avgpool_bwd", [P, P, I, I, I, P])
+    sig("pdl_permute_nhwc_nchw", [P, P, I, I, I, I, P])
+    sig("pdl_linear_fwd", [P, P, P, P, I, I, I, P])
+    sig("pdl_linear_dgrad", [P, P, P, I, I, I, P])
+    sig("pdl_linear_wgrad", [P, P, P, P, I, I, I, P])
+    sig("pdl_cross_entropy", [P, P, I, I, P, P, P, P, P])
+    for name, args, res in _OPTIONAL:
+        if hasattr(L, name):
+            sig(name, args, res)
+
+
+# entry points added by later kernels register here: (name, argtypes, restype)
+_OPTIONAL = []
+
+
+def optional(name, args, res=c_int):
+    _OPTIONAL.append((name, args, res))

@@ -1,0 +1,229 @@
+"""Graph-captured training step for the reference's ConvNet (launch_dist.py:9-41, loop :80-92).
+
+One CUDA graph holds the whole iteration: forward kernels (conv+bias+ReLU, pool with argmax),
+loss, backward kernels (pool-backward with the ReLU mask folded in, wgrad written straight into
+the gradient bucket, dgrad), and the peer-to-peer allreduce fused with 1/W averaging and SGD.
+A step is then: two async H2D copies (if the batch is in host memory) + one graph launch.
+
+Buffers are static per batch size; the gradient bucket is DDP's symmetric arena when the model
+is wrapped (so the in-graph allreduce kernel reads the peers' buckets over NVLink), or a private
+flat buffer for a single un-wrapped GPU.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from .. import _lib
+from . import functional as NF
+
+_p = NF._p
+
+
+class _SoloArena:
+    """World-size-1 stand-in for DDP's bucket arena (no process group needed)."""
+
+    def __init__(self, params, opt_group, optimizer, device):
+        offs, off = [], 0
+        for p in params:
+            offs.append(off)
+            off = (off + p.numel() + 3) // 4 * 4
+        self.total, self.offsets = off, offs
+        self.g_in = torch.zeros(off, dtype=torch.float32, device=device)
+        self.g_avg = torch.zeros(off, dtype=torch.float32, device=device)
+        self.p_flat = torch.zeros(off, dtype=torch.float32, device=device)
+        self.m_flat = torch.zeros(off, dtype=torch.float32, device=device) if opt_group["momentum"] != 0 else None
+        self.state = torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device=device)
+        self.hyper = torch.zeros(8, dtype=torch.float32, device=device)
+        self.hyper_vals = None
+        self.first = 1
+        with torch.no_grad():
+            for p, o in zip(params, offs):
+                v = self.p_flat[o:o + p.numel()].view(p.shape)
+                v.copy_(p.data)
+                p.data = v
+                if self.m_flat is not None:
+                    mv = self.m_flat[o:o + p.numel()].view(p.shape)
+                    old = optimizer.state[p].get("momentum_buffer") if p in optimizer.state else None
+                    if old is not None:
+                        mv.copy_(old)
+                        self.first = 0
+                    optimizer.state[p]["momentum_buffer"] = mv
+
+    def refresh_hyper(self, group):
+        vals = (float(group["lr"]), float(group["momentum"]), float(group["dampening"]), float(group["weight_decay"]), int(bool(group["nesterov"])))
+        if vals != self.hyper_vals:
+            h = torch.zeros(8, dtype=torch.float32)
+            h[0], h[1], h[2], h[3] = vals[:4]
+            hi = h.view(torch.int32)
+            hi[4], hi[5] = vals[4], self.first
+            self.hyper.copy_(h)
+            self.hyper_vals, self.first = vals, 0
+
+    def launch(self, stream_handle):
+        L = _lib.cuda()
+        n4 = (self.total + 3) // 4
+        ins = (ctypes.c_void_p * 1)(self.g_in.data_ptr())
+        outs = (ctypes.c_void_p * 1)(self.g_avg.data_ptr())
+        NF._ok(L.pdl_allreduce_launch(0, 0, 1, 0, n4, ins, outs, None, None, None, None, _p(self.p_flat), _p(self.m_flat) if self.m_flat is not None else None,
+                                      _p(self.hyper), _p(self.state), L.pdl_allreduce_blocks(n4, 1, 0), 1.0, 30.0, ctypes.c_void_p(stream_handle)),
+               "fused SGD kernel")
+
+
+class ConvNetEngine:
+    NAMES = ["conv1.weight", "conv1.bias", "conv2.weight", "conv2.bias", "conv3.weight", "conv3.bias", "fc1.weight", "fc1.bias"]
+
+    @classmethod
+    def try_create(cls, model, criterion, optimizer):
+        from ..models.convnet import ConvNet
+        from ..optim.sgd import SGD
+        from ..parallel.ddp import DistributedDataParallel
+
+        ddp = model if isinstance(model, DistributedDataParallel) else None
+        module = model.module if ddp is not None else model
+        if not isinstance(module, ConvNet) or not isinstance(optimizer, SGD):
+            return None
+        if not isinstance(criterion, torch.nn.CrossEntropyLoss) or criterion.reduction != "mean" or criterion.weight is not None \
+                or criterion.label_smoothing != 0.0:
+            return None
+        params = dict(module.named_parameters())
+        if list(params.keys()) != cls.NAMES or any(p.dtype != torch.float32 or not p.is_cuda or not p.requires_grad for p in params.values()):
+            return None
+        if len(optimizer.param_groups) != 1 or optimizer.param_groups[0].get("maximize", False):
+            return None
+        owned = {id(p) for p in optimizer.param_groups[0]["params"]}
+        if any(id(p) not in owned for p in params.values()):
+            return None
+        if ddp is not None and (len(ddp._buckets) != 1 or not getattr(ddp._backend, "supports_fused_sgd", False)):
+            return None
+        return cls(module, ddp, optimizer)
+
+    def __init__(self, module, ddp, optimizer):
+        self.module, self.ddp, self.optimizer = module, ddp, optimizer
+        self.params = [dict(module.named_parameters())[n] for n in self.NAMES]
+        self.device = self.params[0].device
+        self.group = optimizer.param_groups[0]
+        self.L = _lib.cuda()
+        if ddp is not None:
+            if not ddp._fused_checked:
+                ddp._resolve_fused_optimizers()
+            bk = ddp._buckets[0]
+            if bk.fused_group is None:
+                raise RuntimeError("TrainStep: the optimizer could not be fused into the bucket allreduce")
+            self.backend, self.bucket = ddp._backend, bk
+            index_of = {id(p): i for i, p in enumerate(ddp._params)}
+            self.g_views = [ddp._in_views[index_of[id(p)]] for p in self.params]
+            self.avg_views = [ddp._avg_views[index_of[id(p)]] for p in self.params]
+            self.world = ddp._world
+        else:
+            self.arena = _SoloArena(self.params, self.group, optimizer, self.device)
+            a = self.arena
+            self.g_views = [a.g_in[o:o + p.numel()].view(p.shape) for p, o in zip(self.params, a.offsets)]
+            self.avg_views = [a.g_avg[o:o + p.numel()].view(p.shape) for p, o in zip(self.params, a.offsets)]
+            self.world = 1
+        for p, v in zip(self.params, self.avg_views):
+            p.grad = v
+        self.graphs = {}
+        self.kernel_count = 0
+
+    # ------------------------------------------------------------------ buffers + capture
+    def _build(self, N):
+        dev, f32 = self.device, torch.float32
+        e = lambda *s, dt=f32: torch.empty(s, dtype=dt, device=dev)  # noqa: E731
+        b = {
+            "x": e(N, 28, 28, 1), "y": e(N, dt=torch.int64),
+            "z1": e(N, 26, 26, 32), "a1": e(N, 13, 13, 32), "i1": e(N, 13, 13, 32, dt=torch.uint8),
+            "z2": e(N, 11, 11, 64), "a2": e(N, 10, 10, 64), "i2": e(N, 10, 10, 64, dt=torch.uint8),
+            "z3": e(N, 8, 8, 128), "a3": e(N, 4, 4, 128), "i3": e(N, 4, 4, 128, dt=torch.uint8),
+            "flat": e(N, 2048), "logits": e(N, 10), "row_loss": e(N), "loss": torch.zeros((), dtype=f32, device=dev), "dlogits": e(N, 10),
+            "dflat": e(N, 2048), "da3": e(N, 4, 4, 128), "dz3": e(N, 8, 8, 128), "da2": e(N, 10, 10, 64), "dz2": e(N, 11, 11, 64),
+            "da1": e(N, 13, 13, 32), "dz1": e(N, 26, 26, 32),
+        }
+        shapes = [(N, 28, 28, 1, 32, 5, 5, 1, 1), (N, 13, 13, 32, 64, 3, 3, 1, 0), (N, 10, 10, 64, 128, 3, 3, 1, 0)]
+        nbytes = max(self.L.pdl_conv2d_wgrad_scratch_bytes(*s) for s in shapes)
+        b["scratch"] = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+        b["x"].zero_()
+        b["y"].zero_()
+        entry = {"buf": b, "graph": None, "kernels": 0}
+        # warm-up run outside capture (also validates every launch), then capture
+        side = torch.cuda.Stream(device=dev)
+        side.wait_stream(torch.cuda.current_stream(dev))
+        with torch.cuda.stream(side):
+            self._record(b, N, side.cuda_stream, reduce=False)
+        torch.cuda.current_stream(dev).wait_stream(side)
+        torch.cuda.synchronize(dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            entry["kernels"] = self._record(b, N, torch.cuda.current_stream(dev).cuda_stream, reduce=True)
+        entry["graph"] = g
+        return entry
+
+    def _record(self, b, N, stream_handle, reduce):
+        """Issue the kernels of one iteration on `stream_handle`; returns how many were launched."""
+        L, ok, st = self.L, NF._ok, ctypes.c_void_p(stream_handle)
+        w1, b1, w2, b2, w3, b3, wf, bf = self.params
+        gw1, gb1, gw2, gb2, gw3, gb3, gwf, gbf = self.g_views
+        k = 0
+        # forward
+        ok(L.pdl_conv2d_fwd_simt(_p(b["x"]), _p(w1), _p(b1), _p(b["z1"]), N, 28, 28, 1, 32, 5, 5, 1, 1, 1, st), "conv1"); k += 1
+        ok(L.pdl_maxpool_fwd(_p(b["z1"]), _p(b["a1"]), _p(b["i1"]), N, 26, 26, 32, 2, 2, 0, st), "pool1"); k += 1
+        ok(L.pdl_conv2d_fwd_simt(_p(b["a1"]), _p(w2), _p(b2), _p(b["z2"]), N, 13, 13, 32, 64, 3, 3, 1, 0, 1, st), "conv2"); k += 1
+        ok(L.pdl_maxpool_fwd(_p(b["z2"]), _p(b["a2"]), _p(b["i2"]), N, 11, 11, 64, 2, 1, 0, st), "pool2"); k += 1
+        ok(L.pdl_conv2d_fwd_simt(_p(b["a2"]), _p(w3), _p(b3), _p(b["z3"]), N, 10, 10, 64, 128, 3, 3, 1, 0, 1, st), "conv3"); k += 1
+        ok(L.pdl_maxpool_fwd(_p(b["z3"]), _p(b["a3"]), _p(b["i3"]), N, 8, 8, 128, 2, 2, 0, st), "pool3"); k += 1
+        ok(L.pdl_permute_nhwc_nchw(_p(b["a3"]), _p(b["flat"]), N, 16, 128, 1, st), "flatten"); k += 1
+        ok(L.pdl_linear_fwd(_p(b["flat"]), _p(wf), _p(bf), _p(b["logits"]), N, 10, 2048, st), "fc1"); k += 1
+        ok(L.pdl_cross_entropy(_p(b["logits"]), _p(b["y"]), N, 10, _p(b["row_loss"]), _p(b["loss"]), _p(b["dlogits"]), None, st), "loss"); k += 1
+        # backward
+        ok(L.pdl_linear_wgrad(_p(b["flat"]), _p(b["dlogits"]), _p(gwf), _p(gbf), N, 10, 2048, st), "fc1 wgrad"); k += 1
+        ok(L.pdl_linear_dgrad(_p(b["dlogits"]), _p(wf), _p(b["dflat"]), N, 10, 2048, st), "fc1 dgrad"); k += 1
+        ok(L.pdl_permute_nhwc_nchw(_p(b["dflat"]), _p(b["da3"]), N, 16, 128, 0, st), "unflatten"); k += 1
+        ok(L.pdl_maxpool_bwd(_p(b["da3"]), _p(b["i3"]), _p(b["a3"]), _p(b["dz3"]), N, 8, 8, 128, 2, 2, 0, 1, st), "pool3 bwd"); k += 1
+        ok(L.pdl_conv2d_wgrad_simt(_p(b["a2"]), _p(b["dz3"]), _p(gw3), _p(gb3), _p(b["scratch"]), N, 10, 10, 64, 128, 3, 3, 1, 0, st), "conv3 wgrad"); k += 2
+        ok(L.pdl_conv2d_dgrad_simt(_p(b["dz3"]), _p(w3), _p(b["da2"]), N, 10, 10, 64, 128, 3, 3, 1, 0, st), "conv3 dgrad"); k += 1
+        ok(L.pdl_maxpool_bwd(_p(b["da2"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), N, 11, 11, 64, 2, 1, 0, 1, st), "pool2 bwd"); k += 1
+        ok(L.pdl_conv2d_wgrad_simt(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["scratch"]), N, 13, 13, 32, 64, 3, 3, 1, 0, st), "conv2 wgrad"); k += 2
+        ok(L.pdl_conv2d_dgrad_simt(_p(b["dz2"]), _p(w2), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 1, 0, st), "conv2 dgrad"); k += 1
+        ok(L.pdl_maxpool_bwd(_p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(b["dz1"]), N, 26, 26, 32, 2, 2, 0, 1, st), "pool1 bwd"); k += 1
+        ok(L.pdl_conv2d_wgrad_simt(_p(b["x"]), _p(b["dz1"]), _p(gw1), _p(gb1), _p(b["scratch"]), N, 28, 28, 1, 32, 5, 5, 1, 1, st), "conv1 wgrad"); k += 2
+        # gradient averaging + SGD (one kernel; over NVLink when world > 1)
+        if reduce:
+            if self.ddp is not None:
+                self.backend.launch_bucket_kernel(self.bucket, self.world, self.ddp.algorithm, stream_handle, fused=True)
+            else:
+                self.arena.launch(stream_handle)
+            k += 1
+        return k
+
+    # ------------------------------------------------------------------ stepping
+    def _refresh_hyper(self):
+        if self.ddp is not None:
+            self.backend._hyper_for(self.bucket)
+        else:
+            self.arena.refresh_hyper(self.group)
+
+    def step(self, images, labels):
+        N = images.shape[0]
+        entry = self.graphs.get(N)
+        if entry is None:
+            if tuple(images.shape[1:]) != (1, 28, 28):
+                raise ValueError("ConvNet expects N x 1 x 28 x 28 inputs, got %s" % (tuple(images.shape),))
+            self._refresh_hyper()
+            entry = self.graphs[N] = self._build(N)
+        b = entry["buf"]
+        self._refresh_hyper()
+        b["x"].view(N, 1, 28, 28).copy_(images, non_blocking=True)
+        b["y"].copy_(labels, non_blocking=True)
+        entry["graph"].replay()
+        self.kernel_count = entry["kernels"]
+        if self.ddp is not None:
+            self.ddp._iteration += 1
+        return b["loss"]
+
+    def kernels_per_step(self):
+        return self.kernel_count
+
+    def logits(self, N):
+        """Logits of the most recent step with batch size N (static buffer)."""
+        return self.graphs[N]["buf"]["logits"]

@@ -1,0 +1,232 @@
+"""Autograd functions over the sm_100a kernels (NHWC / channels-last fp32).
+
+Tensors keep their logical NCHW shape (what the reference's models see, launch_dist.py:35-41)
+but are stored channels-last, i.e. physically NHWC, which is what the implicit-GEMM kernels
+want.  Every function calls into libpdl_cuda.so on the CURRENT torch stream; there is no
+PyTorch fallback here -- a missing library raises at import of the library handle.
+"""
+from __future__ import annotations
+
+import ctypes
+
+import torch
+
+from .. import _lib
+
+_CL = torch.channels_last
+
+
+def _stream(t):
+    return ctypes.c_void_p(torch.cuda.current_stream(t.device).cuda_stream)
+
+
+def _p(t):
+    return ctypes.c_void_p(t.data_ptr()) if t is not None else None
+
+
+def _ok(rc, what):
+    if rc != 0:
+        raise RuntimeError("%s failed (%d): %s" % (what, rc, _lib.cuda().pdl_last_error().decode()))
+
+
+def _nhwc(x):
+    return x.contiguous(memory_format=_CL) if x.dim() == 4 else x.contiguous()
+
+
+_scratch = {}
+
+
+def scratch(nbytes, device, tag="default"):
+    """Grow-only per-device scratch buffers (wgrad split-K partials etc.)."""
+    key = (device.index, tag)
+    buf = _scratch.get(key)
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(int(nbytes), 1 << 20), dtype=torch.uint8, device=device)
+        _scratch[key] = buf
+    return buf
+
+
+def conv_out(h, k, s, p):
+    return (h + 2 * p - k) // s + 1
+
+
+class _Conv2d(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b, stride, pad):
+        L = _lib.cuda()
+        x = _nhwc(x)
+        w = w.contiguous()
+        N, Cin, H, W = x.shape
+        Cout, _, KH, KW = w.shape
+        P, Q = conv_out(H, KH, stride, pad), conv_out(W, KW, stride, pad)
+        y = torch.empty((N, Cout, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        from . import tc_conv
+
+        if not tc_conv.conv2d_fwd(x, w, b, y, stride, pad, relu=False):
+            _ok(L.pdl_conv2d_fwd_simt(_p(x), _p(w), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, 0, _stream(x)), "conv2d forward")
+        ctx.save_for_backward(x, w)
+        ctx.geom = (stride, pad, b is not None)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        L = _lib.cuda()
+        x, w = ctx.saved_tensors
+        stride, pad, has_bias = ctx.geom
+        dy = _nhwc(dy)
+        N, Cin, H, W = x.shape
+        Cout, _, KH, KW = w.shape
+        dx = dw = db = None
+        from . import tc_conv
+
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x, memory_format=_CL)
+            if not tc_conv.conv2d_dgrad(dy, w, dx, stride, pad):
+                _ok(L.pdl_conv2d_dgrad_simt(_p(dy), _p(w), _p(dx), N, H, W, Cin, Cout, KH, KW, stride, pad, _stream(x)), "conv2d dgrad")
+        if ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2]):
+            dw = torch.empty_like(w)
+            db = torch.empty(Cout, dtype=w.dtype, device=w.device) if has_bias else None
+            if not tc_conv.conv2d_wgrad(x, dy, dw, db, stride, pad):
+                nbytes = L.pdl_conv2d_wgrad_scratch_bytes(N, H, W, Cin, Cout, KH, KW, stride, pad)
+                sc = scratch(nbytes, x.device, "wgrad")
+                _ok(L.pdl_conv2d_wgrad_simt(_p(x), _p(dy), _p(dw), _p(db), _p(sc), N, H, W, Cin, Cout, KH, KW, stride, pad, _stream(x)), "conv2d wgrad")
+        return dx, dw, db, None, None
+
+
+def conv2d(x, w, b=None, stride=1, padding=0):
+    return _Conv2d.apply(x, w, b, int(stride), int(padding))
+
+
+class _Relu(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = _nhwc(x)
+        y = torch.empty_like(x)
+        _ok(_lib.cuda().pdl_relu_fwd(_p(x), _p(y), x.numel(), _stream(x)), "relu forward")
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if dy.stride() != y.stride():
+            dy = torch.empty_like(y).copy_(dy)  # same physical layout as the saved output
+        dx = torch.empty_like(y)
+        _ok(_lib.cuda().pdl_relu_bwd(_p(y), _p(dy), _p(dx), y.numel(), _stream(y)), "relu backward")
+        return dx
+
+
+def relu(x):
+    return _Relu.apply(x)
+
+
+class _MaxPool2d(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k, stride, pad):
+        x = _nhwc(x)
+        N, C, H, W = x.shape
+        P, Q = conv_out(H, k, stride, pad), conv_out(W, k, stride, pad)
+        y = torch.empty((N, C, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        idx = torch.empty((N, P, Q, C), dtype=torch.uint8, device=x.device)
+        _ok(_lib.cuda().pdl_maxpool_fwd(_p(x), _p(y), _p(idx), N, H, W, C, k, stride, pad, _stream(x)), "maxpool forward")
+        ctx.save_for_backward(idx)
+        ctx.geom = (N, C, H, W, k, stride, pad)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (idx,) = ctx.saved_tensors
+        N, C, H, W, k, stride, pad = ctx.geom
+        dy = _nhwc(dy)
+        dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device, memory_format=_CL)
+        _ok(_lib.cuda().pdl_maxpool_bwd(_p(dy), _p(idx), None, _p(dx), N, H, W, C, k, stride, pad, 0, _stream(dy)), "maxpool backward")
+        return dx, None, None, None
+
+
+def max_pool2d(x, kernel_size, stride=None, padding=0):
+    return _MaxPool2d.apply(x, int(kernel_size), int(stride if stride is not None else kernel_size), int(padding))
+
+
+class _Linear(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, w, b):
+        x, w = x.contiguous(), w.contiguous()
+        M, K = x.shape
+        N = w.shape[0]
+        y = torch.empty((M, N), dtype=x.dtype, device=x.device)
+        _ok(_lib.cuda().pdl_linear_fwd(_p(x), _p(w), _p(b), _p(y), M, N, K, _stream(x)), "linear forward")
+        ctx.save_for_backward(x, w)
+        ctx.has_bias = b is not None
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        x, w = ctx.saved_tensors
+        dy = dy.contiguous()
+        M, K = x.shape
+        N = w.shape[0]
+        L = _lib.cuda()
+        dx = dw = db = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty_like(x)
+            _ok(L.pdl_linear_dgrad(_p(dy), _p(w), _p(dx), M, N, K, _stream(x)), "linear dgrad")
+        if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
+            dw = torch.empty_like(w)
+            db = torch.empty(N, dtype=w.dtype, device=w.device) if ctx.has_bias else None
+            _ok(L.pdl_linear_wgrad(_p(x), _p(dy), _p(dw), _p(db), M, N, K, _stream(x)), "linear wgrad")
+        return dx, dw, db
+
+
+def linear(x, w, b=None):
+    return _Linear.apply(x, w, b)
+
+
+class _CrossEntropy(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target):
+        logits, target = logits.contiguous(), target.contiguous()
+        N, C = logits.shape
+        loss = torch.empty((), dtype=logits.dtype, device=logits.device)
+        row = torch.empty(N, dtype=logits.dtype, device=logits.device)
+        dlogits = torch.empty_like(logits)
+        _ok(_lib.cuda().pdl_cross_entropy(_p(logits), _p(target), N, C, _p(row), _p(loss), _p(dlogits), None, _stream(logits)), "cross entropy")
+        ctx.save_for_backward(dlogits)
+        return loss
+
+    @staticmethod
+    def backward(ctx, dloss):
+        (dlogits,) = ctx.saved_tensors
+        return dlogits * dloss, None
+
+
+def cross_entropy(logits, target):
+    return _CrossEntropy.apply(logits, target)
+
+
+def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps):
+    from . import bn
+
+    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps)
+
+
+class _GlobalAvgPool(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x):
+        x = _nhwc(x)
+        N, C, H, W = x.shape
+        y = torch.empty((N, C, 1, 1), dtype=x.dtype, device=x.device)
+        _ok(_lib.cuda().pdl_global_avgpool_fwd(_p(x), _p(y), N, H * W, C, _stream(x)), "global avgpool forward")
+        ctx.geom = (N, C, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, C, H, W = ctx.geom
+        dy = dy.contiguous()
+        dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device, memory_format=_CL)
+        _ok(_lib.cuda().pdl_global_avgpool_bwd(_p(dy), _p(dx), N, H * W, C, _stream(dy)), "global avgpool backward")
+        return dx
+
+
+def global_avg_pool(x):
+    return _GlobalAvgPool.apply(x)

@@ -62,11 +62,11 @@ class SGD(torch.optim.SGD):
         group = self.group_by_id(group_id)
         if group.get("maximize", False):
             return False
-        backend = ddp._backend
-        if not backend.attach_fused_params(self, group, params, offsets):
+        info = ddp._backend.attach_fused_params(self, group, params, offsets)
+        if not info:
             return False
         self._attached.append((weakref.ref(ddp), bucket, group_id))
-        return True
+        return info
 
     def mark_fused_done(self, params):
         self._fused_done.update(id(p) for p in params)

@@ -1,0 +1,468 @@
+"""The NVLink data plane: symmetric-memory segments + hand-written peer-to-peer collectives.
+
+``B200ProcessGroup`` is what ``init_process_group(backend="nccl")`` creates in this package
+(reference call sites launch_dist.py:49, mpspawn_dist.py:49-54, example_mp.py:37-42).  It makes
+no NCCL call: buckets live in symmetric memory (csrc/cuda/symm.cu) and every collective is one
+of the kernels in csrc/cuda/allreduce.cu.  A small TCP mesh (the CPU backend) rides along as the
+control plane for object exchange and host-side barriers.
+
+CUDA state is created lazily, on the first GPU collective or DDP wrap: the reference's spawn
+scripts call ``torch.cuda.set_device`` only AFTER ``init_process_group`` (mpspawn_dist.py:49-60).
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+import uuid
+
+import torch
+
+from .. import _lib
+from . import distributed as dist
+from ..utils.logging import debug
+
+ALGOS = {"oneshot": 0, "twoshot": 1, "ring": 2, "nvls": 3}
+ALGO_NAMES = {v: k for k, v in ALGOS.items()}
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError("%s failed (%d): %s" % (what, rc, _lib.cuda().pdl_last_error().decode()))
+
+
+class _RawCuda:
+    """Exposes a raw device range to torch (zero-copy) through __cuda_array_interface__."""
+
+    def __init__(self, ptr, nbytes, owner):
+        self.__cuda_array_interface__ = {"shape": (int(nbytes),), "typestr": "|u1", "data": (int(ptr), False), "version": 3, "strides": None}
+        self._owner = owner
+
+
+class SymmetricSegment:
+    """``nbytes`` of device memory at the same offset on every rank of ``pg``, peer-mapped everywhere.
+
+    Collective constructor.  Layout is the caller's business; ``tensor()`` returns torch views of
+    the local copy, ``ptr(rank)`` the address through which THIS process reaches rank's copy."""
+
+    def __init__(self, pg, nbytes, device_index, want_multicast=True):
+        L = _lib.cuda()
+        self.pg, self.device_index = pg, device_index
+        self.world, self.rank = pg.size(), pg.rank()
+        token = pg._ctl.broadcast_object(uuid.uuid4().hex if self.rank == 0 else None, 0)
+        want_mc = bool(want_multicast and self.world > 1 and os.environ.get("PDL_DISABLE_NVLS", "0") != "1"
+                       and L.pdl_symm_multicast_supported(device_index))
+        want_mc = all(pg._ctl.allgather_object(want_mc))
+        h = ctypes.c_void_p()
+        _check(L.pdl_symm_begin(self.rank, self.world, device_index, int(nbytes), ("pdl-symm-" + token).encode(), int(want_mc), ctypes.byref(h)),
+               "symmetric segment allocation")
+        self._h = h
+        pg._ctl.barrier()  # every rank is listening
+        _check(L.pdl_symm_exchange(h), "symmetric handle exchange")
+        mc_ok = all(pg._ctl.allgather_object(bool(L.pdl_symm_multicast_ready(h))))
+        L.pdl_symm_bind_multicast(h, int(mc_ok))
+        mc_ok = all(pg._ctl.allgather_object(bool(L.pdl_symm_mc_ptr(h))))
+        if not mc_ok:
+            L.pdl_symm_bind_multicast(h, 0)
+        self.bytes = int(L.pdl_symm_bytes(h))
+        self.ptrs = [int(L.pdl_symm_ptr(h, r) or 0) for r in range(self.world)]
+        self.mc_ptr = int(L.pdl_symm_mc_ptr(h) or 0) if mc_ok else 0
+        self._base = torch.as_tensor(_RawCuda(self.ptrs[self.rank], self.bytes, self), device="cuda:%d" % device_index)
+        pg._ctl.barrier()  # everyone mapped (memory is zero-filled by begin)
+        debug("symmetric segment: %d bytes, multicast=%s" % (self.bytes, bool(self.mc_ptr)))
+
+    def tensor(self, offset_bytes, numel, dtype=torch.float32):
+        nbytes = numel * torch.empty((), dtype=dtype).element_size()
+        return self._base[offset_bytes:offset_bytes + nbytes].view(dtype)
+
+    def ptr(self, rank, offset_bytes=0):
+        return self.ptrs[rank] + offset_bytes
+
+    def destroy(self):
+        if self._h:
+            self._base = None
+            _lib.cuda().pdl_symm_destroy(self._h)
+            self._h = None
+
+
+def _ptr_array(values):
+    return (ctypes.c_void_p * len(values))(*values)
+
+
+def choose_algorithm(nbytes, world, has_multicast, override=None):
+    """Per-bucket variant.  Defaults follow the measured crossover (see profiles/allreduce_sweep.md):
+    latency-bound buckets take the 1-hop one-shot kernel, bandwidth-bound ones the in-switch (NVLS)
+    or two-shot reduction."""
+    if override:
+        name = override.lower()
+        if name not in ALGOS:
+            raise ValueError("unknown allreduce algorithm %r (choose from %s)" % (override, sorted(ALGOS)))
+        if name == "nvls" and not has_multicast:
+            raise RuntimeError("allreduce algorithm 'nvls' was requested but this box exposes no NVSwitch multicast")
+        return ALGOS[name]
+    if world == 1:
+        return ALGOS["oneshot"]
+    threshold = int(os.environ.get("PDL_ONESHOT_MAX_BYTES", 1 << 20))
+    if nbytes <= threshold:
+        return ALGOS["oneshot"]
+    return ALGOS["nvls"] if has_multicast else ALGOS["twoshot"]
+
+
+class B200ProcessGroup(dist.ProcessGroup):
+    backend = "b200"
+    STAGING_BYTES = 64 << 20
+
+    def __init__(self, store, group_rank, ranks, name, master_host, timeout_s, device_index=None):
+        super().__init__(store, group_rank, ranks, name)
+        if not torch.cuda.is_available():
+            raise RuntimeError("backend 'nccl'/'b200' needs a CUDA device; use backend='gloo' for CPU-only runs")
+        _lib.cuda()  # fail loudly now if the kernel library was not built
+        self._ctl = dist.CpuProcessGroup(store, group_rank, ranks, name + "/ctl", master_host, timeout_s)
+        self.timeout_s = float(timeout_s)
+        self.device_index = device_index
+        self._staging = None
+        self._segments = []
+        self._comm_stream = None
+        if device_index is not None:
+            self._ensure_cuda(device_index)
+
+    # -- lazy CUDA bring-up -------------------------------------------------------------
+    def _ensure_cuda(self, device_index=None):
+        if self.device_index is None:
+            self.device_index = torch.cuda.current_device() if device_index is None else device_index
+        elif device_index is not None and device_index != self.device_index:
+            raise RuntimeError("process group is bound to cuda:%d but was used with cuda:%d" % (self.device_index, device_index))
+        if self._comm_stream is None:
+            with torch.cuda.device(self.device_index):
+                self._comm_stream = torch.cuda.Stream(priority=-1)
+        return self.device_index
+
+    @property
+    def comm_stream(self):
+        self._ensure_cuda()
+        return self._comm_stream
+
+    def new_segment(self, nbytes, want_multicast=True):
+        seg = SymmetricSegment(self, nbytes, self._ensure_cuda(), want_multicast)
+        self._segments.append(seg)
+        return seg
+
+    def new_comm_state(self):
+        return torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device="cuda:%d" % self._ensure_cuda())
+
+    def _stage(self):
+        if self._staging is None:
+            L = _lib.cuda()
+            pad = (L.pdl_signal_pad_bytes() + 4095) // 4096 * 4096
+            half = self.STAGING_BYTES
+            seg = self.new_segment(pad + 2 * half, want_multicast=False)
+            self._staging = {"seg": seg, "pad": pad, "half": half, "state": self.new_comm_state(),
+                             "pads": _ptr_array([seg.ptr(r) for r in range(self.size())])}
+        return self._staging
+
+    def make_reducer_backend(self, device):
+        if device.type != "cuda":
+            raise RuntimeError("the 'nccl'/'b200' backend reduces CUDA gradients only; this module lives on %s" % device)
+        self._ensure_cuda(device.index)
+        return B200ReducerBackend(self)
+
+    # -- collectives ----------------------------------------------------------------------
+    def _stream(self):
+        return ctypes.c_void_p(torch.cuda.current_stream(self.device_index).cuda_stream)
+
+    def _pull(self, root, nbytes, dst_ptr, blocks=8):
+        st = self._stage()
+        seg = st["seg"]
+        n16 = (nbytes + 15) // 16
+        src = _ptr_array([seg.ptr(r, st["pad"]) for r in range(self.size())])
+        _check(_lib.cuda().pdl_pull_launch(self.rank(), self.size(), 0, root, n16, src, ctypes.c_void_p(dst_ptr), st["pads"],
+                                           ctypes.c_void_p(st["state"].data_ptr()), blocks, self.timeout_s, self._stream()), "peer copy kernel")
+
+    def broadcast(self, tensor, src):
+        if not tensor.is_cuda:
+            return self._ctl.broadcast(tensor, src)
+        self._ensure_cuda(tensor.device.index)
+        if self.size() == 1:
+            return tensor
+        st = self._stage()
+        seg, half = st["seg"], st["half"]
+        work = tensor.contiguous()
+        flat = work.view(-1).view(torch.uint8)
+        send = seg.tensor(st["pad"], half, torch.uint8)
+        recv = seg.tensor(st["pad"] + half, half, torch.uint8)
+        for off in range(0, flat.numel(), half):
+            n = min(half, flat.numel() - off)
+            if self.rank() == src:
+                send[:n].copy_(flat[off:off + n])
+            self._pull(src, n, recv.data_ptr(), blocks=min(32, max(1, n >> 16)))
+            if self.rank() != src:
+                flat[off:off + n].copy_(recv[:n])
+        if work is not tensor:
+            tensor.copy_(work)
+        return tensor
+
+    def allgather(self, tensor):
+        if not tensor.is_cuda:
+            return self._ctl.allgather(tensor)
+        self._ensure_cuda(tensor.device.index)
+        W = self.size()
+        work = tensor.contiguous()
+        if W == 1:
+            return [work.clone()]
+        st = self._stage()
+        seg, half = st["seg"], st["half"]
+        nbytes = work.numel() * work.element_size()
+        slot = (nbytes + 15) // 16 * 16
+        if slot * W > half:
+            raise RuntimeError("allgather of %d bytes per rank exceeds the %d-byte staging window" % (nbytes, half // W))
+        send = seg.tensor(st["pad"], half, torch.uint8)
+        recv = seg.tensor(st["pad"] + half, half, torch.uint8)
+        send[:nbytes].copy_(work.view(-1).view(torch.uint8))
+        self._pull(-1, slot, recv.data_ptr())
+        return [recv[r * slot:r * slot + nbytes].clone().view(work.dtype).view(work.shape) for r in range(W)]
+
+    def allreduce(self, tensor, op=dist.ReduceOp.SUM, algorithm=None):
+        if not tensor.is_cuda:
+            return self._ctl.allreduce(tensor, op)
+        self._ensure_cuda(tensor.device.index)
+        W = self.size()
+        if W == 1:
+            return tensor
+        if tensor.dtype != torch.float32 or op not in (dist.ReduceOp.SUM, dist.ReduceOp.AVG):
+            host = tensor.detach().cpu()  # rare control-plane reductions (ints, MIN/MAX): host path
+            self._ctl.allreduce(host, op)
+            tensor.copy_(host)
+            return tensor
+        st = self._stage()
+        seg, half, L = st["seg"], st["half"], _lib.cuda()
+        work = tensor.contiguous()
+        flat = work.view(-1)
+        send = seg.tensor(st["pad"], half // 4)
+        recv = seg.tensor(st["pad"] + half, half // 4)
+        cap = half // 4 // 2  # floats per pass (second half of the send window is the ring staging area)
+        scale = 1.0 if op == dist.ReduceOp.SUM else 1.0 / W
+        for off in range(0, flat.numel(), cap):
+            n = min(cap, flat.numel() - off)
+            n4 = (n + 3) // 4
+            send[:n].copy_(flat[off:off + n])
+            if n4 * 4 > n:
+                send[n:n4 * 4].zero_()
+            algo = choose_algorithm(n * 4, W, False, algorithm)
+            blocks = L.pdl_allreduce_blocks(n4, W, algo)
+            ins = _ptr_array([seg.ptr(r, st["pad"]) for r in range(W)])
+            outs = _ptr_array([seg.ptr(r, st["pad"] + half) for r in range(W)])
+            rings = _ptr_array([seg.ptr(r, st["pad"] + cap * 4) for r in range(W)])
+            _check(L.pdl_allreduce_launch(algo, self.rank(), W, 0, n4, ins, outs, rings, st["pads"], None, None, None, None, None,
+                                          ctypes.c_void_p(st["state"].data_ptr()), blocks, scale, self.timeout_s, self._stream()), "allreduce kernel")
+            flat[off:off + n].copy_(recv[:n])
+        if work is not tensor:
+            tensor.copy_(work)
+        return tensor
+
+    def barrier(self):
+        if self.device_index is not None and self._staging is not None:
+            torch.cuda.synchronize(self.device_index)
+        self._ctl.barrier()
+
+    def device_barrier(self):
+        """Barrier executed by a kernel on the current stream (no host round trip)."""
+        self._ensure_cuda()
+        if self.size() > 1:
+            st = self._stage()
+            self._pull(0, 0, st["seg"].ptr(self.rank(), st["pad"] + st["half"]), blocks=1)
+
+    def send(self, tensor, dst):
+        host = tensor.detach().cpu() if tensor.is_cuda else tensor
+        self._ctl.send(host, dst)
+
+    def recv(self, tensor, src):
+        if tensor.is_cuda:
+            host = torch.empty(tensor.shape, dtype=tensor.dtype)
+            self._ctl.recv(host, src)
+            tensor.copy_(host)
+            return tensor
+        return self._ctl.recv(tensor, src)
+
+    def check_device_errors(self):
+        """Raise if a kernel gave up waiting for a peer (dead or hung rank)."""
+        bad = False
+        if self._staging is not None:
+            state = self._staging["state"]
+            bad = int(state.view(torch.int32)[-1].item()) != 0
+        return bad
+
+    # control plane
+    def _cpu_allgather(self, t):
+        return self._ctl.allgather(t)
+
+    def _cpu_broadcast(self, t, src):
+        return self._ctl.broadcast(t, src)
+
+    def destroy(self):
+        if self.device_index is not None:
+            torch.cuda.synchronize(self.device_index)
+        try:
+            self._ctl.barrier()
+        except Exception:
+            pass
+        for seg in self._segments:
+            seg.destroy()
+        self._segments = []
+        self._staging = None
+        self._ctl.destroy()
+
+
+class B200ReducerBackend:
+    """DDP's data plane on GPUs: buckets in symmetric memory, one fused kernel per bucket."""
+
+    supports_fused_sgd = True
+
+    def __init__(self, pg):
+        self.pg = pg
+        self.L = _lib.cuda()
+        self.seg = None
+        self.g_in = self.g_avg = None
+        self.p_flat = self.m_flat = None
+        self.total = 0
+        self.collect_stats = os.environ.get("PDL_STATS", "0") == "1"
+        self._exposed_ms = []
+        self._launch_cache = {}
+        self._hyper = {}
+        self._last_done = None
+        self._bw_end = None
+        self._algo_used = {}
+
+    def allocate(self, total, dtype, device, bucket_ranges):
+        if dtype != torch.float32:
+            raise NotImplementedError("the NVLink reducer averages fp32 gradients (the reference trains in fp32); got %s" % dtype)
+        self._launch_cache.clear()
+        if self.seg is not None and total <= self.total:
+            return
+        pg, L = self.pg, self.L
+        self.total = total
+        self.pad_bytes = (L.pdl_signal_pad_bytes() + 4095) // 4096 * 4096
+        self.area = (total * 4 + 4095) // 4096 * 4096
+        self.seg = pg.new_segment(self.pad_bytes + 3 * self.area)
+        self.state = pg.new_comm_state()
+        self.g_in = self.seg.tensor(self.pad_bytes, total)
+        self.g_avg = self.seg.tensor(self.pad_bytes + self.area, total)
+        self.device = device
+        W = pg.size()
+        self._pads = _ptr_array([self.seg.ptr(r) for r in range(W)])
+
+    # -- fused optimizer plumbing -----------------------------------------------------------
+    def attach_fused_params(self, opt, group, params, offsets):
+        if any(p.dtype != torch.float32 or not p.is_cuda for p in params):
+            return False
+        if self.p_flat is None:
+            self.p_flat = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+        mu = group["momentum"]
+        if mu != 0 and self.m_flat is None:
+            self.m_flat = torch.zeros(self.total, dtype=torch.float32, device=self.device)
+        had_state = False
+        with torch.no_grad():
+            for p, off in zip(params, offsets):
+                view = self.p_flat[off:off + p.numel()].view(p.shape)
+                view.copy_(p.data)
+                p.data = view
+                if mu != 0:
+                    mview = self.m_flat[off:off + p.numel()].view(p.shape)
+                    old = opt.state[p].get("momentum_buffer") if p in opt.state else None
+                    if old is not None:
+                        mview.copy_(old)
+                        had_state = True
+                    opt.state[p]["momentum_buffer"] = mview
+        return {"first": 0 if had_state else 1}
+
+    def _hyper_for(self, bk):
+        """Device-resident SgdHyper of a bucket, re-uploaded only when the optimizer's numbers change."""
+        opt, gid = bk.fused_group
+        group = opt.group_by_id(gid)
+        key = bk.index
+        entry = self._hyper.get(key)
+        vals = (float(group["lr"]), float(group["momentum"]), float(group["dampening"]), float(group["weight_decay"]), int(bool(group["nesterov"])))
+        if entry is None:
+            dev = torch.zeros(8, dtype=torch.float32, device=self.device)
+            entry = self._hyper[key] = {"dev": dev, "hosts": [], "vals": None, "first": getattr(bk, "first_flag", 1)}
+        if entry["vals"] != vals:
+            h = torch.zeros(8, dtype=torch.float32)
+            h[0], h[1], h[2], h[3] = vals[0], vals[1], vals[2], vals[3]
+            hi = h.view(torch.int32)
+            hi[4] = vals[4]
+            hi[5] = entry["first"]
+            h = h.pin_memory()
+            entry["hosts"] = entry["hosts"][-7:] + [h]  # keep in-flight pinned sources alive
+            entry["dev"].copy_(h, non_blocking=True)
+            entry["vals"] = vals
+        entry["first"] = 0
+        return entry["dev"]
+
+    def bucket_launch_args(self, bk, world, algorithm):
+        """(algo, blocks, ctypes pointer arrays) for a bucket; cached, also used by graph capture."""
+        key = (bk.index, algorithm)
+        c = self._launch_cache.get(key)
+        if c is None:
+            seg, W = self.seg, world
+            off = bk.offset * 4
+            n4 = (bk.numel + 3) // 4
+            algo = choose_algorithm(bk.numel * 4, W, bool(seg.mc_ptr), algorithm)
+            c = {
+                "algo": algo, "n4": n4, "blocks": self.L.pdl_allreduce_blocks(n4, W, algo),
+                "in": _ptr_array([seg.ptr(r, self.pad_bytes + off) for r in range(W)]),
+                "out": _ptr_array([seg.ptr(r, self.pad_bytes + self.area + off) for r in range(W)]),
+                "ring": _ptr_array([seg.ptr(r, self.pad_bytes + 2 * self.area + off) for r in range(W)]),
+                "mc_in": ctypes.c_void_p(seg.mc_ptr + self.pad_bytes + off) if seg.mc_ptr else None,
+                "mc_out": ctypes.c_void_p(seg.mc_ptr + self.pad_bytes + self.area + off) if seg.mc_ptr else None,
+                "channel": bk.index % self.L.pdl_comm_max_channels(),
+            }
+            self._launch_cache[key] = c
+            self._algo_used[bk.index] = ALGO_NAMES[algo]
+        return c
+
+    def launch_bucket_kernel(self, bk, world, algorithm, stream_handle, fused):
+        c = self.bucket_launch_args(bk, world, algorithm)
+        param = mom = hyper = None
+        if fused:
+            off = bk.offset * 4
+            param = ctypes.c_void_p(self.p_flat.data_ptr() + off)
+            group = bk.fused_group[0].group_by_id(bk.fused_group[1])
+            if group["momentum"] != 0:
+                mom = ctypes.c_void_p(self.m_flat.data_ptr() + off)
+            hyper = ctypes.c_void_p(self._hyper_for(bk).data_ptr())
+        _check(self.L.pdl_allreduce_launch(c["algo"], self.pg.rank(), world, c["channel"], c["n4"], c["in"], c["out"], c["ring"], self._pads,
+                                           c["mc_in"], c["mc_out"], param, mom, hyper, ctypes.c_void_p(self.state.data_ptr()), c["blocks"],
+                                           1.0 / world, self.pg.timeout_s, ctypes.c_void_p(stream_handle)), "bucket allreduce kernel")
+
+    def reduce_bucket(self, bk, world, algorithm):
+        comm = self.pg.comm_stream
+        cur = torch.cuda.current_stream(self.device)
+        ready = torch.cuda.Event()
+        ready.record(cur)
+        comm.wait_event(ready)
+        fused = bk.fused_group is not None
+        with torch.cuda.stream(comm):
+            self.launch_bucket_kernel(bk, world, algorithm, comm.cuda_stream, fused)
+        done = torch.cuda.Event(enable_timing=self.collect_stats)
+        done.record(comm)
+        self._last_done = done
+        if fused:
+            opt = bk.fused_group[0]
+            opt.mark_fused_done(bk.fused_params)
+
+    def finish(self, buckets):
+        cur = torch.cuda.current_stream(self.device)
+        if self.collect_stats:
+            self._bw_end = torch.cuda.Event(enable_timing=True)
+            self._bw_end.record(cur)
+        if self._last_done is not None:
+            cur.wait_event(self._last_done)
+            if self.collect_stats:
+                self._exposed_ms.append((self._bw_end, self._last_done))
+        self._last_done = None
+
+    def stats(self):
+        out = {"backend": "b200", "algorithms": dict(self._algo_used), "multicast": bool(self.seg and self.seg.mc_ptr)}
+        if self._exposed_ms:
+            torch.cuda.synchronize(self.device)
+            vals = [max(0.0, a.elapsed_time(b)) for a, b in self._exposed_ms[-50:]]
+            out["exposed_comm_ms"] = sum(vals) / len(vals)
+        return out

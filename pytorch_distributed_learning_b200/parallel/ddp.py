@@ -56,13 +56,12 @@ def compute_bucket_assignment_by_size(sizes_bytes, limits, kinds=None):
 
 
 class _Bucket:
-    __slots__ = ("index", "param_ids", "offset", "numel", "pending", "launched", "fused_group", "ready_event", "done_event", "grads")
+    __slots__ = ("index", "param_ids", "offset", "numel", "pending", "launched", "fused_group", "fused_params", "first_flag", "grads")
 
     def __init__(self, index, param_ids, offset, numel):
         self.index, self.param_ids, self.offset, self.numel = index, param_ids, offset, numel
         self.pending, self.launched = len(param_ids), False
-        self.fused_group = None
-        self.ready_event = self.done_event = None
+        self.fused_group, self.fused_params, self.first_flag = None, (), 1
         self.grads = {}
 
 
@@ -317,8 +316,10 @@ class DistributedDataParallel(nn.Module):
             if owner is None:
                 continue
             opt, group = owner
-            if opt.attach_bucket(self, bk, [self._params[i] for i in bk.param_ids], [self._offset_of[i] for i in bk.param_ids], group):
-                bk.fused_group = (opt, group)
+            members = [self._params[i] for i in bk.param_ids]
+            info = opt.attach_bucket(self, bk, members, [self._offset_of[i] for i in bk.param_ids], group)
+            if info:
+                bk.fused_group, bk.fused_params, bk.first_flag = (opt, group), members, info.get("first", 1)
 
     # ------------------------------------------------------------------ API parity
     @contextmanager

@@ -1,0 +1,143 @@
+"""Whole-step checks on one B200: graphed TrainStep and the GPU DDP path (world size 1)."""
+import copy
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+import pytorch_distributed_learning_b200 as pdl  # noqa: E402
+from conftest import free_port  # noqa: E402
+
+
+@pytest.fixture(autouse=True)
+def _strict_fp32():
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    yield
+
+
+class RefConvNet(torch.nn.Module):  # the reference model's layer list (launch_dist.py:9-41) on stock torch ops
+    def __init__(self):
+        super().__init__()
+        self.conv1, self.conv2, self.conv3 = torch.nn.Conv2d(1, 32, 5, 1, 1), torch.nn.Conv2d(32, 64, 3), torch.nn.Conv2d(64, 128, 3)
+        self.fc1 = torch.nn.Linear(2048, 10)
+
+    def forward(self, x):
+        x = F.max_pool2d(torch.relu(self.conv1(x)), 2, 2)
+        x = F.max_pool2d(torch.relu(self.conv2(x)), 2, 1)
+        x = F.max_pool2d(torch.relu(self.conv3(x)), 2, 2)
+        return self.fc1(x.view(-1, 2048))
+
+
+def _reference_run(state, batches, opt_kw):
+    ref = RefConvNet().cuda()
+    ref.load_state_dict(state)
+    opt = torch.optim.SGD(ref.parameters(), **opt_kw)
+    losses = []
+    for x, y in batches:
+        loss = F.cross_entropy(ref(x.cuda()), y.cuda())
+        opt.zero_grad()
+        loss.backward()
+        opt.step()
+        losses.append(loss.item())
+    return ref, losses
+
+
+@pytest.mark.parametrize("opt_kw", [dict(lr=1e-2), dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)])
+@pytest.mark.parametrize("batch", [100, 7])
+def test_graphed_trainstep_matches_torch(opt_kw, batch):
+    torch.manual_seed(0)
+    model = pdl.models.ConvNet().cuda()
+    state = copy.deepcopy(model.state_dict())
+    opt = pdl.optim.SGD(model.parameters(), **opt_kw)
+    step = pdl.TrainStep(model, pdl.nn.CrossEntropyLoss(), opt)
+    assert step.graphed
+    g = torch.Generator().manual_seed(1)
+    batches = [(torch.randn(batch, 1, 28, 28, generator=g).pin_memory(), torch.randint(0, 10, (batch,), generator=g).pin_memory()) for _ in range(5)]
+    losses = [step(x, y).item() for x, y in batches]
+    ref, ref_losses = _reference_run(state, batches, opt_kw)
+    torch.testing.assert_close(torch.tensor(losses), torch.tensor(ref_losses), rtol=1e-4, atol=1e-5)
+    for (n, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
+        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5, msg=lambda m, n=n: "%s: %s" % (n, m))
+    assert step.kernels_per_step() > 0
+    # state_dict keys are the reference model's
+    assert list(model.state_dict().keys())[0] == "conv1.weight"
+
+
+def test_eager_trainstep_equals_graphed():
+    torch.manual_seed(0)
+    a = pdl.models.ConvNet().cuda()
+    b = copy.deepcopy(a)
+    oa, ob = pdl.optim.SGD(a.parameters(), 1e-2), pdl.optim.SGD(b.parameters(), 1e-2)
+    sa = pdl.TrainStep(a, pdl.nn.CrossEntropyLoss(), oa)
+    sb = pdl.TrainStep(b, pdl.nn.CrossEntropyLoss(), ob, use_graph=False)
+    assert sa.graphed and not sb.graphed
+    x, y = torch.randn(16, 1, 28, 28).cuda(), torch.randint(0, 10, (16,)).cuda()
+    for _ in range(3):
+        la, lb = sa(x, y), sb(x, y)
+        torch.testing.assert_close(la, lb, rtol=1e-5, atol=1e-6)
+    for pa, pb in zip(a.parameters(), b.parameters()):
+        torch.testing.assert_close(pa, pb, rtol=1e-5, atol=1e-6)
+
+
+@pytest.mark.parametrize("ours_optim", [True, False])
+def test_ddp_world1_b200_backend(ours_optim):
+    """Symmetric segment + bucket kernel on a single rank: fused SGD with our optimizer, plain
+    averaging (then torch.optim.SGD) otherwise.  Reference call shape: launch_dist.py:59-61."""
+    dist = pdl.distributed
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % free_port(), world_size=1, rank=0)
+    try:
+        torch.manual_seed(0)
+        model = pdl.models.ConvNet().cuda()
+        state = copy.deepcopy(model.state_dict())
+        kw = dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)
+        opt = (pdl.optim.SGD if ours_optim else torch.optim.SGD)(model.parameters(), **kw)  # optimizer BEFORE the wrap, like launch_dist.py
+        ddp = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[0], output_device=0)
+        crit = pdl.nn.CrossEntropyLoss().cuda(0)
+        g = torch.Generator().manual_seed(1)
+        batches = [(torch.randn(12, 1, 28, 28, generator=g), torch.randint(0, 10, (12,), generator=g)) for _ in range(4)]
+        losses = []
+        for x, y in batches:
+            x, y = x.cuda(non_blocking=True), y.cuda(non_blocking=True)
+            loss = crit(ddp(x), y)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            losses.append(loss.item())
+        stats = ddp.get_step_stats()
+        assert stats["buckets_launched"] == 4 and stats["backend"] == "b200"
+        assert stats["fused_buckets"] == (4 if ours_optim else 0)
+        ref, ref_losses = _reference_run(state, batches, kw)
+        torch.testing.assert_close(torch.tensor(losses), torch.tensor(ref_losses), rtol=1e-4, atol=1e-5)
+        for a, b in zip(model.parameters(), ref.parameters()):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5)
+        # graphed step on top of the same DDP object keeps working
+        if ours_optim:
+            step = pdl.TrainStep(ddp, crit, opt)
+            assert step.graphed
+            l0 = step(batches[0][0].pin_memory(), batches[0][1].pin_memory()).item()
+            assert l0 == l0
+    finally:
+        dist.destroy_process_group()
+
+
+def test_resnet18_modules_train_step_matches_torchvision():
+    import torchvision
+
+    torch.manual_seed(0)
+    ours = pdl.models.resnet18(num_classes=10).cuda()
+    ref = torchvision.models.resnet18(num_classes=10).cuda()
+    ref.load_state_dict(ours.state_dict())
+    x, y = torch.randn(8, 3, 32, 32).cuda(), torch.randint(0, 10, (8,)).cuda()
+    lo = pdl.nn.CrossEntropyLoss()(ours(x), y)
+    lr = F.cross_entropy(ref(x), y)
+    torch.testing.assert_close(lo, lr, rtol=1e-3, atol=1e-3)
+    lo.backward()
+    lr.backward()
+    ga = dict(ours.named_parameters())["conv1.weight"].grad
+    gb = dict(ref.named_parameters())["conv1.weight"].grad
+    torch.testing.assert_close(ga, gb, rtol=5e-2, atol=5e-3)
+    for (n, a), (_, b) in zip(ours.named_buffers(), ref.named_buffers()):
+        torch.testing.assert_close(a.float(), b.float(), rtol=1e-3, atol=1e-4, msg=lambda m, n=n: "%s: %s" % (n, m))
