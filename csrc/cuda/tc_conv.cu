@@ -1,0 +1,367 @@
+// Implicit-GEMM convolution on the 5th-gen tensor cores: TMA-fed, tcgen05.mma (kind::tf32) with the
+// accumulator in TMEM, warp-specialised (TMA producer / single-thread MMA issuer / epilogue warps).
+//
+// Replaces the cuDNN TF32 convolutions the reference's ConvNet runs (launch_dist.py:15-25 forward,
+// backward through loss.backward() at :91):
+//   forward  y[m, co]  = sum_{r,s,ci} x[pix(m)+(r,s), ci] * w[co, ci, r, s]   (+bias, ReLU, 2x2 max-pool fused)
+//   dgrad    dx[m, ci] = sum_{r,s,co} dy[pix(m)-(r,s), co] * w[co, ci, r, s]   (TMA zero-fills the halo)
+// Activations are NHWC.  One M tile = a 4-D TMA box (32 channels x BW x BH x BN pixels <= 128 rows)
+// landing as 128-byte rows in a SWIZZLE_128B K-major operand; the filter tap only shifts the box
+// origin, so no im2col buffer ever exists.  Weights are pre-packed per tap as [tap][n][k] (K-major).
+// fp32 storage everywhere, TF32 multiplies, fp32 accumulation (the reference's convs are TF32 too).
+#include "common.cuh"
+#include "tc_common.cuh"
+
+namespace {
+
+constexpr int kStages = 4;
+constexpr int kThreads = 256;
+constexpr int A_BYTES = 128 * 128;  // 128 rows x 32 tf32
+
+enum Epi : int { EPI_STORE = 0, EPI_RELU_POOL = 1 };
+
+struct TcGeom {
+  int num_tiles;
+  int BW, BH, BN;        // TMA box extents in pixels; rows = BW*BH*BN <= 128
+  int tiles_per_img;     // row strips per image when BN == 1
+  int R, S, kchunks;     // filter taps, 32-wide K chunks per tap
+  int a_w0, a_h0;        // input coordinate read by output pixel (0,0) at tap (0,0)
+  int tap_sign;          // +1: coord = base + tap (forward); -1: coord = base - tap (dgrad)
+  int Nimg, Hout, Wout;  // output extent (Wout == BW)
+};
+
+struct EpiArgs {
+  float* out;
+  uint8_t* idx;
+  const float* bias;
+  int relu;
+  int pool_stride;
+  int* error;
+};
+
+template <int N_GEMM>
+struct Smem {
+  static constexpr int B_BYTES = N_GEMM * 128;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGING_LD = N_GEMM + 4;
+  static constexpr int STAGING_BYTES = 128 * STAGING_LD * 4;
+  static constexpr int BAR_OFFSET = kStages * STAGE_BYTES + STAGING_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // + barriers + alignment slack
+};
+
+template <int N_GEMM, int EPI>
+__global__ void __launch_bounds__(kThreads, 1)
+tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcGeom g, const EpiArgs e) {
+  using SM = Smem<N_GEMM>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  float* staging = reinterpret_cast<float*>(smem + kStages * SM::STAGE_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + SM::BAR_OFFSET);
+  uint64_t* empty = full + kStages;
+  uint64_t* tfull = empty + kStages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  volatile int* failed = reinterpret_cast<volatile int*>(tmem_slot + 1);
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  constexpr uint32_t kTmemCols = (2 * N_GEMM <= 32) ? 32 : (2 * N_GEMM <= 64) ? 64 : (2 * N_GEMM <= 128) ? 128 : (2 * N_GEMM <= 256) ? 256 : 512;
+
+  if (threadIdx.x == 0) {
+    tc::prefetch_tmap(&tmA);
+    tc::prefetch_tmap(&tmB);
+    for (int i = 0; i < kStages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { tc::mbar_init(&tfull[i], 1); tc::mbar_init(&tempty[i], 4); }
+    *failed = 0;
+    tc::fence_barrier_init();
+  }
+  if (warp == 2) tc::tmem_alloc(tmem_slot, kTmemCols);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int ksteps = g.R * g.S * g.kchunks;
+  const int rows = g.BW * g.BH * g.BN;
+  const uint32_t stage_tx = static_cast<uint32_t>(rows * 128 + SM::B_BYTES);
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (tc::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < g.num_tiles && !*failed; tile += gridDim.x) {
+        const int n0 = g.BN > 1 ? tile * g.BN : tile / g.tiles_per_img;
+        const int h0 = g.BN > 1 ? 0 : (tile % g.tiles_per_img) * g.BH;
+        for (int ks = 0; ks < ksteps; ++ks) {
+          if (!tc::mbar_wait(&empty[stage], phase ^ 1)) { *failed = 1; break; }
+          const int tap = ks / g.kchunks, kc = ks % g.kchunks;
+          const int r = tap / g.S, s = tap % g.S;
+          uint8_t* a_dst = smem + stage * SM::STAGE_BYTES;
+          tc::mbar_expect_tx(&full[stage], stage_tx);
+          tc::tma_load_4d(a_dst, &tmA, &full[stage], kc * 32, g.a_w0 + g.tap_sign * s, h0 + g.a_h0 + g.tap_sign * r, n0);
+          tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, tap * N_GEMM);
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    constexpr uint32_t idesc = tc::idesc_tf32(128, N_GEMM, 0, 0);
+    int stage = 0, acc = 0;
+    uint32_t phase = 0, acc_phase = 0;
+    for (int tile = blockIdx.x; tile < g.num_tiles && !*failed; tile += gridDim.x) {
+      if (!tc::mbar_wait(&tempty[acc], acc_phase ^ 1)) { *failed = 1; break; }
+      tc::tc_fence_after();
+      const uint32_t d_tmem = tmem_base + acc * N_GEMM;
+      for (int ks = 0; ks < ksteps; ++ks) {
+        if (!tc::mbar_wait(&full[stage], phase)) { *failed = 1; break; }
+        tc::tc_fence_after();
+        if (tc::elect_one()) {
+          const uint32_t a_addr = tc::smem_u32(smem + stage * SM::STAGE_BYTES);
+          const uint32_t b_addr = a_addr + A_BYTES;
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {  // 4 x K=8 tf32 = one 128-byte swizzle row
+            tc::mma_tf32(d_tmem, tc::smem_desc_sw128(a_addr + k * 32, 0, 1024), tc::smem_desc_sw128(b_addr + k * 32, 0, 1024), idesc,
+                         (ks | k) != 0);
+          }
+          tc::mma_commit(&empty[stage]);                      // frees the smem slot when these MMAs retire
+          if (ks == ksteps - 1) tc::mma_commit(&tfull[acc]);  // accumulator complete -> epilogue
+        }
+        __syncwarp();
+        if (++stage == kStages) { stage = 0; phase ^= 1; }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (128 threads, thread t owns accumulator row t) =====================
+    const int et = threadIdx.x - 128;
+    const int quarter = warp & 3;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
+      if (*failed || !tc::mbar_wait(&tfull[acc], acc_phase)) { *failed = 1; break; }
+      tc::tc_fence_after();
+      const int n0 = g.BN > 1 ? tile * g.BN : tile / g.tiles_per_img;
+      const int h0 = g.BN > 1 ? 0 : (tile % g.tiles_per_img) * g.BH;
+      const uint32_t t_row = tmem_base + acc * N_GEMM + (static_cast<uint32_t>(quarter * 32) << 16);
+      const int bw = et % g.BW, t2 = et / g.BW, bh = t2 % g.BH, bn = t2 / g.BH;
+      const bool valid = et < rows && (n0 + bn) < g.Nimg && (h0 + bh) < g.Hout;
+      if (EPI == EPI_STORE) {
+        float* dst = e.out + ((static_cast<long long>(n0 + bn) * g.Hout + h0 + bh) * g.Wout + bw) * N_GEMM;
+#pragma unroll 1
+        for (int c = 0; c < N_GEMM; c += 32) {
+          float v[32];
+          tc::tmem_ld32(t_row + c, v);
+          if (valid) {
+#pragma unroll
+            for (int j = 0; j < 32; j += 4) {
+              float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+              if (e.bias) { o.x += e.bias[c + j]; o.y += e.bias[c + j + 1]; o.z += e.bias[c + j + 2]; o.w += e.bias[c + j + 3]; }
+              if (e.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+              *reinterpret_cast<float4*>(dst + c + j) = o;
+            }
+          }
+        }
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&tempty[acc]);
+      } else {
+        // bias + ReLU into the staging tile, then 2x2 max-pool (stride 1 or 2) with first-max argmax
+#pragma unroll 1
+        for (int c = 0; c < N_GEMM; c += 32) {
+          float v[32];
+          tc::tmem_ld32(t_row + c, v);
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) {
+            float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+            if (e.bias) { o.x += e.bias[c + j]; o.y += e.bias[c + j + 1]; o.z += e.bias[c + j + 2]; o.w += e.bias[c + j + 3]; }
+            o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
+            *reinterpret_cast<float4*>(staging + et * SM::STAGING_LD + c + j) = o;
+          }
+        }
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&tempty[acc]);  // TMEM buffer is free: the next tile's MMAs may start
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const int ps = e.pool_stride;
+        const int PH = (g.BH - 2) / ps + 1, PW = (g.BW - 2) / ps + 1;
+        constexpr int C4 = N_GEMM / 4;
+        const int per_img = PH * PW * C4;
+        for (int o = et; o < g.BN * per_img; o += 128) {
+          const int img = o / per_img, rem = o % per_img;
+          const int pp = rem / C4, c4 = rem % C4;
+          const int ph = pp / PW, pw = pp % PW;
+          if (n0 + img >= g.Nimg) continue;
+          const float* base = staging + ((img * g.BH + ph * ps) * g.BW + pw * ps) * SM::STAGING_LD + c4 * 4;
+          const float4 v00 = *reinterpret_cast<const float4*>(base);
+          const float4 v01 = *reinterpret_cast<const float4*>(base + SM::STAGING_LD);
+          const float4 v10 = *reinterpret_cast<const float4*>(base + g.BW * SM::STAGING_LD);
+          const float4 v11 = *reinterpret_cast<const float4*>(base + (g.BW + 1) * SM::STAGING_LD);
+          float4 best = v00;
+          uchar4 arg = make_uchar4(0, 0, 0, 0);
+#define PDL_POOL_STEP(V, K)                                   \
+  if (V.x > best.x) { best.x = V.x; arg.x = K; }              \
+  if (V.y > best.y) { best.y = V.y; arg.y = K; }              \
+  if (V.z > best.z) { best.z = V.z; arg.z = K; }              \
+  if (V.w > best.w) { best.w = V.w; arg.w = K; }
+          PDL_POOL_STEP(v01, 1)
+          PDL_POOL_STEP(v10, 2)
+          PDL_POOL_STEP(v11, 3)
+#undef PDL_POOL_STEP
+          const long long oidx = (static_cast<long long>(n0 + img) * PH * PW + pp) * N_GEMM + c4 * 4;
+          *reinterpret_cast<float4*>(e.out + oidx) = best;
+          *reinterpret_cast<uchar4*>(e.idx + oidx) = arg;
+        }
+        asm volatile("bar.sync 1, 128;" ::: "memory");  // staging may be overwritten by the next tile
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, kTmemCols);
+  if (threadIdx.x == 0 && *failed && e.error) *e.error = 1;
+}
+
+// ---- host side ----
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+EncodeTiledFn encode_tiled() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+
+// NHWC activation [N][H][W][C] viewed as a 4-D tensor (C, W, H, N); box = (32, bw, bh, bn).
+int make_act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int bw, int bh, int bn) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) { pdl_set_error("cuTensorMapEncodeTiled is not available"); return -1; }
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+  cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(activation %dx%dx%dx%d, box %dx%dx%d) failed: %d", N, H, W, C, bw, bh, bn, (int)r); return -2; }
+  return 0;
+}
+
+// Packed weights [rows][K] (K contiguous) as a 2-D tensor (K, rows); box = (32, box_rows).
+int make_weight_map(CUtensorMap* m, const float* base, int rows, int K, int box_rows) {
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) { pdl_set_error("cuTensorMapEncodeTiled is not available"); return -1; }
+  cuuint64_t dims[2] = {(cuuint64_t)K, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)K * 4};
+  cuuint32_t box[2] = {32, (cuuint32_t)box_rows};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(weights %dx%d) failed: %d", rows, K, (int)r); return -2; }
+  return 0;
+}
+
+template <int N_GEMM, int EPI>
+int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const TcGeom& g, const EpiArgs& e, cudaStream_t stream) {
+  static bool configured = false;
+  auto kernel = tc_conv_kernel<N_GEMM, EPI>;
+  if (!configured) {
+    PDL_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<N_GEMM>::TOTAL));
+    configured = true;
+  }
+  int grid = g.num_tiles < 148 ? g.num_tiles : 148;
+  kernel<<<grid, kThreads, Smem<N_GEMM>::TOTAL, stream>>>(a, b, g, e);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+template <int EPI>
+int dispatch_n(int n_gemm, const CUtensorMap& a, const CUtensorMap& b, const TcGeom& g, const EpiArgs& e, cudaStream_t stream) {
+  switch (n_gemm) {
+    case 32: return launch_tc<32, EPI>(a, b, g, e, stream);
+    case 64: return launch_tc<64, EPI>(a, b, g, e, stream);
+    case 128: return launch_tc<128, EPI>(a, b, g, e, stream);
+    default: pdl_set_error("tc_conv: unsupported GEMM N %d", n_gemm); return -3;
+  }
+}
+
+// Chooses the M-tile box for an output of Hout x Wout pixels per image.  Returns false if no box fits.
+bool choose_box(int Hout, int Wout, int need_whole_image, TcGeom* g) {
+  if (Wout > 128) return false;
+  if (Hout * Wout <= 128) {
+    g->BW = Wout; g->BH = Hout; g->BN = 128 / (Hout * Wout); g->tiles_per_img = 1;
+    if (g->BN > 1 && !need_whole_image && false) g->BN = 1;
+    return true;
+  }
+  if (need_whole_image) return false;
+  g->BW = Wout; g->BH = 128 / Wout; g->BN = 1; g->tiles_per_img = (Hout + g->BH - 1) / g->BH;
+  return g->BH >= 1;
+}
+
+__global__ void pack_weights_kernel(const float* __restrict__ w, float* __restrict__ fwd, float* __restrict__ bwd, int Cout, int Cin, int taps) {
+  // w[co][ci][tap] -> fwd[tap][co][ci] (forward B operand, K = ci) and bwd[tap][ci][co] (dgrad B operand, K = co)
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  int total = Cout * Cin * taps;
+  if (i >= total) return;
+  int tap = i % taps, ci = (i / taps) % Cin, co = i / (taps * Cin);
+  float v = w[i];
+  if (fwd) fwd[(tap * Cout + co) * Cin + ci] = v;
+  if (bwd) bwd[(tap * Cin + ci) * Cout + co] = v;
+}
+
+}  // namespace
+
+// 1 if the tensor-core forward path covers this shape (stride 1, Cin % 32 == 0, Cout in {32,64,128}).
+PDL_API int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool) {
+  if (stride != 1 || Cin % 32 || !(Cout == 32 || Cout == 64 || Cout == 128)) return 0;
+  int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
+  TcGeom g{};
+  return choose_box(P, Q, pool, &g) ? 1 : 0;
+}
+
+// w[Cout][Cin][KH][KW] -> packed_fwd[tap][Cout][Cin], packed_bwd[tap][Cin][Cout] (either may be null).
+PDL_API int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed_bwd, int Cout, int Cin, int taps, cudaStream_t stream) {
+  int total = Cout * Cin * taps;
+  pack_weights_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(w, packed_fwd, packed_bwd, Cout, Cin, taps);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// Forward: y = conv(x, w) + bias, optional ReLU; with pool_stride in {1,2} the 2x2 max-pool is fused and
+// `y`/`idx` receive the POOLED output [N][PH][PW][Cout] and its argmax (0..3).  x is NHWC.
+PDL_API int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin,
+                              int Cout, int KH, int KW, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream) {
+  TcGeom g{};
+  const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
+  if (!choose_box(P, Q, pool_stride > 0, &g)) { pdl_set_error("tc_conv fwd: no tile for %dx%d output", P, Q); return -4; }
+  g.num_tiles = g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img;
+  g.R = KH; g.S = KW; g.kchunks = Cin / 32; g.a_w0 = -pad; g.a_h0 = -pad; g.tap_sign = 1; g.Nimg = N; g.Hout = P; g.Wout = Q;
+  CUtensorMap ta, tb;
+  if (int rc = make_act_map(&ta, x, N, H, W, Cin, g.BW, g.BH, g.BN)) return rc;
+  if (int rc = make_weight_map(&tb, packed_w, KH * KW * Cout, Cin, Cout)) return rc;
+  EpiArgs e{y, idx, bias, relu, pool_stride, error_flag};
+  return pool_stride > 0 ? dispatch_n<EPI_RELU_POOL>(Cout, ta, tb, g, e, stream) : dispatch_n<EPI_STORE>(Cout, ta, tb, g, e, stream);
+}
+
+// dgrad (stride 1): dx[N][H][W][Cin] from dy[N][P][Q][Cout] and packed_bwd[tap][Cin][Cout].
+PDL_API int pdl_tc_conv2d_dgrad(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                                int pad, int* error_flag, cudaStream_t stream) {
+  TcGeom g{};
+  const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
+  if (Cout % 32 || !(Cin == 32 || Cin == 64 || Cin == 128)) { pdl_set_error("tc_conv dgrad: unsupported channels %d -> %d", Cout, Cin); return -3; }
+  if (!choose_box(H, W, 0, &g)) { pdl_set_error("tc_conv dgrad: no tile for %dx%d", H, W); return -4; }
+  g.num_tiles = g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img;
+  // dx[h, w] = sum_{r,s} dy[h + pad - r, w + pad - s] * w[r, s]
+  g.R = KH; g.S = KW; g.kchunks = Cout / 32; g.a_w0 = pad; g.a_h0 = pad; g.tap_sign = -1; g.Nimg = N; g.Hout = H; g.Wout = W;
+  CUtensorMap ta, tb;
+  if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
+  if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, Cin)) return rc;
+  EpiArgs e{dx, nullptr, nullptr, 0, 0, error_flag};
+  return dispatch_n<EPI_STORE>(Cin, ta, tb, g, e, stream);
+}

@@ -1,0 +1,275 @@
+// Convolution weight gradient on tcgen05 tensor cores (TF32 in, FP32 accumulate in TMEM).
+//
+//   dW[co][ci][r][s] = sum over pixels (n,p,q) of dy[n,p,q,co] * x[n, p+r-pad, q+s-pad, ci]
+//
+// GEMM view: M = Cout, N = Cin (one accumulator per filter tap), K = pixels.  Both operands are
+// "MN-major" (channels contiguous, one 128-byte row per pixel), which is exactly how TMA lands an
+// NHWC box in shared memory -- no transposes, and the filter tap only shifts the x box in the outer
+// (W, H) coordinates.  32-bit MN-major operands need the 32-byte-atom flavour of the 128-byte
+// swizzle on both sides (TMA: SWIZZLE_128B_ATOM_32B, UMMA descriptor: SWIZZLE_128B_BASE32B, 4-row
+// K atoms); the plain SWIZZLE_128B descriptor silently yields zeros for TF32 (measured).  A pixel
+// box is (32 ch, BW, BH, 1) with BW rounded up to a multiple of 8; TMA zero-fills the out-of-range
+// columns/rows of dy, so padded rows add exact zeros.  The dy tile is reused for the taps of one
+// filter row, K is split over CTAs, each CTA writes partial sums to a scratch buffer, and a second
+// kernel reduces the splits in fixed order (deterministic) into the gradient bucket and finishes the
+// bias gradient.  Replaces cuDNN wgrad + ATen bias reductions.
+#include "common.cuh"
+#include "tc_common.cuh"
+
+#include <cstdlib>
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kMaxTapsPerCta = 3;
+
+struct WgGeom {
+  int BW, BH;            // pixel box (BW % 8 == 0), rows = BW*BH in {64, 128}
+  int strips;            // row strips per image
+  int units;             // N * strips  (K work items)
+  int units_per_cta;     // K split
+  int S;                 // taps per filter row (= taps handled by one CTA, <= 3)
+  int pad;
+  int layout_type, lbo, sbo, tma_swizzle;  // descriptor knobs (defaults set on the host)
+};
+
+__device__ __forceinline__ uint64_t smem_desc_lt(uint32_t smem_addr, uint32_t lbo, uint32_t sbo, uint32_t layout_type) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr >> 4) & 0x3FFF);
+  d |= static_cast<uint64_t>((lbo >> 4) & 0x3FFF) << 16;
+  d |= static_cast<uint64_t>((sbo >> 4) & 0x3FFF) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(layout_type & 7) << 61;
+  return d;
+}
+
+template <int M_GEMM, int N_GEMM>  // M_GEMM = Cout (64|128), N_GEMM = Cin (32|64)
+__global__ void __launch_bounds__(kThreads, 1)
+tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant__ CUtensorMap tmX, const WgGeom g, float* __restrict__ partial,
+                int* __restrict__ error) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
+  const int rows = g.BW * g.BH;
+  const int chunk_bytes = rows * 128;
+  constexpr int A_CHUNKS = M_GEMM / 32, B_CHUNKS = N_GEMM / 32;
+  const int a_bytes = A_CHUNKS * chunk_bytes;
+  const int b_tap_bytes = B_CHUNKS * chunk_bytes;
+  const int stage_bytes = a_bytes + g.S * b_tap_bytes;
+  const int stages = (stage_bytes * 4 <= 200 * 1024) ? 4 : (stage_bytes * 3 <= 200 * 1024) ? 3 : 2;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * stage_bytes);
+  uint64_t* empty = full + 4;
+  uint64_t* done = empty + 4;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done + 1);
+  volatile int* failed = reinterpret_cast<volatile int*>(tmem_slot + 1);
+
+  const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+  constexpr uint32_t kCols = (kMaxTapsPerCta * N_GEMM <= 128) ? 128 : 256;
+  const int tap_row = blockIdx.x;  // filter row r
+  const int split = blockIdx.y;
+  const int u_begin = split * g.units_per_cta;
+  const int u_end = min(g.units, u_begin + g.units_per_cta);
+
+  if (threadIdx.x == 0) {
+    tc::prefetch_tmap(&tmDy);
+    tc::prefetch_tmap(&tmX);
+    for (int i = 0; i < 4; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+    tc::mbar_init(done, 1);
+    *failed = 0;
+    tc::fence_barrier_init();
+  }
+  if (warp == 2) tc::tmem_alloc(tmem_slot, kCols);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (tc::elect_one()) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int u = u_begin; u < u_end; ++u) {
+        if (!tc::mbar_wait(&empty[stage], phase ^ 1)) { *failed = 1; break; }
+        const int n = u / g.strips, h0 = (u % g.strips) * g.BH;
+        uint8_t* base = smem + stage * stage_bytes;
+        tc::mbar_expect_tx(&full[stage], static_cast<uint32_t>(stage_bytes));
+        for (int c = 0; c < A_CHUNKS; ++c) tc::tma_load_4d(base + c * chunk_bytes, &tmDy, &full[stage], c * 32, 0, h0, n);
+        for (int s = 0; s < g.S; ++s)
+          for (int c = 0; c < B_CHUNKS; ++c)
+            tc::tma_load_4d(base + a_bytes + s * b_tap_bytes + c * chunk_bytes, &tmX, &full[stage], c * 32, s - g.pad, h0 + tap_row - g.pad, n);
+        if (++stage == stages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    constexpr uint32_t idesc = tc::idesc_tf32(M_GEMM, N_GEMM, 1, 1);  // both operands MN-major
+    const uint32_t lbo = g.lbo ? g.lbo : chunk_bytes, sbo = g.sbo;
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int u = u_begin; u < u_end; ++u) {
+      if (!tc::mbar_wait(&full[stage], phase)) { *failed = 1; break; }
+      tc::tc_fence_after();
+      if (tc::elect_one()) {
+        const uint32_t a_addr = tc::smem_u32(smem + stage * stage_bytes);
+        const uint32_t b_addr = a_addr + a_bytes;
+        for (int k8 = 0; k8 < rows / 8; ++k8) {  // one MMA = 8 pixels = 8 rows of 128 B
+          const uint64_t a_desc = smem_desc_lt(a_addr + k8 * 1024, lbo, sbo, g.layout_type);
+          for (int s = 0; s < g.S; ++s) {
+            const uint64_t b_desc = smem_desc_lt(b_addr + s * b_tap_bytes + k8 * 1024, lbo, sbo, g.layout_type);
+            tc::mma_tf32(tmem_base + s * N_GEMM, a_desc, b_desc, idesc, (u != u_begin) || (k8 != 0));
+          }
+        }
+        tc::mma_commit(&empty[stage]);
+        if (u == u_end - 1) tc::mma_commit(done);
+      }
+      __syncwarp();
+      if (++stage == stages) { stage = 0; phase ^= 1; }
+    }
+  } else if (warp >= 4) {
+    const int quarter = warp & 3;
+    const bool has_work = u_end > u_begin;
+    bool ok = true;
+    if (has_work) ok = tc::mbar_wait(done, 0);
+    if (!ok) *failed = 1;
+    tc::tc_fence_after();
+    // accumulator row -> output channel: M=128: lane index; M=64: 16 rows per 32-lane quarter
+    const int co = (M_GEMM == 128) ? quarter * 32 + lane : quarter * 16 + lane;
+    const bool row_valid = (M_GEMM == 128) || lane < 16;
+    for (int s = 0; s < g.S; ++s) {
+      const int tap = tap_row * g.S + s;
+      float* dst = partial + ((static_cast<long long>(split) * (gridDim.x * g.S) + tap) * M_GEMM + co) * N_GEMM;
+#pragma unroll 1
+      for (int c = 0; c < N_GEMM; c += 32) {
+        float v[32];
+        if (has_work && ok) {
+          tc::tmem_ld32(tmem_base + s * N_GEMM + c + (static_cast<uint32_t>(quarter * 32) << 16), v);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) v[j] = 0.f;
+        }
+        if (row_valid) {
+#pragma unroll
+          for (int j = 0; j < 32; j += 4) *reinterpret_cast<float4*>(dst + c + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+      }
+    }
+  }
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tc::tmem_dealloc(tmem_base, kCols);
+  if (threadIdx.x == 0 && *failed && error) *error = 1;
+}
+
+// dw[co][ci][tap] = sum_split partial[split][tap][co][ci];  db[co] = sum_blk db_partial[blk][co]
+__global__ void wgrad_finish_kernel(const float* __restrict__ partial, int splits, int taps, int Cout, int Cin, float* __restrict__ dw,
+                                    const float* __restrict__ db_partial, int db_blocks, float* __restrict__ db) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per_split = taps * Cout * Cin;
+  if (i < per_split) {
+    // i indexes the OUTPUT layout so writes are coalesced
+    const int tap = i % taps, ci = (i / taps) % Cin, co = i / (taps * Cin);
+    const float* src = partial + (static_cast<long long>(tap) * Cout + co) * Cin + ci;
+    float acc = 0.f;
+    for (int s = 0; s < splits; ++s) acc += src[static_cast<long long>(s) * per_split];
+    dw[i] = acc;
+  } else if (db && i < per_split + Cout) {
+    const int co = i - per_split;
+    float acc = 0.f;
+    for (int b = 0; b < db_blocks; ++b) acc += db_partial[b * Cout + co];
+    db[co] = acc;
+  }
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                  const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_wg() {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  return fn;
+}
+int act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int bw, int bh, int swizzle) {
+  EncodeTiledFn enc = encode_tiled_wg();
+  if (!enc) { pdl_set_error("cuTensorMapEncodeTiled is not available"); return -1; }
+  cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
+  cuuint64_t strides[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
+  cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, 1};
+  cuuint32_t es[4] = {1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   static_cast<CUtensorMapSwizzle>(swizzle), CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(wgrad operand) failed: %d", (int)r); return -2; }
+  return 0;
+}
+
+int env_int(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
+
+bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KW, int pad, WgGeom* g) {
+  if (!(Cout == 64 || Cout == 128) || !(Cin == 32 || Cin == 64) || KW > kMaxTapsPerCta) return false;
+  int bw = (Q + 7) / 8 * 8;
+  if (bw > 64) return false;
+  int bh = 64 / bw;  // 64-pixel K stages keep several stages in flight
+  if (bw * bh != 64) return false;
+  g->BW = bw; g->BH = bh; g->strips = (P + bh - 1) / bh; g->units = N * g->strips;
+  int splits = g->units < 16 ? g->units : (g->units <= 2048 ? 16 : 48);
+  g->units_per_cta = (g->units + splits - 1) / splits;
+  g->S = KW; g->pad = pad;
+  g->layout_type = env_int("PDL_WG_LT", 1);   // SWIZZLE_128B_BASE32B
+  g->lbo = env_int("PDL_WG_LBO", 0);          // 0 = distance between 32-channel chunks
+  g->sbo = env_int("PDL_WG_SBO", 512);        // 4-row K atoms, dense
+  g->tma_swizzle = env_int("PDL_WG_TMASW", static_cast<int>(CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B));
+  return true;
+}
+int wg_splits(const WgGeom& g) { return (g.units + g.units_per_cta - 1) / g.units_per_cta; }
+
+template <int M, int Nn>
+int launch_wg(const CUtensorMap& a, const CUtensorMap& b, const WgGeom& g, int KH, float* partial, int* error, cudaStream_t stream) {
+  auto kernel = tc_wgrad_kernel<M, Nn>;
+  static bool configured = false;
+  const int smem = 210 * 1024;
+  if (!configured) {
+    PDL_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  dim3 grid(KH, wg_splits(g));
+  kernel<<<grid, kThreads, smem, stream>>>(a, b, g, partial, error);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace
+
+PDL_API int pdl_tc_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
+  if (stride != 1) return 0;
+  WgGeom g{};
+  return wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KW, pad, &g) ? 1 : 0;
+}
+
+PDL_API long long pdl_tc_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad) {
+  WgGeom g{};
+  if (!wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KW, pad, &g)) return 0;
+  return static_cast<long long>(wg_splits(g)) * KH * KW * Cout * Cin * sizeof(float);
+}
+
+// x[N][H][W][Cin], dy[N][P][Q][Cout] (NHWC) -> dw[Cout][Cin][KH][KW]
+// (+ db[Cout] = fixed-order sum of db_partial[db_blocks][Cout] when db != nullptr).
+PDL_API int pdl_tc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch,
+                                int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad, int* error_flag, cudaStream_t stream) {
+  WgGeom g{};
+  const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
+  if (!wg_geometry(N, P, Q, Cin, Cout, KW, pad, &g)) { pdl_set_error("tc wgrad: unsupported shape"); return -3; }
+  CUtensorMap ta, tb;
+  if (int rc = act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.tma_swizzle)) return rc;
+  if (int rc = act_map(&tb, x, N, H, W, Cin, g.BW, g.BH, g.tma_swizzle)) return rc;
+  int rc = -3;
+  if (Cout == 128 && Cin == 64) rc = launch_wg<128, 64>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (Cout == 128 && Cin == 32) rc = launch_wg<128, 32>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (Cout == 64 && Cin == 32) rc = launch_wg<64, 32>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (Cout == 64 && Cin == 64) rc = launch_wg<64, 64>(ta, tb, g, KH, scratch, error_flag, stream);
+  if (rc) return rc;
+  const int total = KH * KW * Cout * Cin + (db ? Cout : 0);
+  wgrad_finish_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(scratch, wg_splits(g), KH * KW, Cout, Cin, dw, db_partial, db_blocks, db);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}

@@ -44,6 +44,14 @@ def declare(L):
     sig("pdl_conv2d_dgrad_simt", [P, P, P, I, I, I, I, I, I, I, I, I, P])
     sig("pdl_conv2d_wgrad_scratch_bytes", [I, I, I, I, I, I, I, I, I], LL)
     sig("pdl_conv2d_wgrad_simt", [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P])
+    # convolution (tcgen05 / TMA tensor-core path)
+    sig("pdl_tc_conv_supported", [I, I, I, I, I, I, I, I, I])
+    sig("pdl_tc_pack_weights", [P, P, P, I, I, I, P])
+    sig("pdl_tc_conv2d_fwd", [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, P])
+    sig("pdl_tc_conv2d_dgrad", [P, P, P, I, I, I, I, I, I, I, I, P, P])
+    sig("pdl_tc_wgrad_supported", [I, I, I, I, I, I, I, I, I])
+    sig("pdl_tc_wgrad_scratch_bytes", [I, I, I, I, I, I, I, I], LL)
+    sig("pdl_tc_conv2d_wgrad", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, P, P])
     # element-wise / pooling / linear / loss
     sig("pdl_relu_fwd", [P, P, LL, P])
     sig("pdl_relu_bwd", [P, P, P, LL, P])

@@ -111,6 +111,7 @@ class ConvNetEngine:
             bk = ddp._buckets[0]
             if bk.fused_group is None:
                 raise RuntimeError("TrainStep: the optimizer could not be fused into the bucket allreduce")
+            ddp._rebuilt = True  # the captured graph bakes in arena offsets: freeze the bucket layout
             self.backend, self.bucket = ddp._backend, bk
             index_of = {id(p): i for i, p in enumerate(ddp._params)}
             self.g_views = [ddp._in_views[index_of[id(p)]] for p in self.params]

@@ -330,11 +330,13 @@ class B200ReducerBackend:
         self._last_done = None
         self._bw_end = None
         self._algo_used = {}
+        self._attached = []
 
     def allocate(self, total, dtype, device, bucket_ranges):
         if dtype != torch.float32:
             raise NotImplementedError("the NVLink reducer averages fp32 gradients (the reference trains in fp32); got %s" % dtype)
         self._launch_cache.clear()
+        self._detach_fused_params()  # a re-layout moves every offset: params leave the flat arena first
         if self.seg is not None and total <= self.total:
             return
         pg, L = self.pg, self.L
@@ -350,6 +352,17 @@ class B200ReducerBackend:
         self._pads = _ptr_array([self.seg.ptr(r) for r in range(W)])
 
     # -- fused optimizer plumbing -----------------------------------------------------------
+    def _detach_fused_params(self):
+        with torch.no_grad():
+            for opt, group, params in getattr(self, "_attached", []):
+                for p in params:
+                    p.data = p.data.clone()
+                    st = opt.state.get(p)
+                    if st is not None and st.get("momentum_buffer") is not None:
+                        st["momentum_buffer"] = st["momentum_buffer"].clone()
+        self._attached = []
+        self._hyper = {}
+
     def attach_fused_params(self, opt, group, params, offsets):
         if any(p.dtype != torch.float32 or not p.is_cuda for p in params):
             return False
@@ -371,6 +384,7 @@ class B200ReducerBackend:
                         mview.copy_(old)
                         had_state = True
                     opt.state[p]["momentum_buffer"] = mview
+        self._attached.append((opt, group, list(params)))
         return {"first": 0 if had_state else 1}
 
     def _hyper_for(self, bk):

@@ -14,9 +14,11 @@ from pytorch_distributed_learning_b200.ops import functional as NF  # noqa: E402
 
 @pytest.fixture(autouse=True)
 def _strict_fp32():
+    old = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
     yield
+    torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = old
 
 
 def _dev():
