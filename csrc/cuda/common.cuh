@@ -23,6 +23,14 @@ void pdl_set_error(const char* fmt, ...);
 
 static inline int pdl_ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
 
+// Round-to-nearest TF32 (10-bit mantissa).  The tensor cores TRUNCATE fp32 operands to TF32; producers of
+// MMA operands round on store instead, which halves the error and removes the toward-zero bias.
+__device__ __forceinline__ float round_tf32(float x) {
+  uint32_t u;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(u) : "f"(x));
+  return __uint_as_float(u);
+}
+
 struct SgdHyper {  // lives in device memory so a captured CUDA graph sees LR-schedule changes
   float lr;
   float momentum;

@@ -1,0 +1,181 @@
+// Backward-side fused kernels of the ConvNet step (reference autograd of launch_dist.py:36-38):
+//   * 2x2 max-pool backward (stride 1 = overlapping windows, or 2) with the preceding ReLU folded in
+//     and the bias gradient of the preceding conv produced as per-CTA partial sums;
+//   * conv1 weight/bias gradient with pool1-backward + ReLU folded into the operand load
+//     (Cin = 1, 25 taps: CUDA cores; dz1 [N][26][26][32] is never materialised).
+// Both are latency-bound at batch 100, so loads are issued branch-free / staged through shared
+// memory to keep many of them in flight.
+#include "common.cuh"
+
+namespace {
+
+constexpr int kThreads = 256;
+
+// dz[n][h][w][c] = sum over the <=4 windows containing (h,w) whose argmax is (h,w) and whose pooled value > 0.
+// A CTA owns `pix_per_cta` consecutive pixels of the flattened [N*H*W] axis; column sums -> dbpart[cta][C].
+template <int C, int stride>
+__global__ void __launch_bounds__(kThreads) pool2_bwd_dbias_kernel(const float* __restrict__ da, const uint8_t* __restrict__ idx,
+                                                                   const float* __restrict__ pooled, float* __restrict__ dz,
+                                                                   float* __restrict__ dbpart, unsigned total_pix, unsigned H, unsigned W,
+                                                                   unsigned pix_per_cta) {
+  const int PH = (static_cast<int>(H) - 2) / stride + 1, PW = (static_cast<int>(W) - 2) / stride + 1;
+  constexpr int G = kThreads / C;
+  const int c = threadIdx.x % C, grp = threadIdx.x / C;
+  float colsum = 0.f;
+  const unsigned p_lo = blockIdx.x * pix_per_cta;  // 32-bit index math: 64-bit div/mod made this kernel ALU-bound
+  const unsigned p_hi = min(total_pix, p_lo + pix_per_cta);
+#pragma unroll 4
+  for (unsigned px = p_lo + grp; px < p_hi; px += G) {
+    const int w = static_cast<int>(px % W);
+    const unsigned t = px / W;
+    const int h = static_cast<int>(t % H);
+    const int n = static_cast<int>(t / H);
+    float acc = 0.f;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {  // window whose element (r,s) = (k/2, k%2) is this pixel
+      const int r = k >> 1, s = k & 1;
+      const int ph_ = h - r, pw_ = w - s;
+      const bool valid = ph_ >= 0 && pw_ >= 0 && (ph_ % stride) == 0 && (pw_ % stride) == 0 && (ph_ / stride) < PH && (pw_ / stride) < PW;
+      const int o = valid ? ((n * PH + ph_ / stride) * PW + pw_ / stride) * C + c : 0;  // branch-free: loads overlap
+      const float g = da[o], pv = pooled[o];
+      const int a = idx[o];
+      acc += (valid && a == k && pv > 0.f) ? g : 0.f;
+    }
+    colsum += acc;
+    dz[static_cast<size_t>(px) * C + c] = round_tf32(acc);  // operand of the tcgen05 dgrad / wgrad
+  }
+  __shared__ float cs[kThreads];
+  cs[threadIdx.x] = colsum;
+  __syncthreads();
+  if (threadIdx.x < C) {
+    float s = 0.f;
+#pragma unroll
+    for (int g = 0; g < G; ++g) s += cs[g * C + threadIdx.x];
+    dbpart[blockIdx.x * C + threadIdx.x] = s;
+  }
+}
+
+__device__ unsigned int g_c1w_done = 0;
+
+// conv1 wgrad: gw1[c][r][s] = sum_{n,ph,pw} g * x[n][2ph+dy+r-1][2pw+dx+s-1],  g = (a1 > 0) ? da1 : 0,
+// (dy,dx) = argmax of the pool window.  gb1[c] = sum g.  Per image: image, g and argmax are staged in shared
+// memory with coalesced, independent loads; thread = (channel, tap group).  Partials per CTA, the last CTA
+// reduces them in CTA order.
+__global__ void __launch_bounds__(kThreads) conv1_wgrad_fused_kernel(const float* __restrict__ x, const float* __restrict__ da1,
+                                                                     const uint8_t* __restrict__ idx1, const float* __restrict__ a1,
+                                                                     float* __restrict__ gw1, float* __restrict__ gb1, float* __restrict__ partial,
+                                                                     int N, int imgs_per_cta) {
+  __shared__ float img[30][32];
+  __shared__ float sg[169 * 32];
+  __shared__ uint8_t sarg[169 * 32];
+  const int c = threadIdx.x % 32, tg = threadIdx.x / 32;
+  float acc[4] = {0.f, 0.f, 0.f, 0.f}, accb = 0.f;
+  const int n_lo = blockIdx.x * imgs_per_cta, n_hi = min(N, n_lo + imgs_per_cta);
+  for (int n = n_lo; n < n_hi; ++n) {
+    __syncthreads();
+    for (int i = threadIdx.x; i < 30 * 32; i += kThreads) {
+      const int r = i / 32, cc = i % 32, h = r - 1, w = cc - 1;
+      img[r][cc] = (h >= 0 && h < 28 && w >= 0 && w < 28) ? x[(static_cast<long long>(n) * 28 + h) * 28 + w] : 0.f;
+    }
+    const long long base = static_cast<long long>(n) * 169 * 32;
+#pragma unroll 8
+    for (int i = threadIdx.x; i < 169 * 32; i += kThreads) {
+      const float a = a1[base + i], d = da1[base + i];
+      sg[i] = a > 0.f ? d : 0.f;
+      sarg[i] = idx1[base + i];
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int pp = 0; pp < 169; ++pp) {
+      const float g = sg[pp * 32 + c];
+      const int arg = sarg[pp * 32 + c];
+      const int h = 2 * (pp / 13) + (arg >> 1), w = 2 * (pp % 13) + (arg & 1);
+      if (tg == 0) accb += g;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const int t = tg + 8 * k;
+        if (t < 25) acc[k] = fmaf(g, img[h + t / 5][w + t % 5], acc[k]);
+      }
+    }
+  }
+  float* mine = partial + static_cast<long long>(blockIdx.x) * 832;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int t = tg + 8 * k;
+    if (t < 25) mine[c * 25 + t] = acc[k];
+  }
+  if (tg == 0) mine[800 + c] = accb;
+  __shared__ bool is_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    is_last = atomicAdd(&g_c1w_done, 1u) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (is_last) {
+    __threadfence();
+    // 4 outputs per thread, 8 partial rows per pass: 32 independent loads in flight (latency-bound otherwise)
+    float s[4] = {0.f, 0.f, 0.f, 0.f};
+    const unsigned nb = gridDim.x;
+#pragma unroll 8
+    for (unsigned b = 0; b < nb; ++b) {
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const int i = threadIdx.x + q * kThreads;
+        if (i < 832) s[q] += __ldcg(partial + static_cast<size_t>(b) * 832 + i);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int i = threadIdx.x + q * kThreads;
+      if (i < 800) gw1[i] = s[q]; else if (i < 832) gb1[i - 800] = s[q];
+    }
+    if (threadIdx.x == 0) g_c1w_done = 0;
+  }
+}
+
+int imgs_per_cta(int N) { int v = (N + 295) / 296; return v < 1 ? 1 : v; }
+
+int pool_pix_per_cta(long long total_pix, int C) {
+  const int G = kThreads / C;
+  long long p = (total_pix + 511) / 512;  // at most ~512 CTAs (= rows of dbpart)
+  if (p < 8 * G) p = 8 * G;
+  return static_cast<int>((p + G - 1) / G * G);
+}
+
+}  // namespace
+
+// Number of CTAs (= rows of `partial`) pdl_conv1_wgrad_fused uses for a batch of N images.
+PDL_API int pdl_bwd_blocks(int N) { int ipc = imgs_per_cta(N); return (N + ipc - 1) / ipc; }
+
+// Number of CTAs (= rows of `dbpart`) pdl_pool2_bwd_dbias uses.
+PDL_API int pdl_pool2_bwd_blocks(int N, int H, int W, int C) {
+  const long long total = static_cast<long long>(N) * H * W;
+  const int ppc = pool_pix_per_cta(total, C);
+  return static_cast<int>((total + ppc - 1) / ppc);
+}
+
+PDL_API int pdl_pool2_bwd_dbias(const float* da, const uint8_t* idx, const float* pooled, float* dz, float* dbpart, int N, int H, int W, int C,
+                                int stride, cudaStream_t stream) {
+  const long long total = static_cast<long long>(N) * H * W;
+  const int ppc = pool_pix_per_cta(total, C);
+  const int blocks = static_cast<int>((total + ppc - 1) / ppc);
+  if (total * C >= (1ll << 31) || (stride != 1 && stride != 2)) { pdl_set_error("pool2_bwd_dbias: tensor too large or bad stride"); return -1; }
+  const unsigned T = static_cast<unsigned>(total);
+#define PDL_POOL_CASE(CC, SS) \
+  if (C == CC && stride == SS) pool2_bwd_dbias_kernel<CC, SS><<<blocks, kThreads, 0, stream>>>(da, idx, pooled, dz, dbpart, T, H, W, ppc)
+  PDL_POOL_CASE(32, 1); else PDL_POOL_CASE(64, 1); else PDL_POOL_CASE(128, 1); else PDL_POOL_CASE(32, 2); else PDL_POOL_CASE(64, 2);
+  else PDL_POOL_CASE(128, 2); else { pdl_set_error("pool2_bwd_dbias: unsupported channel count %d", C); return -1; }
+#undef PDL_POOL_CASE
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// partial must hold pdl_bwd_blocks(N) * 832 floats.
+PDL_API int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_t* idx1, const float* a1, float* gw1, float* gb1, float* partial,
+                                  int N, cudaStream_t stream) {
+  const int ipc = imgs_per_cta(N), blocks = (N + ipc - 1) / ipc;
+  conv1_wgrad_fused_kernel<<<blocks, kThreads, 0, stream>>>(x, da1, idx1, a1, gw1, gb1, partial, N, ipc);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}

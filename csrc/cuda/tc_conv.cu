@@ -209,6 +209,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           PDL_POOL_STEP(v11, 3)
 #undef PDL_POOL_STEP
           const long long oidx = (static_cast<long long>(n0 + img) * PH * PW + pp) * N_GEMM + c4 * 4;
+          best = make_float4(round_tf32(best.x), round_tf32(best.y), round_tf32(best.z), round_tf32(best.w));  // next layer's MMA operand
           *reinterpret_cast<float4*>(e.out + oidx) = best;
           *reinterpret_cast<uchar4*>(e.idx + oidx) = arg;
         }
@@ -310,7 +311,7 @@ __global__ void pack_weights_kernel(const float* __restrict__ w, float* __restri
   int total = Cout * Cin * taps;
   if (i >= total) return;
   int tap = i % taps, ci = (i / taps) % Cin, co = i / (taps * Cin);
-  float v = w[i];
+  float v = round_tf32(w[i]);
   if (fwd) fwd[(tap * Cout + co) * Cin + ci] = v;
   if (bwd) bwd[(tap * Cin + ci) * Cout + co] = v;
 }

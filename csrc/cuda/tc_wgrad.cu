@@ -170,11 +170,19 @@ __global__ void wgrad_finish_kernel(const float* __restrict__ partial, int split
     float acc = 0.f;
     for (int s = 0; s < splits; ++s) acc += src[static_cast<long long>(s) * per_split];
     dw[i] = acc;
-  } else if (db && i < per_split + Cout) {
-    const int co = i - per_split;
-    float acc = 0.f;
-    for (int b = 0; b < db_blocks; ++b) acc += db_partial[b * Cout + co];
-    db[co] = acc;
+  }
+  // bias gradient: one warp per channel, lanes stride over the partial rows, fixed shuffle tree (deterministic)
+  if (db) {
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
+    const int first = (per_split + 31) / 32;  // warps past the weight outputs
+    const int co = warp_global - first;
+    if (co >= 0 && co < Cout) {
+      float acc = 0.f;
+      for (int b = lane; b < db_blocks; b += 32) acc += db_partial[b * Cout + co];
+#pragma unroll
+      for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+      if (lane == 0) db[co] = acc;
+    }
   }
 }
 
@@ -268,7 +276,7 @@ PDL_API int pdl_tc_conv2d_wgrad(const float* x, const float* dy, float* dw, floa
   else if (Cout == 64 && Cin == 32) rc = launch_wg<64, 32>(ta, tb, g, KH, scratch, error_flag, stream);
   else if (Cout == 64 && Cin == 64) rc = launch_wg<64, 64>(ta, tb, g, KH, scratch, error_flag, stream);
   if (rc) return rc;
-  const int total = KH * KW * Cout * Cin + (db ? Cout : 0);
+  const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
   wgrad_finish_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(scratch, wg_splits(g), KH * KW, Cout, Cin, dw, db_partial, db_blocks, db);
   PDL_LAUNCH_CHECK();
   return 0;

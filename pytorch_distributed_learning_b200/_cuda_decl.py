@@ -52,6 +52,17 @@ def declare(L):
     sig("pdl_tc_wgrad_supported", [I, I, I, I, I, I, I, I, I])
     sig("pdl_tc_wgrad_scratch_bytes", [I, I, I, I, I, I, I, I], LL)
     sig("pdl_tc_conv2d_wgrad", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, P, P])
+    # fused ConvNet kernels
+    sig("pdl_convnet_pack", [P, P, P, P, P, P, P, P, P])
+    sig("pdl_conv1_fused_fwd", [P, P, P, P, P, I, P])
+    sig("pdl_fc_ce_fused", [P, P, P, P, P, P, P, P, I, P])
+    sig("pdl_fc_bwd_splits", [I])
+    sig("pdl_fc_bwd_scratch_floats", [I], LL)
+    sig("pdl_fc_bwd_pool3_fused", [P, P, P, P, P, P, P, P, P, I, P])
+    sig("pdl_bwd_blocks", [I])
+    sig("pdl_pool2_bwd_blocks", [I, I, I, I])
+    sig("pdl_pool2_bwd_dbias", [P, P, P, P, P, I, I, I, I, I, P])
+    sig("pdl_conv1_wgrad_fused", [P, P, P, P, P, P, P, I, P])
     # element-wise / pooling / linear / loss
     sig("pdl_relu_fwd", [P, P, LL, P])
     sig("pdl_relu_bwd", [P, P, P, LL, P])

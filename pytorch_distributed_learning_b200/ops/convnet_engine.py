@@ -144,9 +144,24 @@ class ConvNetEngine:
         shapes = [(N, 28, 28, 1, 32, 5, 5, 1, 1), (N, 13, 13, 32, 64, 3, 3, 1, 0), (N, 10, 10, 64, 128, 3, 3, 1, 0)]
         nbytes = max(self.L.pdl_conv2d_wgrad_scratch_bytes(*s) for s in shapes)
         b["scratch"] = torch.empty(int(nbytes), dtype=torch.uint8, device=dev)
+        from . import tc_conv
+
+        self.use_tc = tc_conv.enabled()
+        if self.use_tc:  # tensor-core path: packed weights, bias partials, split-K scratch
+            L = self.L
+            blocks = L.pdl_bwd_blocks(N)
+            pool2_blocks = L.pdl_pool2_bwd_blocks(N, 11, 11, 64)
+            wg = max(L.pdl_tc_wgrad_scratch_bytes(N, 13, 13, 32, 64, 3, 3, 0), L.pdl_tc_wgrad_scratch_bytes(N, 10, 10, 64, 128, 3, 3, 0))
+            b.update({
+                "p2f": e(9, 64, 32), "p2b": e(9, 32, 64), "p3f": e(9, 128, 64), "p3b": e(9, 64, 128), "wfp": e(10, 2048),
+                "fc_scratch": e(int(L.pdl_fc_bwd_scratch_floats(N))), "db3part": e(N, 128), "db2part": e(pool2_blocks, 64),
+                "c1part": e(blocks, 832), "wg_scratch": torch.empty(int(wg), dtype=torch.uint8, device=dev),
+                "err": tc_conv.error_flag(dev),
+            })
+            self.db2_blocks = pool2_blocks
         b["x"].zero_()
         b["y"].zero_()
-        entry = {"buf": b, "graph": None, "kernels": 0}
+        entry = {"buf": b, "graph": None, "kernels": 0, "tc": self.use_tc}
         # warm-up run outside capture (also validates every launch), then capture
         side = torch.cuda.Stream(device=dev)
         side.wait_stream(torch.cuda.current_stream(dev))
@@ -161,7 +176,45 @@ class ConvNetEngine:
         return entry
 
     def _record(self, b, N, stream_handle, reduce):
-        """Issue the kernels of one iteration on `stream_handle`; returns how many were launched."""
+        k = self._record_tc(b, N, stream_handle) if self.use_tc else self._record_simt(b, N, stream_handle)
+        # gradient averaging + SGD (one kernel; over NVLink when world > 1)
+        if reduce:
+            if self.ddp is not None:
+                self.backend.launch_bucket_kernel(self.bucket, self.world, self.ddp.algorithm, stream_handle, fused=True)
+            else:
+                self.arena.launch(stream_handle)
+            k += 1
+        return k
+
+    def _record_tc(self, b, N, stream_handle):
+        """Tensor-core path: 15 launches (tcgen05 conv2/conv3 fwd+dgrad+wgrad, fused CUDA-core kernels for the rest)."""
+        L, ok, st = self.L, NF._ok, ctypes.c_void_p(stream_handle)
+        w1, b1, w2, b2, w3, b3, wf, bf = self.params
+        gw1, gb1, gw2, gb2, gw3, gb3, gwf, gbf = self.g_views
+        err = _p(b["err"])
+        k = 0
+        ok(L.pdl_convnet_pack(_p(w2), _p(w3), _p(wf), _p(b["p2f"]), _p(b["p2b"]), _p(b["p3f"]), _p(b["p3b"]), _p(b["wfp"]), st), "weight pack"); k += 1
+        # forward: conv+bias+ReLU+pool fused per layer
+        ok(L.pdl_conv1_fused_fwd(_p(b["x"]), _p(w1), _p(b1), _p(b["a1"]), _p(b["i1"]), N, st), "conv1"); k += 1
+        ok(L.pdl_tc_conv2d_fwd(_p(b["a1"]), _p(b["p2f"]), _p(b2), _p(b["a2"]), _p(b["i2"]), N, 13, 13, 32, 64, 3, 3, 0, 1, 1, err, st), "conv2"); k += 1
+        ok(L.pdl_tc_conv2d_fwd(_p(b["a2"]), _p(b["p3f"]), _p(b3), _p(b["a3"]), _p(b["i3"]), N, 10, 10, 64, 128, 3, 3, 0, 1, 2, err, st), "conv3"); k += 1
+        ok(L.pdl_fc_ce_fused(_p(b["a3"]), _p(b["wfp"]), _p(bf), _p(b["y"]), _p(b["logits"]), _p(b["row_loss"]), _p(b["loss"]), _p(b["dlogits"]), N, st),
+           "fc1 + loss"); k += 1
+        # backward
+        ok(L.pdl_fc_bwd_pool3_fused(_p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
+                                    _p(b["db3part"]), N, st), "fc1 backward + pool3 backward"); k += 1
+        ok(L.pdl_tc_conv2d_wgrad(_p(b["a2"]), _p(b["dz3"]), _p(gw3), _p(gb3), _p(b["db3part"]), N, _p(b["wg_scratch"]), N, 10, 10, 64, 128, 3, 3, 0,
+                                 err, st), "conv3 wgrad"); k += 2
+        ok(L.pdl_tc_conv2d_dgrad(_p(b["dz3"]), _p(b["p3b"]), _p(b["da2"]), N, 10, 10, 64, 128, 3, 3, 0, err, st), "conv3 dgrad"); k += 1
+        ok(L.pdl_pool2_bwd_dbias(_p(b["da2"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 11, 11, 64, 1, st), "pool2 backward"); k += 1
+        ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
+                                 3, 3, 0, err, st), "conv2 wgrad"); k += 2
+        ok(L.pdl_tc_conv2d_dgrad(_p(b["dz2"]), _p(b["p2b"]), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 dgrad"); k += 1
+        ok(L.pdl_conv1_wgrad_fused(_p(b["x"]), _p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(gw1), _p(gb1), _p(b["c1part"]), N, st), "conv1 wgrad"); k += 1
+        return k
+
+    def _record_simt(self, b, N, stream_handle):
+        """Strict-fp32 CUDA-core path (used when TF32 convolutions are disabled)."""
         L, ok, st = self.L, NF._ok, ctypes.c_void_p(stream_handle)
         w1, b1, w2, b2, w3, b3, wf, bf = self.params
         gw1, gb1, gw2, gb2, gw3, gb3, gwf, gbf = self.g_views
@@ -188,13 +241,6 @@ class ConvNetEngine:
         ok(L.pdl_conv2d_dgrad_simt(_p(b["dz2"]), _p(w2), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 1, 0, st), "conv2 dgrad"); k += 1
         ok(L.pdl_maxpool_bwd(_p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(b["dz1"]), N, 26, 26, 32, 2, 2, 0, 1, st), "pool1 bwd"); k += 1
         ok(L.pdl_conv2d_wgrad_simt(_p(b["x"]), _p(b["dz1"]), _p(gw1), _p(gb1), _p(b["scratch"]), N, 28, 28, 1, 32, 5, 5, 1, 1, st), "conv1 wgrad"); k += 2
-        # gradient averaging + SGD (one kernel; over NVLink when world > 1)
-        if reduce:
-            if self.ddp is not None:
-                self.backend.launch_bucket_kernel(self.bucket, self.world, self.ddp.algorithm, stream_handle, fused=True)
-            else:
-                self.arena.launch(stream_handle)
-            k += 1
         return k
 
     # ------------------------------------------------------------------ stepping
@@ -206,18 +252,22 @@ class ConvNetEngine:
 
     def step(self, images, labels):
         N = images.shape[0]
-        entry = self.graphs.get(N)
+        from . import tc_conv
+
+        key = (N, tc_conv.enabled())
+        entry = self.graphs.get(key)
         if entry is None:
             if tuple(images.shape[1:]) != (1, 28, 28):
                 raise ValueError("ConvNet expects N x 1 x 28 x 28 inputs, got %s" % (tuple(images.shape),))
             self._refresh_hyper()
-            entry = self.graphs[N] = self._build(N)
+            entry = self.graphs[key] = self._build(N)
         b = entry["buf"]
         self._refresh_hyper()
         b["x"].view(N, 1, 28, 28).copy_(images, non_blocking=True)
         b["y"].copy_(labels, non_blocking=True)
         entry["graph"].replay()
         self.kernel_count = entry["kernels"]
+        self.last_key = key
         if self.ddp is not None:
             self.ddp._iteration += 1
         return b["loss"]
@@ -227,4 +277,4 @@ class ConvNetEngine:
 
     def logits(self, N):
         """Logits of the most recent step with batch size N (static buffer)."""
-        return self.graphs[N]["buf"]["logits"]
+        return self.graphs[(N, self.last_key[1])]["buf"]["logits"]

@@ -128,3 +128,36 @@ def test_tc_path_is_used_by_autograd_function():
     _tf32_close(y, yr)
     _tf32_close(x.grad, xr.grad)
     _tf32_close(w.grad, wr.grad)
+
+
+@pytest.mark.parametrize("batch", [100, 7])
+@pytest.mark.parametrize("opt_kw", [dict(lr=1e-2), dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)])
+def test_graphed_trainstep_tensor_core_path(batch, opt_kw):
+    """The flagship path: whole step in one CUDA graph with the tcgen05 conv kernels (TF32), against fp32 torch."""
+    import copy
+
+    import pytorch_distributed_learning_b200 as pdl
+    from test_gpu_engine import _reference_run
+
+    torch.manual_seed(0)
+    model = pdl.models.ConvNet().cuda()
+    state = copy.deepcopy(model.state_dict())
+    opt = pdl.optim.SGD(model.parameters(), **opt_kw)
+    step = pdl.TrainStep(model, pdl.nn.CrossEntropyLoss(), opt)
+    assert step.graphed
+    g = torch.Generator().manual_seed(1)
+    batches = [(torch.randn(batch, 1, 28, 28, generator=g).pin_memory(), torch.randint(0, 10, (batch,), generator=g).pin_memory()) for _ in range(5)]
+    losses = [step(x, y).item() for x, y in batches]
+    assert step.engine.use_tc and step.kernels_per_step() <= 16
+    tc_conv.check_errors(DEV)
+    torch.backends.cudnn.allow_tf32 = False
+    ref, ref_losses = _reference_run(state, batches, opt_kw)
+    torch.backends.cudnn.allow_tf32 = True
+    ref_tf32, _ = _reference_run(state, batches, opt_kw)  # the reference's DEFAULT precision (cuDNN TF32 convs)
+    torch.testing.assert_close(torch.tensor(losses), torch.tensor(ref_losses), rtol=3e-3, atol=3e-3)
+    # parity criterion: be as close to strict fp32 as torch's own TF32 convolutions are (see profiles/tf32_parity.md)
+    for (n, a), (_, b), (_, c) in zip(model.named_parameters(), ref.named_parameters(), ref_tf32.named_parameters()):
+        delta_ref = (b - state[n].cuda()).norm().item()
+        err_ours, err_torch = (a - b).norm().item(), (c - b).norm().item()
+        assert err_ours <= 2.5 * err_torch + 1e-2 * delta_ref + 1e-7, \
+            "%s: |ours - fp32| = %.3e, |torch TF32 - fp32| = %.3e, update norm %.3e" % (n, err_ours, err_torch, delta_ref)
