@@ -58,53 +58,60 @@ __global__ void __launch_bounds__(kThreads) pool2_bwd_dbias_kernel(const float* 
 __device__ unsigned int g_c1w_done = 0;
 
 // conv1 wgrad: gw1[c][r][s] = sum_{n,ph,pw} g * x[n][2ph+dy+r-1][2pw+dx+s-1],  g = (a1 > 0) ? da1 : 0,
-// (dy,dx) = argmax of the pool window.  gb1[c] = sum g.  Per image: image, g and argmax are staged in shared
-// memory with coalesced, independent loads; thread = (channel, tap group).  Partials per CTA, the last CTA
-// reduces them in CTA order.
-__global__ void __launch_bounds__(kThreads) conv1_wgrad_fused_kernel(const float* __restrict__ x, const float* __restrict__ da1,
-                                                                     const uint8_t* __restrict__ idx1, const float* __restrict__ a1,
-                                                                     float* __restrict__ gw1, float* __restrict__ gb1, float* __restrict__ partial,
-                                                                     int N, int imgs_per_cta) {
-  __shared__ float img[30][32];
-  __shared__ float sg[169 * 32];
-  __shared__ uint8_t sarg[169 * 32];
-  const int c = threadIdx.x % 32, tg = threadIdx.x / 32;
-  float acc[4] = {0.f, 0.f, 0.f, 0.f}, accb = 0.f;
+// (dy,dx) = argmax of the pool window.  gb1[c] = sum g.  One CTA (16 warps) per image at a time: image, g and
+// argmax are staged in shared memory with coalesced independent loads; lane = channel, warp = slice of the
+// 169 pooled pixels, all 25 taps accumulate in registers (index math amortised over 25 FMAs).  The 16 warps
+// are summed in shared memory in warp order, the CTA's row goes to `partial`, the last CTA adds the rows in
+// CTA order (deterministic).
+constexpr int kC1Threads = 512, kC1Warps = kC1Threads / 32;
+constexpr int kC1StageFloats = 30 * 32 + 169 * 32 + 169 * 32 / 4;  // img + g + argmax bytes
+__global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const float* __restrict__ x, const float* __restrict__ da1,
+                                                                       const uint8_t* __restrict__ idx1, const float* __restrict__ a1,
+                                                                       float* __restrict__ gw1, float* __restrict__ gb1,
+                                                                       float* __restrict__ partial, int N, int imgs_per_cta) {
+  extern __shared__ float c1_smem[];
+  float* img = c1_smem;          // [30][32]
+  float* sg = img + 30 * 32;     // [169][32]
+  uint8_t* sarg = reinterpret_cast<uint8_t*>(sg + 169 * 32);
+  float* red = c1_smem + kC1StageFloats;  // [16][832]
+  const int c = threadIdx.x % 32, wp = threadIdx.x / 32;
+  float acc[25], accb = 0.f;
+#pragma unroll
+  for (int t = 0; t < 25; ++t) acc[t] = 0.f;
   const int n_lo = blockIdx.x * imgs_per_cta, n_hi = min(N, n_lo + imgs_per_cta);
   for (int n = n_lo; n < n_hi; ++n) {
     __syncthreads();
-    for (int i = threadIdx.x; i < 30 * 32; i += kThreads) {
+    for (int i = threadIdx.x; i < 30 * 32; i += kC1Threads) {
       const int r = i / 32, cc = i % 32, h = r - 1, w = cc - 1;
-      img[r][cc] = (h >= 0 && h < 28 && w >= 0 && w < 28) ? x[(static_cast<long long>(n) * 28 + h) * 28 + w] : 0.f;
+      img[i] = (h >= 0 && h < 28 && w >= 0 && w < 28) ? x[(static_cast<long long>(n) * 28 + h) * 28 + w] : 0.f;
     }
     const long long base = static_cast<long long>(n) * 169 * 32;
-#pragma unroll 8
-    for (int i = threadIdx.x; i < 169 * 32; i += kThreads) {
+#pragma unroll 11
+    for (int i = threadIdx.x; i < 169 * 32; i += kC1Threads) {
       const float a = a1[base + i], d = da1[base + i];
       sg[i] = a > 0.f ? d : 0.f;
       sarg[i] = idx1[base + i];
     }
     __syncthreads();
-#pragma unroll 4
-    for (int pp = 0; pp < 169; ++pp) {
+    for (int pp = wp; pp < 169; pp += kC1Warps) {
       const float g = sg[pp * 32 + c];
       const int arg = sarg[pp * 32 + c];
-      const int h = 2 * (pp / 13) + (arg >> 1), w = 2 * (pp % 13) + (arg & 1);
-      if (tg == 0) accb += g;
+      const float* patch = img + (2 * (pp / 13) + (arg >> 1)) * 32 + 2 * (pp % 13) + (arg & 1);
+      accb += g;
 #pragma unroll
-      for (int k = 0; k < 4; ++k) {
-        const int t = tg + 8 * k;
-        if (t < 25) acc[k] = fmaf(g, img[h + t / 5][w + t % 5], acc[k]);
-      }
+      for (int t = 0; t < 25; ++t) acc[t] = fmaf(g, patch[(t / 5) * 32 + t % 5], acc[t]);
     }
   }
-  float* mine = partial + static_cast<long long>(blockIdx.x) * 832;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int t = tg + 8 * k;
-    if (t < 25) mine[c * 25 + t] = acc[k];
+  for (int t = 0; t < 25; ++t) red[wp * 832 + c * 25 + t] = acc[t];
+  red[wp * 832 + 800 + c] = accb;
+  __syncthreads();
+  for (int i = threadIdx.x; i < 832; i += kC1Threads) {
+    float s = 0.f;
+#pragma unroll
+    for (int w = 0; w < kC1Warps; ++w) s += red[w * 832 + i];
+    partial[static_cast<size_t>(blockIdx.x) * 832 + i] = s;
   }
-  if (tg == 0) mine[800 + c] = accb;
   __shared__ bool is_last;
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -114,27 +121,19 @@ __global__ void __launch_bounds__(kThreads) conv1_wgrad_fused_kernel(const float
   __syncthreads();
   if (is_last) {
     __threadfence();
-    // 4 outputs per thread, 8 partial rows per pass: 32 independent loads in flight (latency-bound otherwise)
-    float s[4] = {0.f, 0.f, 0.f, 0.f};
     const unsigned nb = gridDim.x;
-#pragma unroll 8
-    for (unsigned b = 0; b < nb; ++b) {
-#pragma unroll
-      for (int q = 0; q < 4; ++q) {
-        const int i = threadIdx.x + q * kThreads;
-        if (i < 832) s[q] += __ldcg(partial + static_cast<size_t>(b) * 832 + i);
-      }
-    }
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int i = threadIdx.x + q * kThreads;
-      if (i < 800) gw1[i] = s[q]; else if (i < 832) gb1[i - 800] = s[q];
+    for (int i = threadIdx.x; i < 832; i += kC1Threads) {
+      float s = 0.f;
+#pragma unroll 16
+      for (unsigned b = 0; b < nb; ++b) s += __ldcg(partial + static_cast<size_t>(b) * 832 + i);
+      if (i < 800) gw1[i] = s; else gb1[i - 800] = s;
     }
     if (threadIdx.x == 0) g_c1w_done = 0;
   }
 }
 
-int imgs_per_cta(int N) { int v = (N + 295) / 296; return v < 1 ? 1 : v; }
+int c1_imgs_per_cta(int N) { int v = (N + 295) / 296; return v < 1 ? 1 : v; }
+int c1_blocks(int N) { int per = c1_imgs_per_cta(N); return (N + per - 1) / per; }
 
 int pool_pix_per_cta(long long total_pix, int C) {
   const int G = kThreads / C;
@@ -146,7 +145,7 @@ int pool_pix_per_cta(long long total_pix, int C) {
 }  // namespace
 
 // Number of CTAs (= rows of `partial`) pdl_conv1_wgrad_fused uses for a batch of N images.
-PDL_API int pdl_bwd_blocks(int N) { int ipc = imgs_per_cta(N); return (N + ipc - 1) / ipc; }
+PDL_API int pdl_bwd_blocks(int N) { return c1_blocks(N); }
 
 // Number of CTAs (= rows of `dbpart`) pdl_pool2_bwd_dbias uses.
 PDL_API int pdl_pool2_bwd_blocks(int N, int H, int W, int C) {
@@ -174,8 +173,13 @@ PDL_API int pdl_pool2_bwd_dbias(const float* da, const uint8_t* idx, const float
 // partial must hold pdl_bwd_blocks(N) * 832 floats.
 PDL_API int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_t* idx1, const float* a1, float* gw1, float* gb1, float* partial,
                                   int N, cudaStream_t stream) {
-  const int ipc = imgs_per_cta(N), blocks = (N + ipc - 1) / ipc;
-  conv1_wgrad_fused_kernel<<<blocks, kThreads, 0, stream>>>(x, da1, idx1, a1, gw1, gb1, partial, N, ipc);
+  const int smem = (kC1StageFloats + kC1Warps * 832) * static_cast<int>(sizeof(float));
+  static bool configured = false;
+  if (!configured) {
+    PDL_CUDA_CHECK(cudaFuncSetAttribute(conv1_wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  conv1_wgrad_fused_kernel<<<c1_blocks(N), kC1Threads, smem, stream>>>(x, da1, idx1, a1, gw1, gb1, partial, N, c1_imgs_per_cta(N));
   PDL_LAUNCH_CHECK();
   return 0;
 }

@@ -97,6 +97,21 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {
   asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
 
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float* v) {
+  uint32_t* r = reinterpret_cast<uint32_t*>(v);
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]),
+                 "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+               : "r"(taddr)
+               : "memory");
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+template <int COLS>
+__device__ __forceinline__ void tmem_ld(uint32_t taddr, float* v) {
+  static_assert(COLS == 16 || COLS == 32, "TMEM load width");
+  if constexpr (COLS == 32) tmem_ld32(taddr, v); else tmem_ld16(taddr, v);
+}
+
 // ---- UMMA descriptors ----
 // Shared-memory operand descriptor, 128-byte swizzle.  `sbo`/`lbo` in bytes.
 //   K-major : rows of 128 B (32 tf32 along K), 8-row groups `sbo` bytes apart (1024 when rows are dense)

@@ -15,7 +15,8 @@
 namespace {
 
 constexpr int kStages = 4;
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;   // 4 control warps (TMA, MMA, TMEM alloc, spare) + 8 epilogue warps
+constexpr int kEpiWarps = 8;
 constexpr int A_BYTES = 128 * 128;  // 128 rows x 32 tf32
 
 enum Epi : int { EPI_STORE = 0, EPI_RELU_POOL = 1 };
@@ -37,6 +38,7 @@ struct EpiArgs {
   int relu;
   int pool_stride;
   int* error;
+  long long* trace;  // optional: clock64() of CTA 0 at pipeline milestones (profiling aid)
 };
 
 template <int N_GEMM>
@@ -46,7 +48,7 @@ struct Smem {
   static constexpr int STAGING_LD = N_GEMM + 4;
   static constexpr int STAGING_BYTES = 128 * STAGING_LD * 4;
   static constexpr int BAR_OFFSET = kStages * STAGE_BYTES + STAGING_BYTES;
-  static constexpr int TOTAL = BAR_OFFSET + 256 + 1024;  // + barriers + alignment slack
+  static constexpr int TOTAL = BAR_OFFSET + 128 + 512 + 512 + 1024;  // + barriers + bias row + pool table + alignment slack
 };
 
 template <int N_GEMM, int EPI>
@@ -62,23 +64,39 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   volatile int* failed = reinterpret_cast<volatile int*>(tmem_slot + 1);
+  float* sbias = reinterpret_cast<float*>(smem + SM::BAR_OFFSET + 128);       // N_GEMM floats
+  int* pool_row = reinterpret_cast<int*>(smem + SM::BAR_OFFSET + 128 + 512);   // <= 128 pooled pixels -> staging row
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
+#define PDL_TRACE(slot) do { if (e.trace && blockIdx.x == 0) e.trace[slot] = clock64(); } while (0)
+  if (threadIdx.x == 0) PDL_TRACE(0);
   constexpr uint32_t kTmemCols = (2 * N_GEMM <= 32) ? 32 : (2 * N_GEMM <= 64) ? 64 : (2 * N_GEMM <= 128) ? 128 : (2 * N_GEMM <= 256) ? 256 : 512;
 
   if (threadIdx.x == 0) {
     tc::prefetch_tmap(&tmA);
     tc::prefetch_tmap(&tmB);
     for (int i = 0; i < kStages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { tc::mbar_init(&tfull[i], 1); tc::mbar_init(&tempty[i], 4); }
+    for (int i = 0; i < 2; ++i) { tc::mbar_init(&tfull[i], 1); tc::mbar_init(&tempty[i], kEpiWarps); }
     *failed = 0;
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc(tmem_slot, kTmemCols);
+  // per-CTA constants of the epilogue, computed once: bias row, pooled pixel -> first staging row of its window
+  const int ps = e.pool_stride > 0 ? e.pool_stride : 1;
+  const int PH = (g.BH - 2) / ps + 1, PW = (g.BW - 2) / ps + 1;
+  if (threadIdx.x >= 128) {
+    const int t = threadIdx.x - 128;
+    if (t < N_GEMM) sbias[t] = e.bias ? e.bias[t] : 0.f;
+    if (EPI == EPI_RELU_POOL && t < g.BN * PH * PW) {
+      const int img = t / (PH * PW), pp = t % (PH * PW);
+      pool_row[t] = (img * g.BH + (pp / PW) * ps) * g.BW + (pp % PW) * ps;
+    }
+  }
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) PDL_TRACE(1);
 
   const int ksteps = g.R * g.S * g.kchunks;
   const int rows = g.BW * g.BH * g.BN;
@@ -89,20 +107,24 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (tc::elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < g.num_tiles && !*failed; tile += gridDim.x) {
+      bool ok = true;
+      for (int tile = blockIdx.x; tile < g.num_tiles && ok; tile += gridDim.x) {
         const int n0 = g.BN > 1 ? tile * g.BN : tile / g.tiles_per_img;
         const int h0 = g.BN > 1 ? 0 : (tile % g.tiles_per_img) * g.BH;
-        for (int ks = 0; ks < ksteps; ++ks) {
-          if (!tc::mbar_wait(&empty[stage], phase ^ 1)) { *failed = 1; break; }
-          const int tap = ks / g.kchunks, kc = ks % g.kchunks;
-          const int r = tap / g.S, s = tap % g.S;
-          uint8_t* a_dst = smem + stage * SM::STAGE_BYTES;
-          tc::mbar_expect_tx(&full[stage], stage_tx);
-          tc::tma_load_4d(a_dst, &tmA, &full[stage], kc * 32, g.a_w0 + g.tap_sign * s, h0 + g.a_h0 + g.tap_sign * r, n0);
-          tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, tap * N_GEMM);
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
-        }
+        int tap = 0;
+        for (int r = 0; r < g.R && ok; ++r)
+          for (int s = 0; s < g.S && ok; ++s, ++tap)
+            for (int kc = 0; kc < g.kchunks; ++kc) {
+              if (!tc::mbar_wait(&empty[stage], phase ^ 1)) { *failed = 1; ok = false; break; }
+              uint8_t* a_dst = smem + stage * SM::STAGE_BYTES;
+              tc::mbar_expect_tx(&full[stage], stage_tx);
+              tc::tma_load_4d(a_dst, &tmA, &full[stage], kc * 32, g.a_w0 + g.tap_sign * s, h0 + g.a_h0 + g.tap_sign * r, n0);
+              tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, tap * N_GEMM);
+              if (tile == blockIdx.x && tap == 0 && kc == 0) PDL_TRACE(2);
+              if (++stage == kStages) { stage = 0; phase ^= 1; }
+            }
       }
+      PDL_TRACE(3);
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
@@ -116,6 +138,8 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       for (int ks = 0; ks < ksteps; ++ks) {
         if (!tc::mbar_wait(&full[stage], phase)) { *failed = 1; break; }
         tc::tc_fence_after();
+        if (tile == blockIdx.x && ks == 0 && lane == 0) PDL_TRACE(4);
+        if (tile == blockIdx.x && ks == ksteps - 1 && lane == 0) PDL_TRACE(5);
         if (tc::elect_one()) {
           const uint32_t a_addr = tc::smem_u32(smem + stage * SM::STAGE_BYTES);
           const uint32_t b_addr = a_addr + A_BYTES;
@@ -133,30 +157,34 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue (128 threads, thread t owns accumulator row t) =====================
-    const int et = threadIdx.x - 128;
-    const int quarter = warp & 3;
+    // ===================== epilogue: 8 warps; warp pair (q, q+4) shares TMEM lane quarter q and splits the columns =====================
+    const int et = threadIdx.x - 128;           // 0..255
+    const int ew = warp - 4, quarter = ew & 3, half = ew >> 2;
+    const int row = quarter * 32 + lane;        // accumulator row = output pixel of the tile
+    constexpr int HALF = N_GEMM / 2;            // columns per warp
+    constexpr int CH = HALF < 32 ? HALF : 32;   // columns per TMEM load
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
       if (*failed || !tc::mbar_wait(&tfull[acc], acc_phase)) { *failed = 1; break; }
       tc::tc_fence_after();
+      if (tile == blockIdx.x && et == 0) PDL_TRACE(6);
       const int n0 = g.BN > 1 ? tile * g.BN : tile / g.tiles_per_img;
       const int h0 = g.BN > 1 ? 0 : (tile % g.tiles_per_img) * g.BH;
-      const uint32_t t_row = tmem_base + acc * N_GEMM + (static_cast<uint32_t>(quarter * 32) << 16);
-      const int bw = et % g.BW, t2 = et / g.BW, bh = t2 % g.BH, bn = t2 / g.BH;
-      const bool valid = et < rows && (n0 + bn) < g.Nimg && (h0 + bh) < g.Hout;
+      const uint32_t t_row = tmem_base + acc * N_GEMM + half * HALF + (static_cast<uint32_t>(quarter * 32) << 16);
       if (EPI == EPI_STORE) {
-        float* dst = e.out + ((static_cast<long long>(n0 + bn) * g.Hout + h0 + bh) * g.Wout + bw) * N_GEMM;
+        const int bw = row % g.BW, t2 = row / g.BW, bh = t2 % g.BH, bn = t2 / g.BH;
+        const bool valid = row < rows && (n0 + bn) < g.Nimg && (h0 + bh) < g.Hout;
+        float* dst = e.out + ((static_cast<long long>(n0 + bn) * g.Hout + h0 + bh) * g.Wout + bw) * N_GEMM + half * HALF;
 #pragma unroll 1
-        for (int c = 0; c < N_GEMM; c += 32) {
-          float v[32];
-          tc::tmem_ld32(t_row + c, v);
+        for (int c = 0; c < HALF; c += CH) {
+          float v[CH];
+          tc::tmem_ld<CH>(t_row + c, v);
           if (valid) {
 #pragma unroll
-            for (int j = 0; j < 32; j += 4) {
-              float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-              if (e.bias) { o.x += e.bias[c + j]; o.y += e.bias[c + j + 1]; o.z += e.bias[c + j + 2]; o.w += e.bias[c + j + 3]; }
+            for (int j = 0; j < CH; j += 4) {
+              const float4 bb = *reinterpret_cast<const float4*>(sbias + half * HALF + c + j);
+              float4 o = make_float4(v[j] + bb.x, v[j + 1] + bb.y, v[j + 2] + bb.z, v[j + 3] + bb.w);
               if (e.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
               *reinterpret_cast<float4*>(dst + c + j) = o;
             }
@@ -168,31 +196,31 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       } else {
         // bias + ReLU into the staging tile, then 2x2 max-pool (stride 1 or 2) with first-max argmax
 #pragma unroll 1
-        for (int c = 0; c < N_GEMM; c += 32) {
-          float v[32];
-          tc::tmem_ld32(t_row + c, v);
+        for (int c = 0; c < HALF; c += CH) {
+          float v[CH];
+          tc::tmem_ld<CH>(t_row + c, v);
+          if (tile == blockIdx.x && et == 0 && c == 0) PDL_TRACE(9);
 #pragma unroll
-          for (int j = 0; j < 32; j += 4) {
-            float4 o = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
-            if (e.bias) { o.x += e.bias[c + j]; o.y += e.bias[c + j + 1]; o.z += e.bias[c + j + 2]; o.w += e.bias[c + j + 3]; }
-            o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f);
-            *reinterpret_cast<float4*>(staging + et * SM::STAGING_LD + c + j) = o;
+          for (int j = 0; j < CH; j += 4) {
+            const float4 bb = *reinterpret_cast<const float4*>(sbias + half * HALF + c + j);
+            float4 o = make_float4(fmaxf(v[j] + bb.x, 0.f), fmaxf(v[j + 1] + bb.y, 0.f), fmaxf(v[j + 2] + bb.z, 0.f), fmaxf(v[j + 3] + bb.w, 0.f));
+            *reinterpret_cast<float4*>(staging + row * SM::STAGING_LD + half * HALF + c + j) = o;
           }
         }
+        if (tile == blockIdx.x && et == 0) PDL_TRACE(10);
         tc::tc_fence_before();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&tempty[acc]);  // TMEM buffer is free: the next tile's MMAs may start
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        const int ps = e.pool_stride;
-        const int PH = (g.BH - 2) / ps + 1, PW = (g.BW - 2) / ps + 1;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (tile == blockIdx.x && et == 0) PDL_TRACE(11);
         constexpr int C4 = N_GEMM / 4;
-        const int per_img = PH * PW * C4;
-        for (int o = et; o < g.BN * per_img; o += 128) {
-          const int img = o / per_img, rem = o % per_img;
-          const int pp = rem / C4, c4 = rem % C4;
-          const int ph = pp / PW, pw = pp % PW;
-          if (n0 + img >= g.Nimg) continue;
-          const float* base = staging + ((img * g.BH + ph * ps) * g.BW + pw * ps) * SM::STAGING_LD + c4 * 4;
+        const int c4 = et % C4;
+        const int npp = min(g.BN, g.Nimg - n0) * PH * PW;  // pooled pixels of this tile that belong to real images
+        float* out_base = e.out + static_cast<long long>(n0) * PH * PW * N_GEMM + c4 * 4;
+        uint8_t* idx_base = e.idx + static_cast<long long>(n0) * PH * PW * N_GEMM + c4 * 4;
+#pragma unroll 2
+        for (int pp = et / C4; pp < npp; pp += 256 / C4) {
+          const float* base = staging + pool_row[pp] * SM::STAGING_LD + c4 * 4;
           const float4 v00 = *reinterpret_cast<const float4*>(base);
           const float4 v01 = *reinterpret_cast<const float4*>(base + SM::STAGING_LD);
           const float4 v10 = *reinterpret_cast<const float4*>(base + g.BW * SM::STAGING_LD);
@@ -208,19 +236,21 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           PDL_POOL_STEP(v10, 2)
           PDL_POOL_STEP(v11, 3)
 #undef PDL_POOL_STEP
-          const long long oidx = (static_cast<long long>(n0 + img) * PH * PW + pp) * N_GEMM + c4 * 4;
           best = make_float4(round_tf32(best.x), round_tf32(best.y), round_tf32(best.z), round_tf32(best.w));  // next layer's MMA operand
-          *reinterpret_cast<float4*>(e.out + oidx) = best;
-          *reinterpret_cast<uchar4*>(e.idx + oidx) = arg;
+          *reinterpret_cast<float4*>(out_base + static_cast<long long>(pp) * N_GEMM) = best;
+          *reinterpret_cast<uchar4*>(idx_base + static_cast<long long>(pp) * N_GEMM) = arg;
         }
-        asm volatile("bar.sync 1, 128;" ::: "memory");  // staging may be overwritten by the next tile
+        if (tile == blockIdx.x && et == 0) PDL_TRACE(12);
+        asm volatile("bar.sync 1, 256;" ::: "memory");  // staging may be overwritten by the next tile
       }
+      if (tile == blockIdx.x && et == 0) PDL_TRACE(7);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   }
 
   tc::tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) PDL_TRACE(8);
   if (warp == 2) tc::tmem_dealloc(tmem_base, kTmemCols);
   if (threadIdx.x == 0 && *failed && e.error) *e.error = 1;
 }
@@ -318,6 +348,10 @@ __global__ void pack_weights_kernel(const float* __restrict__ w, float* __restri
 
 }  // namespace
 
+static long long* g_trace = nullptr;
+// Profiling aid: device buffer of >= 16 int64 that CTA 0 of the next conv launches fills with clock64() milestones.
+PDL_API void pdl_tc_set_trace(long long* buf) { g_trace = buf; }
+
 // 1 if the tensor-core forward path covers this shape (stride 1, Cin % 32 == 0, Cout in {32,64,128}).
 PDL_API int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool) {
   if (stride != 1 || Cin % 32 || !(Cout == 32 || Cout == 64 || Cout == 128)) return 0;
@@ -346,7 +380,7 @@ PDL_API int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float
   CUtensorMap ta, tb;
   if (int rc = make_act_map(&ta, x, N, H, W, Cin, g.BW, g.BH, g.BN)) return rc;
   if (int rc = make_weight_map(&tb, packed_w, KH * KW * Cout, Cin, Cout)) return rc;
-  EpiArgs e{y, idx, bias, relu, pool_stride, error_flag};
+  EpiArgs e{y, idx, bias, relu, pool_stride, error_flag, g_trace};
   return pool_stride > 0 ? dispatch_n<EPI_RELU_POOL>(Cout, ta, tb, g, e, stream) : dispatch_n<EPI_STORE>(Cout, ta, tb, g, e, stream);
 }
 
@@ -363,6 +397,6 @@ PDL_API int pdl_tc_conv2d_dgrad(const float* dy, const float* packed_w_bwd, floa
   CUtensorMap ta, tb;
   if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
   if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, Cin)) return rc;
-  EpiArgs e{dx, nullptr, nullptr, 0, 0, error_flag};
+  EpiArgs e{dx, nullptr, nullptr, 0, 0, error_flag, g_trace};
   return dispatch_n<EPI_STORE>(Cin, ta, tb, g, e, stream);
 }

@@ -220,7 +220,8 @@ bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KW, int pad, WgGeom
   int bh = 64 / bw;  // 64-pixel K stages keep several stages in flight
   if (bw * bh != 64) return false;
   g->BW = bw; g->BH = bh; g->strips = (P + bh - 1) / bh; g->units = N * g->strips;
-  int splits = g->units < 16 ? g->units : (g->units <= 2048 ? 16 : 48);
+  // K split: enough CTAs to occupy the chip (grid = KH x splits), few enough that the partial sums stay cheap
+  int splits = g->units < 48 ? g->units : 48;
   g->units_per_cta = (g->units + splits - 1) / splits;
   g->S = KW; g->pad = pad;
   g->layout_type = env_int("PDL_WG_LT", 1);   // SWIZZLE_128B_BASE32B
