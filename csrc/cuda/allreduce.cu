@@ -80,9 +80,11 @@ __device__ __forceinline__ void mc_st_f4(float* base, long long i, float4 v) {
 __device__ __forceinline__ float4 add4(float4 a, float4 b) { return make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w); }
 __device__ __forceinline__ float4 scale4(float4 a, float s) { return make_float4(a.x * s, a.y * s, a.z * s, a.w * s); }
 
-// Tell `dst` ranks "block `blk` of rank `p.rank` reached value v"; all prior writes of the CTA are published.
+// Tell `dst` ranks "block `blk` of rank `p.rank` reached value v".  bar.sync orders every thread's earlier
+// memory operations before the signalling thread's st.release.sys, and release is cumulative in the PTX
+// memory model, so the CTA's prior (local and remote) writes are visible system-wide to whoever acquires
+// the flag.  (No per-thread fence.sc.sys: 512 of those per barrier cost microseconds on NVLink.)
 __device__ __forceinline__ void signal_peers(const ARParams& p, int blk, uint32_t v, int only = -1) {
-  __threadfence_system();
   __syncthreads();
   int t = threadIdx.x;
   if (t < p.world && t != p.rank && (only < 0 || t == only)) st_release_sys(p.pad[t] + flag_index(p.channel, blk, p.rank), v);
@@ -92,9 +94,14 @@ __device__ __forceinline__ void wait_peers(const ARParams& p, int blk, uint32_t 
   int t = threadIdx.x;
   if (t < p.world && t != p.rank && (only < 0 || t == only)) {
     const uint32_t* f = p.pad[p.rank] + flag_index(p.channel, blk, t);
-    unsigned long long t0 = globaltimer_ns();
+    unsigned long long t0 = 0;
+    uint32_t polls = 0;
     while (static_cast<int32_t>(ld_acquire_sys(f) - v) < 0) {
-      if (globaltimer_ns() - t0 > p.timeout_ns) { p.state->error = 1; break; }
+      if ((++polls & 1023u) == 0) {  // consult the clock rarely: the poll itself is the hot path
+        const unsigned long long now = globaltimer_ns();
+        if (t0 == 0) t0 = now;
+        else if (now - t0 > p.timeout_ns) { p.state->error = 1; break; }
+      }
     }
   }
   __syncthreads();
@@ -131,6 +138,25 @@ __device__ __forceinline__ void retire(const ARParams& p, int nblocks, uint32_t 
 
 enum Algo : int { ONESHOT = 0, TWOSHOT = 1, RING = 2, NVLS = 3 };
 
+// NVLink round trips are ~2-3 us: a thread must have several independent peer loads in flight.  The loads are
+// volatile asm (program order is kept), so every load of a batch is issued BEFORE the first dependent store.
+template <int U, typename LoadF, typename UseF>
+__device__ __forceinline__ void batched(long long lo, long long hi, LoadF load, UseF use) {
+  for (long long base = lo + threadIdx.x; base < hi; base += static_cast<long long>(kThreads) * U) {
+    float4 v[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = base + static_cast<long long>(u) * kThreads;
+      if (i < hi) v[u] = load(i);
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const long long i = base + static_cast<long long>(u) * kThreads;
+      if (i < hi) use(i, v[u]);
+    }
+  }
+}
+
 template <int kAlgo, bool kSgd>
 __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
   const int W = p.world, r = p.rank, tid = threadIdx.x;
@@ -142,28 +168,33 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
 
   if (W == 1) {
     long long per = (p.n4 + nblocks - 1) / nblocks, lo = per * blk, hi = min(p.n4, lo + per);
-    for (long long i = lo + tid; i < hi; i += kThreads) {
-      float4 v = scale4(reinterpret_cast<const float4*>(p.in[0])[i], inv);
-      reinterpret_cast<float4*>(p.out[0])[i] = v;
-      finish_element<kSgd>(p, i, v, h, has_mom);
-    }
+    batched<4>(lo, hi, [&](long long i) { return scale4(reinterpret_cast<const float4*>(p.in[0])[i], inv); },
+               [&](long long i, float4 v) {
+                 reinterpret_cast<float4*>(p.out[0])[i] = v;
+                 finish_element<kSgd>(p, i, v, h, has_mom);
+               });
     retire(p, nblocks, 0, kSgd);
     return;
   }
+
+  auto sum_peers = [&](long long i) {  // fixed rank order 0..W-1: every rank computes the same bits
+    float4 acc = ld_f4(p.in[0], i);
+#pragma unroll
+    for (int q = 1; q < kMaxWorld; ++q)
+      if (q < W) acc = add4(acc, ld_f4(p.in[q], i));
+    return scale4(acc, inv);
+  };
+  auto sgd_use = [&](long long i, float4 v) { finish_element<kSgd>(p, i, v, h, has_mom); };
 
   if (kAlgo == ONESHOT) {
     long long per = (p.n4 + nblocks - 1) / nblocks, lo = per * blk, hi = min(p.n4, lo + per);
     signal_peers(p, blk, e + 1);
     wait_peers(p, blk, e + 1);
-    for (long long i = lo + tid; i < hi; i += kThreads) {
-      float4 acc = ld_f4(p.in[0], i);
-#pragma unroll
-      for (int q = 1; q < kMaxWorld; ++q)
-        if (q < W) acc = add4(acc, ld_f4(p.in[q], i));
-      acc = scale4(acc, inv);
+    auto use = [&](long long i, float4 acc) {
       reinterpret_cast<float4*>(p.out[r])[i] = acc;
       finish_element<kSgd>(p, i, acc, h, has_mom);
-    }
+    };
+    if (W <= 4) batched<4>(lo, hi, sum_peers, use); else batched<2>(lo, hi, sum_peers, use);
     signal_peers(p, blk, e + 2);  // "I no longer read your bucket"
     wait_peers(p, blk, e + 2);
     retire(p, nblocks, 2, kSgd);
@@ -179,27 +210,21 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
   if (kAlgo == TWOSHOT || kAlgo == NVLS) {
     signal_peers(p, blk, e + 1);
     wait_peers(p, blk, e + 1);
-    for (long long i = sub_lo(r) + tid; i < sub_hi(r); i += kThreads) {
-      float4 acc;
-      if (kAlgo == NVLS) {
-        acc = scale4(mc_ld_reduce_f4(p.mc_in, i), inv);
-        mc_st_f4(p.mc_out, i, acc);
-      } else {
-        acc = ld_f4(p.in[0], i);
-#pragma unroll
-        for (int q = 1; q < kMaxWorld; ++q)
-          if (q < W) acc = add4(acc, ld_f4(p.in[q], i));
-        acc = scale4(acc, inv);
+    if (kAlgo == NVLS) {
+      batched<4>(sub_lo(r), sub_hi(r), [&](long long i) { return scale4(mc_ld_reduce_f4(p.mc_in, i), inv); },
+                 [&](long long i, float4 acc) { mc_st_f4(p.mc_out, i, acc); });
+    } else {
+      auto push = [&](long long i, float4 acc) {
 #pragma unroll
         for (int q = 0; q < kMaxWorld; ++q)
           if (q < W) st_f4(p.out[q], i, acc);
-      }
+      };
+      if (W <= 4) batched<4>(sub_lo(r), sub_hi(r), sum_peers, push); else batched<2>(sub_lo(r), sub_hi(r), sum_peers, push);
     }
     signal_peers(p, blk, e + 2);  // my slice is in everyone's `out`; I am done reading `in`
     wait_peers(p, blk, e + 2);
     if (kSgd) {
-      for (int s = 0; s < W; ++s)
-        for (long long i = sub_lo(s) + tid; i < sub_hi(s); i += kThreads) finish_element<kSgd>(p, i, ld_f4(p.out[r], i), h, has_mom);
+      for (int s = 0; s < W; ++s) batched<4>(sub_lo(s), sub_hi(s), [&](long long i) { return ld_f4(p.out[r], i); }, sgd_use);
     }
     retire(p, nblocks, 2, kSgd);
     return;
@@ -210,36 +235,37 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
     // reduce-scatter: step s sends the running sum of slice (r-s) to the next rank's staging buffer
     for (int s = 0; s < W - 1; ++s) {
       int idx = ((r - s) % W + W) % W;
-      for (long long i = sub_lo(idx) + tid; i < sub_hi(idx); i += kThreads) {
-        float4 v = ld_f4(p.in[r], i);
-        if (s > 0) v = add4(ld_f4(p.ring[r], i), v);
-        st_f4(p.ring[next], i, v);
-      }
+      batched<4>(sub_lo(idx), sub_hi(idx),
+                 [&](long long i) {
+                   float4 v = ld_f4(p.in[r], i);
+                   if (s > 0) v = add4(ld_f4(p.ring[r], i), v);
+                   return v;
+                 },
+                 [&](long long i, float4 v) { st_f4(p.ring[next], i, v); });
       signal_peers(p, blk, e + 1 + s, next);
       wait_peers(p, blk, e + 1 + s, prev);
     }
     // slice (r+1) is now complete here: average it, keep it, start the all-gather
     {
       int idx = (r + 1) % W;
-      for (long long i = sub_lo(idx) + tid; i < sub_hi(idx); i += kThreads) {
-        float4 v = scale4(add4(ld_f4(p.ring[r], i), ld_f4(p.in[r], i)), inv);
-        st_f4(p.out[r], i, v);
-        st_f4(p.out[next], i, v);
-      }
+      batched<4>(sub_lo(idx), sub_hi(idx), [&](long long i) { return scale4(add4(ld_f4(p.ring[r], i), ld_f4(p.in[r], i)), inv); },
+                 [&](long long i, float4 v) {
+                   st_f4(p.out[r], i, v);
+                   st_f4(p.out[next], i, v);
+                 });
       signal_peers(p, blk, e + W, next);
     }
     for (int t = 1; t < W - 1; ++t) {
       wait_peers(p, blk, e + W + t - 1, prev);
       int idx = ((r + 1 - t) % W + W) % W;
-      for (long long i = sub_lo(idx) + tid; i < sub_hi(idx); i += kThreads) st_f4(p.out[next], i, ld_f4(p.out[r], i));
+      batched<4>(sub_lo(idx), sub_hi(idx), [&](long long i) { return ld_f4(p.out[r], i); }, [&](long long i, float4 v) { st_f4(p.out[next], i, v); });
       signal_peers(p, blk, e + W + t, next);
     }
     wait_peers(p, blk, e + 2 * W - 2, prev);
     signal_peers(p, blk, e + 2 * W - 1);  // full barrier: staging buffers may be reused
     wait_peers(p, blk, e + 2 * W - 1);
     if (kSgd) {
-      for (int s = 0; s < W; ++s)
-        for (long long i = sub_lo(s) + tid; i < sub_hi(s); i += kThreads) finish_element<kSgd>(p, i, ld_f4(p.out[r], i), h, has_mom);
+      for (int s = 0; s < W; ++s) batched<4>(sub_lo(s), sub_hi(s), [&](long long i) { return ld_f4(p.out[r], i); }, sgd_use);
     }
     retire(p, nblocks, 2 * W - 1, kSgd);
     return;
@@ -326,10 +352,10 @@ PDL_API int pdl_sgd_hyper_bytes() { return static_cast<int>(sizeof(SgdHyper)); }
 // Number of CTAs for a bucket of n4 float4: enough loads in flight to cover NVLink latency, few
 // enough that the flag traffic stays negligible.  Must be a pure function of (n4, world).
 PDL_API int pdl_allreduce_blocks(long long n4, int world, int algo) {
-  long long per_block = 2048;  // float4 per CTA (4 per thread)
+  long long per_block = 1024;  // float4 per CTA: two per thread, all of a thread's peer loads in flight at once
   long long b = (n4 + per_block - 1) / per_block;
   if (b < 1) b = 1;
-  int cap = (algo == ONESHOT) ? 32 : kMaxBlocks;
+  int cap = kMaxBlocks;
   if (b > cap) b = cap;
   (void)world;
   return static_cast<int>(b);

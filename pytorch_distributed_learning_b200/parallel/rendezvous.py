@@ -71,7 +71,35 @@ def parse(init_method, rank=-1, world_size=-1):
     return host, port, rank, world_size
 
 
+_agent_rendezvous_count = 0
+
+
+def _port_via_agent_store(host, port, rank, world_size, timeout):
+    """Under ``python -m torch.distributed.run`` the elastic agent itself listens on MASTER_PORT
+    (TORCHELASTIC_USE_AGENT_STORE=True), so rank 0 cannot host this package's store there.  The agent's
+    store is used for exactly one thing: rank 0 starts our C++ store on an ephemeral port and publishes
+    the number; everything else (handles, barriers, endpoints) goes through our own store."""
+    global _agent_rendezvous_count
+    from datetime import timedelta
+
+    from torch.distributed import TCPStore as AgentStore
+
+    agent = AgentStore(host, port, world_size, is_master=False, timeout=timedelta(seconds=min(timeout, 600.0)))
+    key = "pdl_b200/store_port/%s/%d" % (os.environ.get("TORCHELASTIC_RESTART_COUNT", "0"), _agent_rendezvous_count)
+    _agent_rendezvous_count += 1
+    if rank == 0:
+        store = TCPStore(host, 0, world_size, is_master=True, timeout=timeout)
+        agent.set(key, str(store.port))
+        return store
+    real_port = int(agent.get(key).decode())
+    return TCPStore(host, real_port, world_size, is_master=False, timeout=timeout)
+
+
 def rendezvous(init_method, rank=-1, world_size=-1, timeout=DEFAULT_TIMEOUT_S):
     host, port, rank, world_size = parse(init_method, rank, world_size)
-    store = TCPStore(host, port, world_size, is_master=(rank == 0), timeout=timeout)
+    scheme = urlparse(init_method or "env://").scheme
+    if scheme == "env" and os.environ.get("TORCHELASTIC_USE_AGENT_STORE", "") == "True":
+        store = _port_via_agent_store(host, port, rank, world_size, timeout)
+    else:
+        store = TCPStore(host, port, world_size, is_master=(rank == 0), timeout=timeout)
     return store, rank, world_size
