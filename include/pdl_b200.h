@@ -1,0 +1,123 @@
+/* C ABI of libpdl_cuda.so -- sm_100a kernels and the symmetric-memory runtime.
+ *
+ * Every launcher enqueues on the given stream and returns 0 or an error code (message via
+ * pdl_last_error()).  Activations are NHWC fp32; convolution weights are [Cout][Cin][KH][KW].
+ * "reference:" cites the line of Jackxiini/Pytorch-distributed-learning whose behaviour the
+ * entry point provides (the reference itself ships no native code; it reaches cuDNN/cuBLAS/NCCL
+ * through PyTorch).
+ */
+#ifndef PDL_B200_H_
+#define PDL_B200_H_
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+const char* pdl_last_error(void);
+int pdl_cuda_device_count(void);
+
+/* ---- symmetric memory: same-size VMM allocation on every rank, peer-mapped (+ NVSwitch multicast) ----
+ * reference: the NCCL communicator behind init_process_group(backend='nccl') (launch_dist.py:49).
+ * Phases are separated by caller-side barriers: begin -> exchange -> bind_multicast. */
+int pdl_symm_multicast_supported(int device);
+int pdl_symm_begin(int rank, int world, int device, uint64_t bytes, const char* uds_prefix, int want_multicast, void** out);
+int pdl_symm_exchange(void* seg);
+int pdl_symm_multicast_ready(void* seg);
+int pdl_symm_bind_multicast(void* seg, int all_ok);
+uint64_t pdl_symm_bytes(void* seg);
+void* pdl_symm_ptr(void* seg, int rank); /* address through which THIS process reaches rank's copy */
+void* pdl_symm_mc_ptr(void* seg);        /* multicast alias or NULL */
+void** pdl_symm_dev_ptrs(void* seg);
+int pdl_symm_destroy(void* seg);
+
+/* ---- gradient-bucket allreduce fused with 1/W averaging and SGD (reference: loss.backward() ->
+ *      DDP bucket allreduce -> optimizer.step(), launch_dist.py:91-92) ----
+ * algo: 0 one-shot, 1 two-shot, 2 ring, 3 NVLS multimem.  in/out/ring/pad: `world` peer-mapped pointers.
+ * param/mom/hyper non-NULL => the SGD update (weight decay, momentum, nesterov) runs in the same kernel. */
+int pdl_comm_state_bytes(void);
+int pdl_signal_pad_bytes(void);
+int pdl_comm_max_blocks(void);
+int pdl_comm_max_channels(void);
+int pdl_sgd_hyper_bytes(void);
+int pdl_allreduce_blocks(long long n4, int world, int algo);
+int pdl_allreduce_launch(int algo, int rank, int world, int channel, long long n4, const float* const* in, float* const* out,
+                         float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, float* param, float* mom, void* hyper,
+                         void* state, int blocks, double scale, double timeout_s, cudaStream_t stream);
+/* all `world` ranks as one cooperative launch on one GPU (tests) */
+int pdl_allreduce_emulated(int algo, int world, long long n4, const float* const* in, float* const* out, float* const* ring,
+                           uint32_t* const* pad, float* const* param, float* const* mom, void* const* hyper, void* const* state, int blocks,
+                           cudaStream_t stream);
+/* broadcast (root >= 0) / allgather (root < 0) by pulling from peers' staging buffers (reference: DDP
+ * constructor broadcast + per-forward buffer broadcast, launch_dist.py:61, example_launch.py:29) */
+int pdl_pull_launch(int rank, int world, int channel, int root, long long n16, const void* const* src, void* dst, uint32_t* const* pad,
+                    void* state, int blocks, double timeout_s, cudaStream_t stream);
+
+/* ---- stand-alone SGD (reference: torch.optim.SGD at launch_dist.py:59, example_launch.py:64-70) ---- */
+int pdl_sgd_chunk_elems(void);
+int pdl_multi_tensor_sgd(const void* table, const int* chunk_prefix, int num_tensors, int total_chunks, float lr, float momentum,
+                         float dampening, float weight_decay, int nesterov, int first_step, cudaStream_t stream);
+
+/* ---- convolution, CUDA cores, strict fp32, any shape (reference: nn.Conv2d at launch_dist.py:15-25) ---- */
+int pdl_conv2d_fwd_simt(const float* x, const float* w, const float* bias, float* y, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                        int stride, int pad, int relu, cudaStream_t stream);
+int pdl_conv2d_dgrad_simt(const float* dy, const float* w, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad,
+                          cudaStream_t stream);
+long long pdl_conv2d_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+int pdl_conv2d_wgrad_simt(const float* x, const float* dy, float* dw, float* db, float* scratch, int N, int H, int W, int Cin, int Cout, int KH,
+                          int KW, int stride, int pad, cudaStream_t stream);
+
+/* ---- convolution, tcgen05 tensor cores (TF32 in, fp32 accumulate in TMEM), TMA-fed (same reference lines) ---- */
+int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool);
+int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed_bwd, int Cout, int Cin, int taps, cudaStream_t stream);
+/* pool_stride 0: y = conv+bias(+relu); 1|2: fused ReLU + 2x2 max-pool, y/idx are the pooled output and argmax */
+int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin, int Cout,
+                      int KH, int KW, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream);
+int pdl_tc_conv2d_dgrad(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
+                        int* error_flag, cudaStream_t stream);
+int pdl_tc_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+long long pdl_tc_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad);
+int pdl_tc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch, int N,
+                        int H, int W, int Cin, int Cout, int KH, int KW, int pad, int* error_flag, cudaStream_t stream);
+void pdl_tc_set_trace(long long* buf); /* profiling aid: clock64() milestones of CTA 0 */
+
+/* ---- fused ConvNet kernels (reference: ConvNet.forward launch_dist.py:35-41 and its autograd) ---- */
+int pdl_convnet_pack(const float* w2, const float* w3, const float* wf, float* p2f, float* p2b, float* p3f, float* p3b, float* wfp,
+                     cudaStream_t stream);
+int pdl_conv1_fused_fwd(const float* x, const float* w, const float* bias, float* a1, uint8_t* idx1, int N, cudaStream_t stream);
+int pdl_fc_ce_fused(const float* a3, const float* wfp, const float* bf, const long long* labels, float* logits, float* row_loss, float* loss,
+                    float* dlogits, int N, cudaStream_t stream);
+int pdl_fc_bwd_splits(int N);
+long long pdl_fc_bwd_scratch_floats(int N);
+int pdl_fc_bwd_pool3_fused(const float* a3, const uint8_t* idx3, const float* dlogits, const float* wfp, float* gwf, float* gbf, float* wpart,
+                           float* dz3, float* db3part, int N, cudaStream_t stream);
+int pdl_bwd_blocks(int N);
+int pdl_pool2_bwd_blocks(int N, int H, int W, int C);
+int pdl_pool2_bwd_dbias(const float* da, const uint8_t* idx, const float* pooled, float* dz, float* dbpart, int N, int H, int W, int C,
+                        int stride, cudaStream_t stream);
+int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_t* idx1, const float* a1, float* gw1, float* gb1, float* partial, int N,
+                          cudaStream_t stream);
+
+/* ---- element-wise / pooling / linear / loss (reference: nn.ReLU, nn.MaxPool2d, nn.Linear,
+ *      nn.CrossEntropyLoss at launch_dist.py:13-32,58; ResNet add+ReLU / avgpool at example_launch.py:26) ---- */
+int pdl_relu_fwd(const float* x, float* y, long long n, cudaStream_t stream);
+int pdl_relu_bwd(const float* y, const float* dy, float* dx, long long n, cudaStream_t stream);
+int pdl_add_relu_fwd(const float* a, const float* b, float* y, long long n, cudaStream_t stream);
+int pdl_maxpool_fwd(const float* x, float* y, uint8_t* idx, int N, int H, int W, int C, int k, int stride, int pad, cudaStream_t stream);
+int pdl_maxpool_bwd(const float* dy, const uint8_t* idx, const float* pooled, float* dx, int N, int H, int W, int C, int k, int stride, int pad,
+                    int fuse_relu, cudaStream_t stream);
+int pdl_global_avgpool_fwd(const float* x, float* y, int N, int HW, int C, cudaStream_t stream);
+int pdl_global_avgpool_bwd(const float* dy, float* dx, int N, int HW, int C, cudaStream_t stream);
+int pdl_permute_nhwc_nchw(const float* x, float* y, int N, int HW, int C, int to_nchw, cudaStream_t stream);
+int pdl_linear_fwd(const float* x, const float* w, const float* b, float* y, int M, int N, int K, cudaStream_t stream);
+int pdl_linear_dgrad(const float* dy, const float* w, float* dx, int M, int N, int K, cudaStream_t stream);
+int pdl_linear_wgrad(const float* x, const float* dy, float* dw, float* db, int M, int N, int K, cudaStream_t stream);
+int pdl_cross_entropy(const float* logits, const long long* target, int N, int C, float* row_loss, float* loss, float* dlogits,
+                      const float* grad_scale, cudaStream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PDL_B200_H_ */
