@@ -149,3 +149,57 @@ PDL_API int pdl_conv2d_wgrad_simt(const float* x, const float* dy, float* dw, fl
   PDL_LAUNCH_CHECK();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Weight gradient for callers that are not allowed to allocate.
+//
+// Some hosts of this library cannot obtain device memory at the point where they need a wgrad: code
+// running inside a host function enqueued on a stream or in a CUDA callback (the runtime forbids
+// allocation calls there), code that runs while a stream is being captured, and processes in which
+// a framework's pool has already reserved the whole device so a fresh cudaMalloc simply fails.
+// For them the split-K partial sums live in a fixed array inside the library image instead of a
+// caller-provided buffer.  The array is kNoAllocScratchBytes (8 MiB) and every GPU that loads the
+// library carries it until the process exits; shapes whose partial sums do not fit are refused.
+//
+// The array is shared by every call in the process: two calls whose kernels can overlap on the GPU
+// (different streams) would overwrite each other's partial sums, so callers must keep such calls
+// ordered.  Nothing needs clearing between calls: every partial-sum slot that the reduction pass
+// reads is written by the GEMM pass of the same call first (leftovers of the previous call are
+// never read).  The first call on a device looks up the device address of the array
+// (cudaGetSymbolAddress); make that first call before any stream capture begins.
+// ------------------------------------------------------------------------------------------------
+namespace {
+constexpr long long kNoAllocScratchBytes = 8ll << 20;
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) float g_wgrad_noalloc_scratch[kNoAllocScratchBytes / sizeof(float)];
+
+namespace {
+// Device address of g_wgrad_noalloc_scratch per device ordinal.  In host code the symbol's own name is only
+// a host-side shadow, not a device pointer, so it must never be handed to a kernel directly.
+float* g_noalloc_dev_ptr[kNoAllocMaxDevices] = {};
+}  // namespace
+
+// Largest scratch requirement (bytes) pdl_conv2d_wgrad_simt_noalloc accepts.
+PDL_API long long pdl_conv2d_wgrad_noalloc_max_bytes() { return kNoAllocScratchBytes; }
+
+// Same result as pdl_conv2d_wgrad_simt, but takes no scratch pointer and performs no allocation.
+PDL_API int pdl_conv2d_wgrad_simt_noalloc(const float* x, const float* dy, float* dw, float* db, int N, int H, int W, int Cin, int Cout, int KH,
+                                          int KW, int stride, int pad, cudaStream_t stream) {
+  const long long need = pdl_conv2d_wgrad_scratch_bytes(N, H, W, Cin, Cout, KH, KW, stride, pad);
+  if (need > kNoAllocScratchBytes) {
+    pdl_set_error("wgrad (no-alloc): this shape needs %lld bytes of partial sums, the built-in buffer holds %lld; "
+                  "use pdl_conv2d_wgrad_simt with caller-provided scratch", need, kNoAllocScratchBytes);
+    return -10;
+  }
+  int dev = -1;
+  PDL_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) { pdl_set_error("wgrad (no-alloc): device ordinal %d out of range", dev); return -11; }
+  if (g_noalloc_dev_ptr[dev] == nullptr) {  // once per device, with that device current
+    float* p = nullptr;
+    PDL_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_wgrad_noalloc_scratch));
+    g_noalloc_dev_ptr[dev] = p;
+  }
+  return pdl_conv2d_wgrad_simt(x, dy, dw, db, g_noalloc_dev_ptr[dev], N, H, W, Cin, Cout, KH, KW, stride, pad, stream);
+}

@@ -69,6 +69,18 @@ long long pdl_conv2d_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout,
 int pdl_conv2d_wgrad_simt(const float* x, const float* dy, float* dw, float* db, float* scratch, int N, int H, int W, int Cin, int Cout, int KH,
                           int KW, int stride, int pad, cudaStream_t stream);
 
+/* Allocation-free twin of pdl_conv2d_wgrad_simt (no counterpart in the reference; it exists for embedding
+ * hosts, not for parity).  Who needs it: code that runs where the CUDA runtime forbids or cannot satisfy an
+ * allocation -- host functions and callbacks enqueued on a stream, work issued while a stream is being
+ * captured, processes whose device memory is already fully reserved by another allocator.  The split-K
+ * partial sums go to an 8 MiB array built into the library (resident on every GPU that loads it, for the life
+ * of the process); pdl_conv2d_wgrad_noalloc_max_bytes() is the limit and larger shapes are refused with an
+ * error.  The array is shared: calls that can overlap on the GPU race, keep them stream-ordered.  The first
+ * call on each device resolves the array's device address; make it before any stream capture starts. */
+long long pdl_conv2d_wgrad_noalloc_max_bytes(void);
+int pdl_conv2d_wgrad_simt_noalloc(const float* x, const float* dy, float* dw, float* db, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                                  int stride, int pad, cudaStream_t stream);
+
 /* ---- convolution, tcgen05 tensor cores (TF32 in, fp32 accumulate in TMEM), TMA-fed (same reference lines) ---- */
 int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool);
 int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed_bwd, int Cout, int Cin, int taps, cudaStream_t stream);
