@@ -1,0 +1,125 @@
+"""Shared pieces of the four example scripts.
+
+The examples mirror the reference's four entry points (same flags, same prints, same hyper-parameters):
+  convnet_spawn.py   <- mpspawn_dist.py   (ConvNet / MNIST, mp.spawn, env:// with explicit rank)
+  convnet_launch.py  <- launch_dist.py    (ConvNet / MNIST, launcher env contract)
+  resnet_spawn.py    <- example_mp.py     (ResNet-18 / CIFAR-10, mp.spawn, tcp:// init)
+  resnet_launch.py   <- example_launch.py (ResNet-18 / CIFAR-10, launcher)
+Only the imports differ: everything comes from this package instead of torch.distributed / torch.nn /
+torchvision.  The training boxes have no network, so datasets are synthetic by default; pass --data-root to
+use torchvision's MNIST / CIFAR-10 from disk.
+"""
+from __future__ import annotations
+
+import os
+import sys
+from datetime import datetime
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+import pytorch_distributed_learning_b200 as pdl  # noqa: E402
+import pytorch_distributed_learning_b200.nn as nn  # noqa: E402
+
+dist = pdl.distributed
+
+
+def pick_device(local_rank):
+    if torch.cuda.is_available():
+        torch.cuda.set_device(local_rank % torch.cuda.device_count())
+        return torch.device("cuda", local_rank % torch.cuda.device_count())
+    return torch.device("cpu")
+
+
+def backend_for(device):
+    return "nccl" if device.type == "cuda" else "gloo"
+
+
+def mnist_dataset(data_root=None, length=60000):
+    if data_root:
+        import torchvision
+        import torchvision.transforms as T
+
+        tf = T.Compose([T.ToTensor(), T.Normalize((0.1307,), (0.3081,))])
+        return torchvision.datasets.MNIST(data_root, train=True, download=False, transform=tf)
+    return pdl.utils.data.SyntheticMNIST(length)
+
+
+def cifar_dataset(data_root=None, length=50000):
+    if data_root:
+        import torchvision
+        import torchvision.transforms as T
+
+        tf = T.Compose([T.RandomCrop(32, padding=4), T.RandomHorizontalFlip(), T.ToTensor(),
+                        T.Normalize((0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010))])
+        return torchvision.datasets.CIFAR10(root=data_root, train=True, download=False, transform=tf)
+    return pdl.utils.data.SyntheticCIFAR10(length)
+
+
+def wrap(model, device):
+    if device.type == "cuda":
+        return nn.parallel.DistributedDataParallel(model, device_ids=[device.index], output_device=device.index)
+    return nn.parallel.DistributedDataParallel(model)
+
+
+def train_convnet(model, criterion, optimizer, loader, device, epochs, is_printer, graphed=False, max_steps=None):
+    """Loop body of the reference's ConvNet scripts: loss printed every 100 steps by the node's local rank 0."""
+    start = datetime.now()
+    total_step = len(loader)
+    if is_printer:
+        print("Total step: ", total_step)
+    step_fn = pdl.TrainStep(model, criterion, optimizer) if graphed else None
+    seen = 0
+    for epoch in range(epochs):
+        for i, (images, labels) in enumerate(loader):
+            if step_fn is not None:
+                loss = step_fn(images, labels)
+            else:
+                images = images.to(device, non_blocking=True)
+                labels = labels.to(device, non_blocking=True)
+                outputs = model(images)
+                loss = criterion(outputs, labels)
+                optimizer.zero_grad()
+                loss.backward()
+                optimizer.step()
+            if (i + 1) % 100 == 0 and is_printer:
+                print("Epoch [{}/{}], Step [{}/{}], Loss: {:.4f}".format(epoch + 1, epochs, i + 1, total_step, loss.item()))
+            seen += 1
+            if max_steps and seen >= max_steps:
+                break
+        if max_steps and seen >= max_steps:
+            break
+    if is_printer:
+        print("Training complete in: " + str(datetime.now() - start))
+
+
+def train_resnet(net, criterion, optimizer, loader, device, epochs, is_printer, max_steps=None):
+    """Loop body of the reference's ResNet scripts: running loss / accuracy every 25 steps on global rank 0."""
+    if is_printer:
+        print("            =======  Training  ======= \n")
+    net.train()
+    seen = 0
+    for ep in range(1, epochs + 1):
+        train_loss = correct = total = 0
+        loader.sampler.set_epoch(ep)
+        for idx, (inputs, targets) in enumerate(loader):
+            inputs, targets = inputs.to(device), targets.to(device)
+            outputs = net(inputs)
+            loss = criterion(outputs, targets)
+            optimizer.zero_grad()
+            loss.backward()
+            optimizer.step()
+            train_loss += loss.item()
+            total += targets.size(0)
+            correct += torch.eq(outputs.argmax(dim=1), targets).sum().item()
+            if is_printer and ((idx + 1) % 25 == 0 or (idx + 1) == len(loader)):
+                print("   == step: [{:3}/{}] [{}/{}] | loss: {:.3f} | acc: {:6.3f}%".format(
+                    idx + 1, len(loader), ep, epochs, train_loss / (idx + 1), 100.0 * correct / total))
+            seen += 1
+            if max_steps and seen >= max_steps:
+                break
+        if max_steps and seen >= max_steps:
+            break
+    if is_printer:
+        print("\n            =======  Training Finished  ======= \n")
