@@ -89,9 +89,9 @@ def _ptr_array(values):
 
 
 def choose_algorithm(nbytes, world, has_multicast, override=None):
-    """Per-bucket variant.  Defaults follow the measured crossover (see profiles/allreduce_sweep.md):
-    latency-bound buckets take the 1-hop one-shot kernel, bandwidth-bound ones the in-switch (NVLS)
-    or two-shot reduction."""
+    """Per-bucket variant, from the measured sweep (profiles/allreduce_sweep.md): with NVSwitch multicast the
+    in-switch reduction (NVLS) is the fastest variant at every size on 2 and 8 GPUs; without it the 1-hop
+    one-shot kernel wins for latency-bound buckets and two-shot for everything larger."""
     if override:
         name = override.lower()
         if name not in ALGOS:
@@ -101,10 +101,10 @@ def choose_algorithm(nbytes, world, has_multicast, override=None):
         return ALGOS[name]
     if world == 1:
         return ALGOS["oneshot"]
-    threshold = int(os.environ.get("PDL_ONESHOT_MAX_BYTES", 1 << 20))
-    if nbytes <= threshold:
-        return ALGOS["oneshot"]
-    return ALGOS["nvls"] if has_multicast else ALGOS["twoshot"]
+    if has_multicast:
+        return ALGOS["nvls"]
+    threshold = int(os.environ.get("PDL_ONESHOT_MAX_BYTES", 32 << 10))
+    return ALGOS["oneshot"] if nbytes <= threshold else ALGOS["twoshot"]
 
 
 class B200ProcessGroup(dist.ProcessGroup):
@@ -117,7 +117,8 @@ class B200ProcessGroup(dist.ProcessGroup):
             raise RuntimeError("backend 'nccl'/'b200' needs a CUDA device; use backend='gloo' for CPU-only runs")
         _lib.cuda()  # fail loudly now if the kernel library was not built
         self._ctl = dist.CpuProcessGroup(store, group_rank, ranks, name + "/ctl", master_host, timeout_s)
-        self.timeout_s = float(timeout_s)
+        # device-side bound on every peer wait (a dead rank must not spin a kernel for the 10-minute host timeout)
+        self.timeout_s = min(float(timeout_s), float(os.environ.get("PDL_KERNEL_TIMEOUT_S", "60")))
         self.device_index = device_index
         self._staging = None
         self._segments = []
@@ -211,14 +212,19 @@ class B200ProcessGroup(dist.ProcessGroup):
         st = self._stage()
         seg, half = st["seg"], st["half"]
         nbytes = work.numel() * work.element_size()
-        slot = (nbytes + 15) // 16 * 16
-        if slot * W > half:
-            raise RuntimeError("allgather of %d bytes per rank exceeds the %d-byte staging window" % (nbytes, half // W))
         send = seg.tensor(st["pad"], half, torch.uint8)
         recv = seg.tensor(st["pad"] + half, half, torch.uint8)
-        send[:nbytes].copy_(work.view(-1).view(torch.uint8))
-        self._pull(-1, slot, recv.data_ptr())
-        return [recv[r * slot:r * slot + nbytes].clone().view(work.dtype).view(work.shape) for r in range(W)]
+        flat = work.view(-1).view(torch.uint8)
+        outs = [torch.empty(nbytes, dtype=torch.uint8, device=work.device) for _ in range(W)]
+        chunk = half // W // 16 * 16  # bytes per rank per pass: W slots must fit the receive window
+        for off in range(0, max(nbytes, 1), chunk):
+            n = min(chunk, nbytes - off)
+            slot = (n + 15) // 16 * 16
+            send[:n].copy_(flat[off:off + n])
+            self._pull(-1, slot, recv.data_ptr(), blocks=min(32, max(1, slot >> 14)))
+            for r in range(W):
+                outs[r][off:off + n].copy_(recv[r * slot:r * slot + n])
+        return [o.view(work.dtype).view(work.shape) for o in outs]
 
     def allreduce(self, tensor, op=dist.ReduceOp.SUM, algorithm=None):
         if not tensor.is_cuda:
