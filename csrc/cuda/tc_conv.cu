@@ -29,6 +29,7 @@ struct TcGeom {
   int a_w0, a_h0;        // input coordinate read by output pixel (0,0) at tap (0,0)
   int tap_sign;          // +1: coord = base + tap (forward); -1: coord = base - tap (dgrad)
   int Nimg, Hout, Wout;  // output extent (Wout == BW)
+  int n_tiles, ldc;      // N_GEMM-wide column tiles; ldc = total output channels (tile index = m_tile * n_tiles + n_tile)
 };
 
 struct EpiArgs {
@@ -109,8 +110,9 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       bool ok = true;
       for (int tile = blockIdx.x; tile < g.num_tiles && ok; tile += gridDim.x) {
-        const int n0 = g.BN > 1 ? tile * g.BN : tile / g.tiles_per_img;
-        const int h0 = g.BN > 1 ? 0 : (tile % g.tiles_per_img) * g.BH;
+        const int mt = tile / g.n_tiles, nt = tile % g.n_tiles;
+        const int n0 = g.BN > 1 ? mt * g.BN : mt / g.tiles_per_img;
+        const int h0 = g.BN > 1 ? 0 : (mt % g.tiles_per_img) * g.BH;
         int tap = 0;
         for (int r = 0; r < g.R && ok; ++r)
           for (int s = 0; s < g.S && ok; ++s, ++tap)
@@ -119,7 +121,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               uint8_t* a_dst = smem + stage * SM::STAGE_BYTES;
               tc::mbar_expect_tx(&full[stage], stage_tx);
               tc::tma_load_4d(a_dst, &tmA, &full[stage], kc * 32, g.a_w0 + g.tap_sign * s, h0 + g.a_h0 + g.tap_sign * r, n0);
-              tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, tap * N_GEMM);
+              tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, tap * g.ldc + nt * N_GEMM);
               if (tile == blockIdx.x && tap == 0 && kc == 0) PDL_TRACE(2);
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
@@ -169,13 +171,15 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (*failed || !tc::mbar_wait(&tfull[acc], acc_phase)) { *failed = 1; break; }
       tc::tc_fence_after();
       if (tile == blockIdx.x && et == 0) PDL_TRACE(6);
-      const int n0 = g.BN > 1 ? tile * g.BN : tile / g.tiles_per_img;
-      const int h0 = g.BN > 1 ? 0 : (tile % g.tiles_per_img) * g.BH;
+      const int mt = tile / g.n_tiles, nt = tile % g.n_tiles;
+      const int n0 = g.BN > 1 ? mt * g.BN : mt / g.tiles_per_img;
+      const int h0 = g.BN > 1 ? 0 : (mt % g.tiles_per_img) * g.BH;
       const uint32_t t_row = tmem_base + acc * N_GEMM + half * HALF + (static_cast<uint32_t>(quarter * 32) << 16);
       if (EPI == EPI_STORE) {
         const int bw = row % g.BW, t2 = row / g.BW, bh = t2 % g.BH, bn = t2 / g.BH;
         const bool valid = row < rows && (n0 + bn) < g.Nimg && (h0 + bh) < g.Hout;
-        float* dst = e.out + ((static_cast<long long>(n0 + bn) * g.Hout + h0 + bh) * g.Wout + bw) * N_GEMM + half * HALF;
+        float* dst = e.out + ((static_cast<long long>(n0 + bn) * g.Hout + h0 + bh) * g.Wout + bw) * g.ldc + nt * N_GEMM + half * HALF;
+        const float* bias_t = e.bias ? e.bias + nt * N_GEMM + half * HALF : nullptr;
 #pragma unroll 1
         for (int c = 0; c < HALF; c += CH) {
           float v[CH];
@@ -183,7 +187,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           if (valid) {
 #pragma unroll
             for (int j = 0; j < CH; j += 4) {
-              const float4 bb = *reinterpret_cast<const float4*>(sbias + half * HALF + c + j);
+              const float4 bb = bias_t ? *reinterpret_cast<const float4*>(bias_t + c + j) : make_float4(0.f, 0.f, 0.f, 0.f);
               float4 o = make_float4(v[j] + bb.x, v[j + 1] + bb.y, v[j + 2] + bb.z, v[j + 3] + bb.w);
               if (e.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
               *reinterpret_cast<float4*>(dst + c + j) = o;
@@ -353,8 +357,13 @@ static long long* g_trace = nullptr;
 PDL_API void pdl_tc_set_trace(long long* buf) { g_trace = buf; }
 
 // 1 if the tensor-core forward path covers this shape (stride 1, Cin % 32 == 0, Cout in {32,64,128}).
+static int n_gemm_for(int channels) {  // widest supported column tile dividing `channels`, 0 if none
+  if (channels == 32 || channels == 64) return channels;
+  return channels % 128 == 0 ? 128 : 0;
+}
+
 PDL_API int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool) {
-  if (stride != 1 || Cin % 32 || !(Cout == 32 || Cout == 64 || Cout == 128)) return 0;
+  if (stride != 1 || Cin % 32 || !n_gemm_for(Cout) || (pool && Cout > 128)) return 0;
   int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
   TcGeom g{};
   return choose_box(P, Q, pool, &g) ? 1 : 0;
@@ -375,13 +384,16 @@ PDL_API int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float
   TcGeom g{};
   const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
   if (!choose_box(P, Q, pool_stride > 0, &g)) { pdl_set_error("tc_conv fwd: no tile for %dx%d output", P, Q); return -4; }
-  g.num_tiles = g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img;
+  const int ng = n_gemm_for(Cout);
+  if (!ng || Cin % 32 || (pool_stride > 0 && Cout > 128)) { pdl_set_error("tc_conv fwd: unsupported channels %d -> %d", Cin, Cout); return -3; }
+  g.n_tiles = Cout / ng; g.ldc = Cout;
+  g.num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * g.n_tiles;
   g.R = KH; g.S = KW; g.kchunks = Cin / 32; g.a_w0 = -pad; g.a_h0 = -pad; g.tap_sign = 1; g.Nimg = N; g.Hout = P; g.Wout = Q;
   CUtensorMap ta, tb;
   if (int rc = make_act_map(&ta, x, N, H, W, Cin, g.BW, g.BH, g.BN)) return rc;
-  if (int rc = make_weight_map(&tb, packed_w, KH * KW * Cout, Cin, Cout)) return rc;
+  if (int rc = make_weight_map(&tb, packed_w, KH * KW * Cout, Cin, ng)) return rc;
   EpiArgs e{y, idx, bias, relu, pool_stride, error_flag, g_trace};
-  return pool_stride > 0 ? dispatch_n<EPI_RELU_POOL>(Cout, ta, tb, g, e, stream) : dispatch_n<EPI_STORE>(Cout, ta, tb, g, e, stream);
+  return pool_stride > 0 ? dispatch_n<EPI_RELU_POOL>(ng, ta, tb, g, e, stream) : dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream);
 }
 
 // dgrad (stride 1): dx[N][H][W][Cin] from dy[N][P][Q][Cout] and packed_bwd[tap][Cin][Cout].
@@ -389,14 +401,16 @@ PDL_API int pdl_tc_conv2d_dgrad(const float* dy, const float* packed_w_bwd, floa
                                 int pad, int* error_flag, cudaStream_t stream) {
   TcGeom g{};
   const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
-  if (Cout % 32 || !(Cin == 32 || Cin == 64 || Cin == 128)) { pdl_set_error("tc_conv dgrad: unsupported channels %d -> %d", Cout, Cin); return -3; }
+  const int ng = n_gemm_for(Cin);
+  if (Cout % 32 || !ng) { pdl_set_error("tc_conv dgrad: unsupported channels %d -> %d", Cout, Cin); return -3; }
   if (!choose_box(H, W, 0, &g)) { pdl_set_error("tc_conv dgrad: no tile for %dx%d", H, W); return -4; }
-  g.num_tiles = g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img;
+  g.n_tiles = Cin / ng; g.ldc = Cin;
+  g.num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * g.n_tiles;
   // dx[h, w] = sum_{r,s} dy[h + pad - r, w + pad - s] * w[r, s]
   g.R = KH; g.S = KW; g.kchunks = Cout / 32; g.a_w0 = pad; g.a_h0 = pad; g.tap_sign = -1; g.Nimg = N; g.Hout = H; g.Wout = W;
   CUtensorMap ta, tb;
   if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
-  if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, Cin)) return rc;
+  if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, ng)) return rc;
   EpiArgs e{dx, nullptr, nullptr, 0, 0, error_flag, g_trace};
-  return dispatch_n<EPI_STORE>(Cin, ta, tb, g, e, stream);
+  return dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream);
 }

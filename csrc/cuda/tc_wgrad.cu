@@ -31,6 +31,7 @@ struct WgGeom {
   int S;                 // taps per filter row (= taps handled by one CTA, <= 3)
   int pad;
   int layout_type, lbo, sbo, tma_swizzle;  // descriptor knobs (defaults set on the host)
+  int Cin, Cout, cin_tiles;  // full channel counts; blockIdx.z = cout_tile * cin_tiles + cin_tile
 };
 
 __device__ __forceinline__ uint64_t smem_desc_lt(uint32_t smem_addr, uint32_t lbo, uint32_t sbo, uint32_t layout_type) {
@@ -66,6 +67,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
   constexpr uint32_t kCols = (kMaxTapsPerCta * N_GEMM <= 128) ? 128 : 256;
   const int tap_row = blockIdx.x;  // filter row r
   const int split = blockIdx.y;
+  const int co0 = (blockIdx.z / g.cin_tiles) * M_GEMM, ci0 = (blockIdx.z % g.cin_tiles) * N_GEMM;  // channel tile origin
   const int u_begin = split * g.units_per_cta;
   const int u_end = min(g.units, u_begin + g.units_per_cta);
 
@@ -92,10 +94,10 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
         const int n = u / g.strips, h0 = (u % g.strips) * g.BH;
         uint8_t* base = smem + stage * stage_bytes;
         tc::mbar_expect_tx(&full[stage], static_cast<uint32_t>(stage_bytes));
-        for (int c = 0; c < A_CHUNKS; ++c) tc::tma_load_4d(base + c * chunk_bytes, &tmDy, &full[stage], c * 32, 0, h0, n);
+        for (int c = 0; c < A_CHUNKS; ++c) tc::tma_load_4d(base + c * chunk_bytes, &tmDy, &full[stage], co0 + c * 32, 0, h0, n);
         for (int s = 0; s < g.S; ++s)
           for (int c = 0; c < B_CHUNKS; ++c)
-            tc::tma_load_4d(base + a_bytes + s * b_tap_bytes + c * chunk_bytes, &tmX, &full[stage], c * 32, s - g.pad, h0 + tap_row - g.pad, n);
+            tc::tma_load_4d(base + a_bytes + s * b_tap_bytes + c * chunk_bytes, &tmX, &full[stage], ci0 + c * 32, s - g.pad, h0 + tap_row - g.pad, n);
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
@@ -135,7 +137,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
     const bool row_valid = (M_GEMM == 128) || lane < 16;
     for (int s = 0; s < g.S; ++s) {
       const int tap = tap_row * g.S + s;
-      float* dst = partial + ((static_cast<long long>(split) * (gridDim.x * g.S) + tap) * M_GEMM + co) * N_GEMM;
+      float* dst = partial + ((static_cast<long long>(split) * (gridDim.x * g.S) + tap) * g.Cout + co0 + co) * g.Cin + ci0;
 #pragma unroll 1
       for (int c = 0; c < N_GEMM; c += 32) {
         float v[32];
@@ -213,15 +215,28 @@ int act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int b
 
 int env_int(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
 
-bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KW, int pad, WgGeom* g) {
-  if (!(Cout == 64 || Cout == 128) || !(Cin == 32 || Cin == 64) || KW > kMaxTapsPerCta) return false;
-  int bw = (Q + 7) / 8 * 8;
+// Channel tiles: M (= Cout) tile 128 (64 when Cout == 64), N (= Cin) tile 64 (32 when Cin == 32).
+int wg_m_tile(int Cout) { return Cout == 64 ? 64 : (Cout % 128 == 0 ? 128 : 0); }
+int wg_n_tile(int Cin) { return Cin == 32 ? 32 : (Cin % 64 == 0 ? 64 : 0); }
+
+bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KH, int KW, int pad, WgGeom* g) {
+  const int mt = wg_m_tile(Cout), nt = wg_n_tile(Cin);
+  if (!mt || !nt || KW > kMaxTapsPerCta) return false;
+  int bw = (Q + 7) / 8 * 8;  // K stage = bw x bh pixels, a multiple of 8 rows (one MMA = 8 pixels)
   if (bw > 64) return false;
-  int bh = 64 / bw;  // 64-pixel K stages keep several stages in flight
-  if (bw * bh != 64) return false;
+  int bh = 64 / bw;
+  if (bh < 1) bh = 1;
   g->BW = bw; g->BH = bh; g->strips = (P + bh - 1) / bh; g->units = N * g->strips;
-  // K split: enough CTAs to occupy the chip (grid = KH x splits), few enough that the partial sums stay cheap
-  int splits = g->units < 48 ? g->units : 48;
+  const int rows = bw * bh;
+  const long long stage_bytes = static_cast<long long>(mt / 32 + KW * (nt / 32)) * rows * 128;
+  if (stage_bytes * 2 > 200 * 1024) return false;
+  g->Cin = Cin; g->Cout = Cout; g->cin_tiles = Cin / nt;
+  // K split: enough CTAs to occupy the chip (grid = KH x splits x channel tiles), few enough that the partial sums stay cheap
+  const int tiles = (Cout / mt) * (Cin / nt);
+  int splits = (2 * 148 + KH * tiles - 1) / (KH * tiles);
+  if (splits > 48) splits = 48;
+  if (splits > g->units) splits = g->units;
+  if (splits < 1) splits = 1;
   g->units_per_cta = (g->units + splits - 1) / splits;
   g->S = KW; g->pad = pad;
   g->layout_type = env_int("PDL_WG_LT", 1);   // SWIZZLE_128B_BASE32B
@@ -241,7 +256,7 @@ int launch_wg(const CUtensorMap& a, const CUtensorMap& b, const WgGeom& g, int K
     PDL_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  dim3 grid(KH, wg_splits(g));
+  dim3 grid(KH, wg_splits(g), (g.Cout / M) * g.cin_tiles);
   kernel<<<grid, kThreads, smem, stream>>>(a, b, g, partial, error);
   PDL_LAUNCH_CHECK();
   return 0;
@@ -252,12 +267,12 @@ int launch_wg(const CUtensorMap& a, const CUtensorMap& b, const WgGeom& g, int K
 PDL_API int pdl_tc_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
   if (stride != 1) return 0;
   WgGeom g{};
-  return wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KW, pad, &g) ? 1 : 0;
+  return wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KH, KW, pad, &g) ? 1 : 0;
 }
 
 PDL_API long long pdl_tc_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad) {
   WgGeom g{};
-  if (!wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KW, pad, &g)) return 0;
+  if (!wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KH, KW, pad, &g)) return 0;
   return static_cast<long long>(wg_splits(g)) * KH * KW * Cout * Cin * sizeof(float);
 }
 
@@ -267,15 +282,16 @@ PDL_API int pdl_tc_conv2d_wgrad(const float* x, const float* dy, float* dw, floa
                                 int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad, int* error_flag, cudaStream_t stream) {
   WgGeom g{};
   const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
-  if (!wg_geometry(N, P, Q, Cin, Cout, KW, pad, &g)) { pdl_set_error("tc wgrad: unsupported shape"); return -3; }
+  if (!wg_geometry(N, P, Q, Cin, Cout, KH, KW, pad, &g)) { pdl_set_error("tc wgrad: unsupported shape"); return -3; }
   CUtensorMap ta, tb;
   if (int rc = act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.tma_swizzle)) return rc;
   if (int rc = act_map(&tb, x, N, H, W, Cin, g.BW, g.BH, g.tma_swizzle)) return rc;
   int rc = -3;
-  if (Cout == 128 && Cin == 64) rc = launch_wg<128, 64>(ta, tb, g, KH, scratch, error_flag, stream);
-  else if (Cout == 128 && Cin == 32) rc = launch_wg<128, 32>(ta, tb, g, KH, scratch, error_flag, stream);
-  else if (Cout == 64 && Cin == 32) rc = launch_wg<64, 32>(ta, tb, g, KH, scratch, error_flag, stream);
-  else if (Cout == 64 && Cin == 64) rc = launch_wg<64, 64>(ta, tb, g, KH, scratch, error_flag, stream);
+  const int mt = wg_m_tile(Cout), nt = wg_n_tile(Cin);
+  if (mt == 128 && nt == 64) rc = launch_wg<128, 64>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (mt == 128 && nt == 32) rc = launch_wg<128, 32>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (mt == 64 && nt == 32) rc = launch_wg<64, 32>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (mt == 64 && nt == 64) rc = launch_wg<64, 64>(ta, tb, g, KH, scratch, error_flag, stream);
   if (rc) return rc;
   const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
   wgrad_finish_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(scratch, wg_splits(g), KH * KW, Cout, Cin, dw, db_partial, db_blocks, db);

@@ -112,6 +112,15 @@ int pdl_pool2_bwd_dbias(const float* da, const uint8_t* idx, const float* pooled
 int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_t* idx1, const float* a1, float* gw1, float* gb1, float* partial, int N,
                           cudaStream_t stream);
 
+/* ---- BatchNorm2d, NHWC rows [M = N*H*W][C] (reference: torchvision resnet18 at example_launch.py:26) ---- */
+long long pdl_bn_scratch_floats(long long M, int C);
+int pdl_bn_fwd_train(const float* x, const float* gamma, const float* beta, float* running_mean, float* running_var, float momentum, float eps,
+                     float* y, float* save_mean, float* save_invstd, float* scratch, long long M, int C, int relu, cudaStream_t stream);
+int pdl_bn_fwd_eval(const float* x, const float* gamma, const float* beta, const float* running_mean, const float* running_var, float eps,
+                    float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream);
+int pdl_bn_bwd(const float* x, const float* dy, const float* gamma, const float* save_mean, const float* save_invstd, float* dx, float* dgamma,
+               float* dbeta, float* scratch, long long M, int C, cudaStream_t stream);
+
 /* ---- element-wise / pooling / linear / loss (reference: nn.ReLU, nn.MaxPool2d, nn.Linear,
  *      nn.CrossEntropyLoss at launch_dist.py:13-32,58; ResNet add+ReLU / avgpool at example_launch.py:26) ---- */
 int pdl_relu_fwd(const float* x, float* y, long long n, cudaStream_t stream);

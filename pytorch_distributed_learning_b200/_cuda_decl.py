@@ -63,6 +63,11 @@ def declare(L):
     sig("pdl_pool2_bwd_blocks", [I, I, I, I])
     sig("pdl_pool2_bwd_dbias", [P, P, P, P, P, I, I, I, I, I, P])
     sig("pdl_conv1_wgrad_fused", [P, P, P, P, P, P, P, I, P])
+    # batch norm
+    sig("pdl_bn_scratch_floats", [LL, I], LL)
+    sig("pdl_bn_fwd_train", [P, P, P, P, P, F, F, P, P, P, P, LL, I, I, P])
+    sig("pdl_bn_fwd_eval", [P, P, P, P, P, F, P, P, LL, I, I, P])
+    sig("pdl_bn_bwd", [P, P, P, P, P, P, P, P, P, LL, I, P])
     # element-wise / pooling / linear / loss
     sig("pdl_relu_fwd", [P, P, LL, P])
     sig("pdl_relu_bwd", [P, P, P, LL, P])

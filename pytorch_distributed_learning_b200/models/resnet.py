@@ -11,6 +11,7 @@ ones/zeros for batch-norm).
 from __future__ import annotations
 
 from .. import nn
+from ..nn.modules import add_relu
 
 
 def _conv3x3(cin, cout, stride=1):
@@ -40,7 +41,7 @@ class BasicBlock(nn.Module):
         out = self.bn2(self.conv2(out))
         if self.downsample is not None:
             identity = self.downsample(x)
-        return self.relu(out + identity)
+        return add_relu(out, identity)
 
 
 class Bottleneck(nn.Module):
@@ -65,7 +66,7 @@ class Bottleneck(nn.Module):
         out = self.bn3(self.conv3(out))
         if self.downsample is not None:
             identity = self.downsample(x)
-        return self.relu(out + identity)
+        return add_relu(out, identity)
 
 
 class ResNet(nn.Module):

@@ -230,3 +230,31 @@ class _GlobalAvgPool(torch.autograd.Function):
 
 def global_avg_pool(x):
     return _GlobalAvgPool.apply(x)
+
+
+class _AddRelu(torch.autograd.Function):
+    """y = relu(a + b): the residual join of the ResNet blocks in one kernel; both inputs get dy * (y > 0)."""
+
+    @staticmethod
+    def forward(ctx, a, b):
+        a = _nhwc(a)
+        b = _nhwc(b)
+        if b.stride() != a.stride():
+            b = torch.empty_like(a).copy_(b)
+        y = torch.empty_like(a)
+        _ok(_lib.cuda().pdl_add_relu_fwd(_p(a), _p(b), _p(y), a.numel(), _stream(a)), "add+relu forward")
+        ctx.save_for_backward(y)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        (y,) = ctx.saved_tensors
+        if dy.stride() != y.stride():
+            dy = torch.empty_like(y).copy_(dy)
+        dx = torch.empty_like(y)
+        _ok(_lib.cuda().pdl_relu_bwd(_p(y), _p(dy), _p(dx), y.numel(), _stream(y)), "add+relu backward")
+        return dx, dx
+
+
+def add_relu(a, b):
+    return _AddRelu.apply(a, b)

@@ -97,7 +97,7 @@ def conv2d_dgrad(dy, w, dx, stride, pad):
         return False
     N, Cin, H, W = dx.shape
     Cout, _, KH, KW = w.shape
-    if Cout % 32 or Cin not in (32, 64, 128) or W > 128:
+    if Cout % 32 or not (Cin in (32, 64) or Cin % 128 == 0) or W > 128:
         return False
     _, packed = pack_weights(w, False, True)
     _ok(_lib.cuda().pdl_tc_conv2d_dgrad(_p(dy), _p(packed), _p(dx), N, H, W, Cin, Cout, KH, KW, pad, _p(error_flag(dx.device)), _stream(dx)),

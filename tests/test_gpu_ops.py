@@ -209,3 +209,44 @@ def test_allreduce_fused_sgd_emulated(algo):
 def test_allreduce_soak_emulated():
     _emulated_allreduce(0, 8, 4096, sgd=False, steps=200, blocks=4)
     _emulated_allreduce(2, 8, 4096, sgd=False, steps=100, blocks=4)
+
+
+@pytest.mark.parametrize("shape", [(8, 64, 8, 8), (4, 128, 4, 4), (16, 256, 2, 2), (3, 64, 16, 16), (64, 512, 1, 1)])
+def test_batchnorm_train_fwd_bwd_matches_torch(shape):
+    torch.manual_seed(6)
+    N, C, H, W = shape
+    x = (torch.randn(shape, device=_dev()) * 2 + 0.5).requires_grad_(True)
+    xr = x.detach().clone().requires_grad_(True)
+    ours, ref = pdl.nn.BatchNorm2d(C).to(_dev()), torch.nn.BatchNorm2d(C).to(_dev())
+    with torch.no_grad():
+        ours.weight.uniform_(0.5, 1.5)
+        ours.bias.uniform_(-0.5, 0.5)
+    ref.load_state_dict(ours.state_dict())
+    for _ in range(2):  # twice: running statistics must keep tracking torch's
+        y, yr = ours(x), ref(xr)
+    torch.testing.assert_close(y, yr, rtol=1e-4, atol=1e-4)
+    dy = torch.randn_like(yr)
+    y.backward(dy)
+    yr.backward(dy)
+    torch.testing.assert_close(x.grad, xr.grad, rtol=1e-3, atol=1e-4)
+    torch.testing.assert_close(ours.weight.grad, ref.weight.grad, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(ours.bias.grad, ref.bias.grad, rtol=1e-3, atol=1e-3)
+    torch.testing.assert_close(ours.running_mean, ref.running_mean, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(ours.running_var, ref.running_var, rtol=1e-4, atol=1e-5)
+    assert int(ours.num_batches_tracked) == int(ref.num_batches_tracked) == 2
+    ours.eval(), ref.eval()
+    with torch.no_grad():
+        torch.testing.assert_close(ours(x), ref(xr), rtol=1e-4, atol=1e-4)
+
+
+def test_add_relu():
+    a = torch.randn(4, 64, 8, 8, device=_dev(), requires_grad=True)
+    b = torch.randn(4, 64, 8, 8, device=_dev(), requires_grad=True)
+    ar, br = a.detach().clone().requires_grad_(True), b.detach().clone().requires_grad_(True)
+    y, yr = NF.add_relu(a, b), torch.relu(ar + br)
+    torch.testing.assert_close(y, yr)
+    dy = torch.randn_like(yr)
+    y.backward(dy)
+    yr.backward(dy)
+    torch.testing.assert_close(a.grad, ar.grad)
+    torch.testing.assert_close(b.grad, br.grad)

@@ -32,7 +32,9 @@ def _tf32_close(a, b, scale_ref=None):
 
 # (N, Cin, H, Cout, k, pad): ConvNet conv2 / conv3 and a few other stride-1 shapes
 FWD_CASES = [(5, 32, 13, 64, 3, 0), (5, 64, 10, 128, 3, 0), (100, 32, 13, 64, 3, 0), (7, 64, 10, 128, 3, 0),
-             (3, 64, 8, 64, 3, 1), (2, 32, 20, 32, 3, 1), (4, 128, 6, 128, 1, 0)]
+             (3, 64, 8, 64, 3, 1), (2, 32, 20, 32, 3, 1), (4, 128, 6, 128, 1, 0),
+             # ResNet-style: wide channels (column tiles), 1x1, large spatial extents (row-strip tiles)
+             (2, 256, 4, 256, 3, 1), (2, 512, 2, 512, 3, 1), (2, 64, 56, 256, 1, 0), (2, 128, 28, 128, 3, 1), (3, 1024, 14, 256, 1, 0)]
 
 
 @pytest.mark.parametrize("case", FWD_CASES)
@@ -72,7 +74,8 @@ def test_tc_forward_fused_relu_pool(case, ps):
     assert int(idx.max()) <= 3
 
 
-DGRAD_CASES = [(5, 32, 13, 64, 3, 0), (5, 64, 10, 128, 3, 0), (100, 64, 10, 128, 3, 0), (3, 64, 8, 64, 3, 1)]
+DGRAD_CASES = [(5, 32, 13, 64, 3, 0), (5, 64, 10, 128, 3, 0), (100, 64, 10, 128, 3, 0), (3, 64, 8, 64, 3, 1),
+               (2, 256, 4, 256, 3, 1), (2, 256, 56, 64, 1, 0), (2, 128, 28, 128, 3, 1), (3, 256, 14, 1024, 1, 0)]
 
 
 @pytest.mark.parametrize("case", DGRAD_CASES)
@@ -91,7 +94,8 @@ def test_tc_dgrad_matches_fp32(case):
     _tf32_close(dx, ref)
 
 
-WGRAD_CASES = [(5, 32, 13, 64, 3, 0), (5, 64, 10, 128, 3, 0), (100, 32, 13, 64, 3, 0), (100, 64, 10, 128, 3, 0), (3, 64, 8, 64, 3, 1)]
+WGRAD_CASES = [(5, 32, 13, 64, 3, 0), (5, 64, 10, 128, 3, 0), (100, 32, 13, 64, 3, 0), (100, 64, 10, 128, 3, 0), (3, 64, 8, 64, 3, 1),
+               (2, 256, 4, 256, 3, 1), (2, 64, 56, 256, 1, 0), (2, 128, 28, 128, 3, 1), (3, 1024, 14, 256, 1, 0), (4, 512, 7, 512, 3, 1)]
 
 
 @pytest.mark.parametrize("case", WGRAD_CASES)
