@@ -19,7 +19,10 @@ void pdl_set_error(const char* fmt, ...);
     }                                                                                         \
   } while (0)
 
-#define PDL_LAUNCH_CHECK() PDL_CUDA_CHECK(cudaGetLastError())
+// Every launcher ends with this: counts the call (pdl_launch_count(), used to report how many of this
+// library's launchers ran in a timed region) and surfaces launch errors.
+extern long long g_pdl_launch_calls;
+#define PDL_LAUNCH_CHECK() do { ++g_pdl_launch_calls; PDL_CUDA_CHECK(cudaGetLastError()); } while (0)
 
 static inline int pdl_ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
 

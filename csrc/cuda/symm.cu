@@ -31,6 +31,10 @@ void pdl_set_error(const char* fmt, ...) {
 
 PDL_API const char* pdl_last_error() { return g_err; }
 
+long long g_pdl_launch_calls = 0;
+// Number of launcher calls (each enqueues at least one kernel of this library) made so far in this process.
+PDL_API long long pdl_launch_count() { return g_pdl_launch_calls; }
+
 // ---- driver entry points fetched at run time (the .so must load on a box without libcuda) ----
 namespace {
 

@@ -29,6 +29,9 @@ struct TcGeom {
   int a_w0, a_h0;        // input coordinate read by output pixel (0,0) at tap (0,0)
   int tap_sign;          // +1: coord = base + tap (forward); -1: coord = base - tap (dgrad)
   int Nimg, Hout, Wout;  // output extent (Wout == BW)
+  int in_stride;         // convolution stride (forward): box origin row = h0 * in_stride + a_h0 + tap
+  int tap_r0, tap_s0, tap_step, S_full;  // taps visited: (tap_r0 + r*tap_step, tap_s0 + s*tap_step) of an S_full-wide filter
+  int out_stride, out_oh, out_ow, Hc;    // output pixel = (tile row * out_stride + out_oh, col * out_stride + out_ow); Hc tile-grid rows
   int n_tiles, ldc;      // N_GEMM-wide column tiles; ldc = total output channels (tile index = m_tile * n_tiles + n_tile)
 };
 
@@ -120,8 +123,9 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               if (!tc::mbar_wait(&empty[stage], phase ^ 1)) { *failed = 1; ok = false; break; }
               uint8_t* a_dst = smem + stage * SM::STAGE_BYTES;
               tc::mbar_expect_tx(&full[stage], stage_tx);
-              tc::tma_load_4d(a_dst, &tmA, &full[stage], kc * 32, g.a_w0 + g.tap_sign * s, h0 + g.a_h0 + g.tap_sign * r, n0);
-              tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, tap * g.ldc + nt * N_GEMM);
+              tc::tma_load_4d(a_dst, &tmA, &full[stage], kc * 32, g.a_w0 + g.tap_sign * s, h0 * g.in_stride + g.a_h0 + g.tap_sign * r, n0);
+              const int wtap = (g.tap_r0 + r * g.tap_step) * g.S_full + g.tap_s0 + s * g.tap_step;  // row block of the packed weights
+              tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, wtap * g.ldc + nt * N_GEMM);
               if (tile == blockIdx.x && tap == 0 && kc == 0) PDL_TRACE(2);
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
@@ -177,8 +181,10 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const uint32_t t_row = tmem_base + acc * N_GEMM + half * HALF + (static_cast<uint32_t>(quarter * 32) << 16);
       if (EPI == EPI_STORE) {
         const int bw = row % g.BW, t2 = row / g.BW, bh = t2 % g.BH, bn = t2 / g.BH;
-        const bool valid = row < rows && (n0 + bn) < g.Nimg && (h0 + bh) < g.Hout;
-        float* dst = e.out + ((static_cast<long long>(n0 + bn) * g.Hout + h0 + bh) * g.Wout + bw) * g.ldc + nt * N_GEMM + half * HALF;
+        // output pixel of this row: the tile grid (Hc x BW) is the full image, or one parity class of it (strided dgrad)
+        const int oh = (h0 + bh) * g.out_stride + g.out_oh, ow = bw * g.out_stride + g.out_ow;
+        const bool valid = row < rows && (n0 + bn) < g.Nimg && (h0 + bh) < g.Hc && oh < g.Hout && ow < g.Wout;
+        float* dst = e.out + ((static_cast<long long>(n0 + bn) * g.Hout + oh) * g.Wout + ow) * g.ldc + nt * N_GEMM + half * HALF;
         const float* bias_t = e.bias ? e.bias + nt * N_GEMM + half * HALF : nullptr;
 #pragma unroll 1
         for (int c = 0; c < HALF; c += CH) {
@@ -275,13 +281,14 @@ EncodeTiledFn encode_tiled() {
 }
 
 // NHWC activation [N][H][W][C] viewed as a 4-D tensor (C, W, H, N); box = (32, bw, bh, bn).
-int make_act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int bw, int bh, int bn) {
+int make_act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int bw, int bh, int bn, int stride = 1) {
   EncodeTiledFn enc = encode_tiled();
   if (!enc) { pdl_set_error("cuTensorMapEncodeTiled is not available"); return -1; }
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t strides[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
-  cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
-  cuuint32_t es[4] = {1, 1, 1, 1};
+  // stride s: the box spans bw*s x bh*s input pixels and the traversal stride keeps every s-th one (bw x bh rows land in smem)
+  cuuint32_t box[4] = {32, (cuuint32_t)(bw * stride), (cuuint32_t)(bh * stride), (cuuint32_t)bn};
+  cuuint32_t es[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(activation %dx%dx%dx%d, box %dx%dx%d) failed: %d", N, H, W, C, bw, bh, bn, (int)r); return -2; }
@@ -363,8 +370,9 @@ static int n_gemm_for(int channels) {  // widest supported column tile dividing 
 }
 
 PDL_API int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool) {
-  if (stride != 1 || Cin % 32 || !n_gemm_for(Cout) || (pool && Cout > 128)) return 0;
-  int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
+  if ((stride != 1 && stride != 2) || (stride == 2 && pool) || Cin % 32 || !n_gemm_for(Cout) || (pool && Cout > 128)) return 0;
+  int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
+  if (Q * stride > 256) return 0;
   TcGeom g{};
   return choose_box(P, Q, pool, &g) ? 1 : 0;
 }
@@ -379,10 +387,12 @@ PDL_API int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed
 
 // Forward: y = conv(x, w) + bias, optional ReLU; with pool_stride in {1,2} the 2x2 max-pool is fused and
 // `y`/`idx` receive the POOLED output [N][PH][PW][Cout] and its argmax (0..3).  x is NHWC.
-PDL_API int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin,
-                              int Cout, int KH, int KW, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream) {
+static int tc_fwd_impl(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin, int Cout,
+                       int KH, int KW, int stride, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream) {
   TcGeom g{};
-  const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
+  const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
+  g.in_stride = stride;
+  g.tap_r0 = g.tap_s0 = 0; g.tap_step = 1; g.S_full = KW; g.out_stride = 1; g.out_oh = g.out_ow = 0; g.Hc = P;
   if (!choose_box(P, Q, pool_stride > 0, &g)) { pdl_set_error("tc_conv fwd: no tile for %dx%d output", P, Q); return -4; }
   const int ng = n_gemm_for(Cout);
   if (!ng || Cin % 32 || (pool_stride > 0 && Cout > 128)) { pdl_set_error("tc_conv fwd: unsupported channels %d -> %d", Cin, Cout); return -3; }
@@ -390,27 +400,69 @@ PDL_API int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float
   g.num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * g.n_tiles;
   g.R = KH; g.S = KW; g.kchunks = Cin / 32; g.a_w0 = -pad; g.a_h0 = -pad; g.tap_sign = 1; g.Nimg = N; g.Hout = P; g.Wout = Q;
   CUtensorMap ta, tb;
-  if (int rc = make_act_map(&ta, x, N, H, W, Cin, g.BW, g.BH, g.BN)) return rc;
+  if (int rc = make_act_map(&ta, x, N, H, W, Cin, g.BW, g.BH, g.BN, stride)) return rc;
   if (int rc = make_weight_map(&tb, packed_w, KH * KW * Cout, Cin, ng)) return rc;
   EpiArgs e{y, idx, bias, relu, pool_stride, error_flag, g_trace};
   return pool_stride > 0 ? dispatch_n<EPI_RELU_POOL>(ng, ta, tb, g, e, stream) : dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream);
 }
 
+PDL_API int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin,
+                              int Cout, int KH, int KW, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream) {
+  return tc_fwd_impl(x, packed_w, bias, y, idx, N, H, W, Cin, Cout, KH, KW, 1, pad, relu, pool_stride, error_flag, stream);
+}
+
+// Forward with a convolution stride of 1 or 2 (no fused pooling): the TMA traversal stride subsamples the input box.
+PDL_API int pdl_tc_conv2d_fwd_strided(const float* x, const float* packed_w, const float* bias, float* y, int N, int H, int W, int Cin, int Cout,
+                                      int KH, int KW, int stride, int pad, int relu, int* error_flag, cudaStream_t stream) {
+  if (stride != 1 && stride != 2) { pdl_set_error("tc_conv fwd: stride %d is not supported", stride); return -3; }
+  return tc_fwd_impl(x, packed_w, bias, y, nullptr, N, H, W, Cin, Cout, KH, KW, stride, pad, relu, 0, error_flag, stream);
+}
+
+// dgrad (stride 1): dx[N][H][W][Cin] from dy[N][P][Q][Cout] and packed_bwd[tap][Cin][Cout].
+// dgrad for convolution stride 1 or 2.  Stride 2 is solved as four stride-1 problems, one per parity class
+// (h % 2, w % 2) of dx: only the taps with matching parity reach a class, the class is a dense sub-grid of dx,
+// and its outputs are written with a stride of 2.  Classes no tap reaches (1x1 filters) stay zero.
+PDL_API int pdl_tc_conv2d_dgrad_strided(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH,
+                                        int KW, int stride, int pad, int* error_flag, cudaStream_t stream) {
+  if (stride != 1 && stride != 2) { pdl_set_error("tc_conv dgrad: stride %d is not supported", stride); return -3; }
+  const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
+  const int ng = n_gemm_for(Cin);
+  if (Cout % 32 || !ng) { pdl_set_error("tc_conv dgrad: unsupported channels %d -> %d", Cout, Cin); return -3; }
+  CUtensorMap tb;
+  if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, ng)) return rc;
+  bool need_zero = false;
+  for (int ph = 0; ph < stride; ++ph)
+    for (int pw = 0; pw < stride; ++pw) {
+      const int r0 = (ph + pad) % stride, s0 = (pw + pad) % stride;
+      if (r0 >= KH || s0 >= KW || ph >= H || pw >= W) need_zero = true;
+    }
+  if (need_zero) PDL_CUDA_CHECK(cudaMemsetAsync(dx, 0, sizeof(float) * static_cast<size_t>(N) * H * W * Cin, stream));
+  for (int ph = 0; ph < stride; ++ph)
+    for (int pw = 0; pw < stride; ++pw) {
+      // dx[stride*a + ph, stride*b + pw] = sum over taps r = r0 + stride*i, s = s0 + stride*j of dy[a + (ph+pad-r)/stride, b + (pw+pad-s)/stride] * w[r, s]
+      const int r0 = (ph + pad) % stride, s0 = (pw + pad) % stride;
+      if (r0 >= KH || s0 >= KW || ph >= H || pw >= W) continue;
+      TcGeom g{};
+      const int Hc = (H - ph + stride - 1) / stride, Wc = (W - pw + stride - 1) / stride;
+      if (!choose_box(Hc, Wc, 0, &g)) { pdl_set_error("tc_conv dgrad: no tile for %dx%d", Hc, Wc); return -4; }
+      g.n_tiles = Cin / ng; g.ldc = Cin;
+      g.num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * g.n_tiles;
+      g.in_stride = 1;
+      g.R = (KH - r0 + stride - 1) / stride; g.S = (KW - s0 + stride - 1) / stride; g.kchunks = Cout / 32;
+      g.tap_r0 = r0; g.tap_s0 = s0; g.tap_step = stride; g.S_full = KW;
+      g.a_h0 = (ph + pad - r0) / stride; g.a_w0 = (pw + pad - s0) / stride; g.tap_sign = -1;
+      g.out_stride = stride; g.out_oh = ph; g.out_ow = pw; g.Hc = Hc;
+      g.Nimg = N; g.Hout = H; g.Wout = W;
+      CUtensorMap ta;
+      if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
+      EpiArgs e{dx, nullptr, nullptr, 0, 0, error_flag, g_trace};
+      if (int rc = dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream)) return rc;
+    }
+  return 0;
+}
+
 // dgrad (stride 1): dx[N][H][W][Cin] from dy[N][P][Q][Cout] and packed_bwd[tap][Cin][Cout].
 PDL_API int pdl_tc_conv2d_dgrad(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                                 int pad, int* error_flag, cudaStream_t stream) {
-  TcGeom g{};
-  const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
-  const int ng = n_gemm_for(Cin);
-  if (Cout % 32 || !ng) { pdl_set_error("tc_conv dgrad: unsupported channels %d -> %d", Cout, Cin); return -3; }
-  if (!choose_box(H, W, 0, &g)) { pdl_set_error("tc_conv dgrad: no tile for %dx%d", H, W); return -4; }
-  g.n_tiles = Cin / ng; g.ldc = Cin;
-  g.num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * g.n_tiles;
-  // dx[h, w] = sum_{r,s} dy[h + pad - r, w + pad - s] * w[r, s]
-  g.R = KH; g.S = KW; g.kchunks = Cout / 32; g.a_w0 = pad; g.a_h0 = pad; g.tap_sign = -1; g.Nimg = N; g.Hout = H; g.Wout = W;
-  CUtensorMap ta, tb;
-  if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
-  if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, ng)) return rc;
-  EpiArgs e{dx, nullptr, nullptr, 0, 0, error_flag, g_trace};
-  return dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream);
+  return pdl_tc_conv2d_dgrad_strided(dy, packed_w_bwd, dx, N, H, W, Cin, Cout, KH, KW, 1, pad, error_flag, stream);
 }

@@ -29,7 +29,7 @@ struct WgGeom {
   int units;             // N * strips  (K work items)
   int units_per_cta;     // K split
   int S;                 // taps per filter row (= taps handled by one CTA, <= 3)
-  int pad;
+  int pad, stride;
   int layout_type, lbo, sbo, tma_swizzle;  // descriptor knobs (defaults set on the host)
   int Cin, Cout, cin_tiles;  // full channel counts; blockIdx.z = cout_tile * cin_tiles + cin_tile
 };
@@ -97,7 +97,7 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
         for (int c = 0; c < A_CHUNKS; ++c) tc::tma_load_4d(base + c * chunk_bytes, &tmDy, &full[stage], co0 + c * 32, 0, h0, n);
         for (int s = 0; s < g.S; ++s)
           for (int c = 0; c < B_CHUNKS; ++c)
-            tc::tma_load_4d(base + a_bytes + s * b_tap_bytes + c * chunk_bytes, &tmX, &full[stage], ci0 + c * 32, s - g.pad, h0 + tap_row - g.pad, n);
+            tc::tma_load_4d(base + a_bytes + s * b_tap_bytes + c * chunk_bytes, &tmX, &full[stage], ci0 + c * 32, s - g.pad, h0 * g.stride + tap_row - g.pad, n);
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
@@ -200,13 +200,13 @@ EncodeTiledFn encode_tiled_wg() {
   }
   return fn;
 }
-int act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int bw, int bh, int swizzle) {
+int act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int bw, int bh, int swizzle, int stride) {
   EncodeTiledFn enc = encode_tiled_wg();
   if (!enc) { pdl_set_error("cuTensorMapEncodeTiled is not available"); return -1; }
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t strides[3] = {(cuuint64_t)C * 4, (cuuint64_t)W * C * 4, (cuuint64_t)H * W * C * 4};
-  cuuint32_t box[4] = {32, (cuuint32_t)bw, (cuuint32_t)bh, 1};
-  cuuint32_t es[4] = {1, 1, 1, 1};
+  cuuint32_t box[4] = {32, (cuuint32_t)(bw * stride), (cuuint32_t)(bh * stride), 1};  // traversal stride keeps bw x bh pixels
+  cuuint32_t es[4] = {1, (cuuint32_t)stride, (cuuint32_t)stride, 1};
   CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(base), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    static_cast<CUtensorMapSwizzle>(swizzle), CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(wgrad operand) failed: %d", (int)r); return -2; }
@@ -238,7 +238,7 @@ bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KH, int KW, int pad
   if (splits > g->units) splits = g->units;
   if (splits < 1) splits = 1;
   g->units_per_cta = (g->units + splits - 1) / splits;
-  g->S = KW; g->pad = pad;
+  g->S = KW; g->pad = pad; g->stride = 1;
   g->layout_type = env_int("PDL_WG_LT", 1);   // SWIZZLE_128B_BASE32B
   g->lbo = env_int("PDL_WG_LBO", 0);          // 0 = distance between 32-channel chunks
   g->sbo = env_int("PDL_WG_SBO", 512);        // 4-row K atoms, dense
@@ -265,27 +265,40 @@ int launch_wg(const CUtensorMap& a, const CUtensorMap& b, const WgGeom& g, int K
 }  // namespace
 
 PDL_API int pdl_tc_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
-  if (stride != 1) return 0;
+  if (stride != 1 && stride != 2) return 0;
   WgGeom g{};
-  return wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KH, KW, pad, &g) ? 1 : 0;
+  return wg_geometry(N, (H + 2 * pad - KH) / stride + 1, (W + 2 * pad - KW) / stride + 1, Cin, Cout, KH, KW, pad, &g) ? 1 : 0;
 }
 
-PDL_API long long pdl_tc_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad) {
+PDL_API long long pdl_tc_wgrad_scratch_bytes_strided(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
   WgGeom g{};
-  if (!wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KH, KW, pad, &g)) return 0;
+  if (!wg_geometry(N, (H + 2 * pad - KH) / stride + 1, (W + 2 * pad - KW) / stride + 1, Cin, Cout, KH, KW, pad, &g)) return 0;
   return static_cast<long long>(wg_splits(g)) * KH * KW * Cout * Cin * sizeof(float);
 }
+PDL_API long long pdl_tc_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad) {
+  return pdl_tc_wgrad_scratch_bytes_strided(N, H, W, Cin, Cout, KH, KW, 1, pad);
+}
 
-// x[N][H][W][Cin], dy[N][P][Q][Cout] (NHWC) -> dw[Cout][Cin][KH][KW]
+// x[N][H][W][Cin], dy[N][P][Q][Cout] (NHWC) -> dw[Cout][Cin][KH][KW], convolution stride 1 or 2
 // (+ db[Cout] = fixed-order sum of db_partial[db_blocks][Cout] when db != nullptr).
+PDL_API int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks,
+                                        float* scratch, int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad,
+                                        int* error_flag, cudaStream_t stream);
 PDL_API int pdl_tc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch,
                                 int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad, int* error_flag, cudaStream_t stream) {
+  return pdl_tc_conv2d_wgrad_strided(x, dy, dw, db, db_partial, db_blocks, scratch, N, H, W, Cin, Cout, KH, KW, 1, pad, error_flag, stream);
+}
+PDL_API int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks,
+                                        float* scratch, int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad,
+                                        int* error_flag, cudaStream_t stream) {
   WgGeom g{};
-  const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
+  if (stride != 1 && stride != 2) { pdl_set_error("tc wgrad: stride %d is not supported", stride); return -3; }
+  const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
   if (!wg_geometry(N, P, Q, Cin, Cout, KH, KW, pad, &g)) { pdl_set_error("tc wgrad: unsupported shape"); return -3; }
+  g.stride = stride;
   CUtensorMap ta, tb;
-  if (int rc = act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.tma_swizzle)) return rc;
-  if (int rc = act_map(&tb, x, N, H, W, Cin, g.BW, g.BH, g.tma_swizzle)) return rc;
+  if (int rc = act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.tma_swizzle, 1)) return rc;
+  if (int rc = act_map(&tb, x, N, H, W, Cin, g.BW, g.BH, g.tma_swizzle, stride)) return rc;
   int rc = -3;
   const int mt = wg_m_tile(Cout), nt = wg_n_tile(Cin);
   if (mt == 128 && nt == 64) rc = launch_wg<128, 64>(ta, tb, g, KH, scratch, error_flag, stream);

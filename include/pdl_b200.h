@@ -18,6 +18,7 @@ extern "C" {
 
 const char* pdl_last_error(void);
 int pdl_cuda_device_count(void);
+long long pdl_launch_count(void); /* launcher calls made by this process so far (each enqueues >= 1 kernel) */
 
 /* ---- symmetric memory: same-size VMM allocation on every rank, peer-mapped (+ NVSwitch multicast) ----
  * reference: the NCCL communicator behind init_process_group(backend='nccl') (launch_dist.py:49).
@@ -87,12 +88,20 @@ int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed_bwd, in
 /* pool_stride 0: y = conv+bias(+relu); 1|2: fused ReLU + 2x2 max-pool, y/idx are the pooled output and argmax */
 int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin, int Cout,
                       int KH, int KW, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream);
+int pdl_tc_conv2d_fwd_strided(const float* x, const float* packed_w, const float* bias, float* y, int N, int H, int W, int Cin, int Cout, int KH,
+                              int KW, int stride, int pad, int relu, int* error_flag, cudaStream_t stream); /* stride 1 or 2 */
 int pdl_tc_conv2d_dgrad(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
                         int* error_flag, cudaStream_t stream);
 int pdl_tc_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
 long long pdl_tc_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad);
 int pdl_tc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch, int N,
                         int H, int W, int Cin, int Cout, int KH, int KW, int pad, int* error_flag, cudaStream_t stream);
+int pdl_tc_conv2d_dgrad_strided(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                                int stride, int pad, int* error_flag, cudaStream_t stream); /* stride 2 = four parity-class launches */
+long long pdl_tc_wgrad_scratch_bytes_strided(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch,
+                                int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int* error_flag,
+                                cudaStream_t stream); /* stride 1 or 2 */
 void pdl_tc_set_trace(long long* buf); /* profiling aid: clock64() milestones of CTA 0 */
 
 /* ---- fused ConvNet kernels (reference: ConvNet.forward launch_dist.py:35-41 and its autograd) ---- */

@@ -15,6 +15,7 @@ def declare(L):
 
     sig("pdl_last_error", [], c_char_p)
     sig("pdl_cuda_device_count", [])
+    sig("pdl_launch_count", [], LL)
     # symmetric memory
     sig("pdl_symm_multicast_supported", [I])
     sig("pdl_symm_begin", [I, I, I, c_uint64, c_char_p, I, POINTER(P)])
@@ -48,9 +49,13 @@ def declare(L):
     sig("pdl_tc_conv_supported", [I, I, I, I, I, I, I, I, I])
     sig("pdl_tc_pack_weights", [P, P, P, I, I, I, P])
     sig("pdl_tc_conv2d_fwd", [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, P])
+    sig("pdl_tc_conv2d_fwd_strided", [P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv2d_dgrad", [P, P, P, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_wgrad_supported", [I, I, I, I, I, I, I, I, I])
     sig("pdl_tc_wgrad_scratch_bytes", [I, I, I, I, I, I, I, I], LL)
+    sig("pdl_tc_conv2d_dgrad_strided", [P, P, P, I, I, I, I, I, I, I, I, I, P, P])
+    sig("pdl_tc_wgrad_scratch_bytes_strided", [I, I, I, I, I, I, I, I, I], LL)
+    sig("pdl_tc_conv2d_wgrad_strided", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv2d_wgrad", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, P, P])
     # fused ConvNet kernels
     sig("pdl_convnet_pack", [P, P, P, P, P, P, P, P, P])

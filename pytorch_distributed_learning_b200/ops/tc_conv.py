@@ -68,8 +68,8 @@ def conv2d_fwd(x, w, b, y, stride, pad, relu=False):
     if not L.pdl_tc_conv_supported(H, W, Cin, Cout, KH, KW, stride, pad, 0):
         return False
     packed, _ = pack_weights(w, True, False)
-    _ok(L.pdl_tc_conv2d_fwd(_p(x), _p(packed), _p(b), _p(y), None, N, H, W, Cin, Cout, KH, KW, pad, int(relu), 0,
-                            _p(error_flag(x.device)), _stream(x)), "tensor-core conv forward")
+    _ok(L.pdl_tc_conv2d_fwd_strided(_p(x), _p(packed), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, int(relu),
+                                    _p(error_flag(x.device)), _stream(x)), "tensor-core conv forward")
     return True
 
 
@@ -93,15 +93,15 @@ def conv2d_fwd_relu_pool(x, w, b, pool_stride):
 
 
 def conv2d_dgrad(dy, w, dx, stride, pad):
-    if not enabled() or stride != 1:
+    if not enabled() or stride not in (1, 2):
         return False
     N, Cin, H, W = dx.shape
     Cout, _, KH, KW = w.shape
-    if Cout % 32 or not (Cin in (32, 64) or Cin % 128 == 0) or W > 128:
+    if Cout % 32 or not (Cin in (32, 64) or Cin % 128 == 0) or W > 128 * stride:
         return False
     _, packed = pack_weights(w, False, True)
-    _ok(_lib.cuda().pdl_tc_conv2d_dgrad(_p(dy), _p(packed), _p(dx), N, H, W, Cin, Cout, KH, KW, pad, _p(error_flag(dx.device)), _stream(dx)),
-        "tensor-core conv dgrad")
+    _ok(_lib.cuda().pdl_tc_conv2d_dgrad_strided(_p(dy), _p(packed), _p(dx), N, H, W, Cin, Cout, KH, KW, stride, pad,
+                                                _p(error_flag(dx.device)), _stream(dx)), "tensor-core conv dgrad")
     return True
 
 
@@ -115,11 +115,10 @@ def conv2d_wgrad(x, dy, dw, db, stride, pad):
         return False
     from .functional import scratch
 
-    sc = scratch(L.pdl_tc_wgrad_scratch_bytes(N, H, W, Cin, Cout, KH, KW, pad), x.device, "tc_wgrad")
-    x_chw, dy_chw = x, dy
+    sc = scratch(L.pdl_tc_wgrad_scratch_bytes_strided(N, H, W, Cin, Cout, KH, KW, stride, pad), x.device, "tc_wgrad")
     db_part = None
     if db is not None:
         db_part = dy.sum(dim=(0, 2, 3)).reshape(1, Cout).contiguous()  # eager path only; the engine fuses this into pool-backward
-    _ok(L.pdl_tc_conv2d_wgrad(_p(x_chw), _p(dy_chw), _p(dw), _p(db), _p(db_part), 1 if db is not None else 0, _p(sc), N, H, W, Cin, Cout, KH, KW,
-                              pad, _p(error_flag(x.device)), _stream(x)), "tensor-core conv wgrad")
+    _ok(L.pdl_tc_conv2d_wgrad_strided(_p(x), _p(dy), _p(dw), _p(db), _p(db_part), 1 if db is not None else 0, _p(sc), N, H, W, Cin, Cout,
+                                      KH, KW, stride, pad, _p(error_flag(x.device)), _stream(x)), "tensor-core conv wgrad")
     return True

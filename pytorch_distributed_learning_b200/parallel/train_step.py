@@ -36,7 +36,12 @@ class TrainStep:
             return None
         from ..ops.convnet_engine import ConvNetEngine
 
-        return ConvNetEngine.try_create(self.model, self.criterion, self.optimizer)
+        engine = ConvNetEngine.try_create(self.model, self.criterion, self.optimizer)
+        if engine is None:  # any other model: capture the eager iteration (hooks, side stream and all) as one graph
+            from .graph_engine import GenericGraphEngine
+
+            engine = GenericGraphEngine(self.model, self.criterion, self.optimizer)
+        return engine
 
     @property
     def graphed(self):

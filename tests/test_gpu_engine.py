@@ -125,6 +125,36 @@ def test_ddp_world1_b200_backend(ours_optim):
         dist.destroy_process_group()
 
 
+def test_generic_graph_engine_resnet18_matches_eager():
+    """Any model: TrainStep captures the eager iteration (our ops, DDP hooks, fused SGD) into one CUDA graph."""
+    dist = pdl.distributed
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % free_port(), world_size=1, rank=0)
+    try:
+        torch.manual_seed(0)
+        kw = dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)
+        a = pdl.models.resnet18(num_classes=10).cuda()
+        b = copy.deepcopy(a)
+        da = pdl.nn.parallel.DistributedDataParallel(a, device_ids=[0])
+        db = pdl.nn.parallel.DistributedDataParallel(b, device_ids=[0])
+        oa, ob = pdl.optim.SGD(a.parameters(), **kw), pdl.optim.SGD(b.parameters(), **kw)
+        crit = pdl.nn.CrossEntropyLoss()
+        sa = pdl.TrainStep(da, crit, oa)
+        sb = pdl.TrainStep(db, crit, ob, use_graph=False)
+        assert sa.graphed and not sb.graphed
+        g = torch.Generator().manual_seed(3)
+        for _ in range(3):
+            x, y = torch.randn(16, 3, 32, 32, generator=g).cuda(), torch.randint(0, 10, (16,), generator=g).cuda()
+            la, lb = sa(x, y).item(), sb(x, y).item()
+            assert abs(la - lb) <= 1e-3 * max(1.0, abs(lb)), (la, lb)
+        assert sa.kernels_per_step() > 50
+        for (n, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+            torch.testing.assert_close(pa, pb, rtol=1e-3, atol=1e-4, msg=lambda m, n=n: "%s: %s" % (n, m))
+        for (n, ba), (_, bb) in zip(a.named_buffers(), b.named_buffers()):
+            torch.testing.assert_close(ba.float(), bb.float(), rtol=1e-3, atol=1e-4, msg=lambda m, n=n: "%s: %s" % (n, m))
+    finally:
+        dist.destroy_process_group()
+
+
 def test_resnet18_modules_train_step_matches_torchvision():
     import torchvision
 

@@ -116,6 +116,22 @@ def test_tc_wgrad_matches_fp32(case):
     torch.testing.assert_close(db, dy.sum(dim=(0, 2, 3)), rtol=1e-4, atol=1e-3)
 
 
+@pytest.mark.parametrize("case", [(2, 64, 56, 128, 3, 1), (3, 256, 14, 512, 1, 0), (2, 128, 28, 256, 3, 1), (5, 64, 8, 128, 3, 1), (4, 512, 7, 1024, 1, 0)])
+def test_tc_forward_stride2(case):
+    N, Cin, H, Cout, k, pad = case
+    torch.manual_seed(5)
+    x = torch.randn(N, Cin, H, H, device=DEV).contiguous(memory_format=CL)
+    w = torch.randn(Cout, Cin, k, k, device=DEV) * 0.1
+    P = (H + 2 * pad - k) // 2 + 1
+    y = torch.empty((N, Cout, P, P), device=DEV).contiguous(memory_format=CL)
+    assert tc_conv.conv2d_fwd(x, w, None, y, 2, pad)
+    tc_conv.check_errors(DEV)
+    torch.backends.cudnn.allow_tf32 = False
+    ref = F.conv2d(x, w, None, stride=2, padding=pad)
+    torch.backends.cudnn.allow_tf32 = True
+    _tf32_close(y, ref)
+
+
 def test_tc_path_is_used_by_autograd_function():
     torch.manual_seed(4)
     x = torch.randn(4, 32, 13, 13, device=DEV, requires_grad=True)
