@@ -1,15 +1,24 @@
 // BatchNorm2d for the ResNets the reference trains (torchvision resnet18 at example_launch.py:26; ResNet-50
-// per BASELINE.json), NHWC fp32.  Training mode: per-channel batch statistics (single pass, Welford, merged
-// in fixed order => deterministic), normalise + affine (+ optional fused ReLU), running-stat update with the
-// unbiased variance exactly like torch.  Backward: dgamma/dbeta and dx in the standard closed form.
-//   x, y, dy, dx : [M][C] with M = N*H*W rows, channels contiguous
+// per BASELINE.json), NHWC fp32, with the block's ReLU and residual add fused in:
+//     y = act( (x - mean) * invstd * gamma + beta  [+ residual] ),   act = ReLU or identity
+// Training mode: per-channel batch statistics in one pass over x (per-thread shifted sums turned into
+// Welford triples and merged in a fixed order => deterministic), running-stat update with the unbiased
+// variance exactly like torch.  Backward: dgamma/dbeta, dx in the standard closed form and (for the residual
+// form) the gradient of the skip connection, with the ReLU mask recomputed from x (bit-exact: same fmaf,
+// same saved scale/shift) or taken from y when a residual was added.
+//   x, y, dy, dx, residual : [M][C] with M = N*H*W rows, channels contiguous, C % 4 == 0
+//   saved                  : [4][C] = mean, invstd, scale, shift (written by forward, read by backward)
+// Everything is HBM-bound: float4 accesses, >= 8 CTAs per SM worth of splits, no 64-bit division.
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kCG = 32;              // channels per CTA (one 128-byte row segment)
-constexpr int kRL = kThreads / kCG;  // row lanes per CTA
+constexpr int kCG = 32;              // channels per CTA of the statistics kernels (one 128-byte row segment)
+constexpr int kQL = kCG / 4;         // float4 lanes across the channel group
+constexpr int kRL = kThreads / kQL;  // row lanes per CTA
 
 struct Welford { float n, mean, m2; };
 __device__ __forceinline__ Welford merge(Welford a, Welford b) {
@@ -18,55 +27,101 @@ __device__ __forceinline__ Welford merge(Welford a, Welford b) {
   const float n = a.n + b.n, d = b.mean - a.mean;
   return {n, a.mean + d * (b.n / n), a.m2 + b.m2 + d * d * (a.n * b.n / n)};
 }
+__device__ __forceinline__ Welford from_shifted(float n, float pivot, float s, float q) {
+  if (n == 0.f) return {0.f, 0.f, 0.f};
+  const float m = s / n;
+  return {n, pivot + m, fmaxf(q - s * m, 0.f)};
+}
 
 // partial[(split * C + c) * 3 + {0,1,2}] = (count, mean, M2) of x[rows of this split][c]
 __global__ void __launch_bounds__(kThreads) bn_stats_kernel(const float* __restrict__ x, float* __restrict__ partial, long long M, int C,
                                                             long long rows_per_split) {
-  const int cl = threadIdx.x % kCG, rl = threadIdx.x / kCG;
-  const int c = blockIdx.x * kCG + cl;
+  const int ql = threadIdx.x % kQL, rl = threadIdx.x / kQL;
+  const int c = blockIdx.x * kCG + ql * 4;
   const long long r_lo = blockIdx.y * rows_per_split, r_hi = min(M, r_lo + rows_per_split);
-  Welford w{0.f, 0.f, 0.f};
+  __shared__ float shs[kRL][kCG + 1], shq[kRL][kCG + 1], shn[kRL], shk[kCG];
   if (c < C) {
-#pragma unroll 4
+    const float4* xp = reinterpret_cast<const float4*>(x + c);
+    const long long ld = C / 4;
+    // pivot: first row of the split (inside the data range, shared by all row lanes); a trailing split may be empty
+    const float4 k = r_lo < M ? __ldg(xp + r_lo * ld) : make_float4(0.f, 0.f, 0.f, 0.f);
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f), q = s;
+    float n = 0.f;
+#pragma unroll 8
     for (long long r = r_lo + rl; r < r_hi; r += kRL) {
-      const float v = x[r * C + c];
-      w.n += 1.f;
-      const float d = v - w.mean;
-      w.mean += d / w.n;
-      w.m2 += d * (v - w.mean);
+      const float4 v = __ldg(xp + r * ld);
+      const float a = v.x - k.x, b = v.y - k.y, cc = v.z - k.z, d = v.w - k.w;
+      s.x += a; s.y += b; s.z += cc; s.w += d;
+      q.x = fmaf(a, a, q.x); q.y = fmaf(b, b, q.y); q.z = fmaf(cc, cc, q.z); q.w = fmaf(d, d, q.w);
+      n += 1.f;
     }
+    shs[rl][ql * 4 + 0] = s.x; shs[rl][ql * 4 + 1] = s.y; shs[rl][ql * 4 + 2] = s.z; shs[rl][ql * 4 + 3] = s.w;
+    shq[rl][ql * 4 + 0] = q.x; shq[rl][ql * 4 + 1] = q.y; shq[rl][ql * 4 + 2] = q.z; shq[rl][ql * 4 + 3] = q.w;
+    if (ql == 0) shn[rl] = n;
+    if (rl == 0) { shk[ql * 4 + 0] = k.x; shk[ql * 4 + 1] = k.y; shk[ql * 4 + 2] = k.z; shk[ql * 4 + 3] = k.w; }
   }
-  __shared__ Welford sh[kRL][kCG];
-  sh[rl][cl] = w;
   __syncthreads();
-  if (rl == 0 && c < C) {
-    Welford t = sh[0][cl];
+  if (threadIdx.x < kCG && blockIdx.x * kCG + threadIdx.x < C) {  // one warp: fixed-order sums over the row lanes
+    const int ch = threadIdx.x;
+    float n = 0.f, ss = 0.f, qq = 0.f;
 #pragma unroll
-    for (int i = 1; i < kRL; ++i) t = merge(t, sh[i][cl]);
-    float* o = partial + (static_cast<long long>(blockIdx.y) * C + c) * 3;
+    for (int i = 0; i < kRL; ++i) { n += shn[i]; ss += shs[i][ch]; qq += shq[i][ch]; }
+    const Welford t = from_shifted(n, shk[ch], ss, qq);
+    float* o = partial + (static_cast<long long>(blockIdx.y) * C + blockIdx.x * kCG + ch) * 3;
     o[0] = t.n; o[1] = t.mean; o[2] = t.m2;
   }
 }
 
-// Merge the splits per channel; emit mean / invstd / scale / shift; update running stats (torch semantics).
-__global__ void bn_finalize_kernel(const float* __restrict__ partial, int splits, int C, const float* __restrict__ gamma,
-                                   const float* __restrict__ beta, float* __restrict__ running_mean, float* __restrict__ running_var,
-                                   float momentum, float eps, float* __restrict__ save_mean, float* __restrict__ save_invstd,
-                                   float* __restrict__ scale, float* __restrict__ shift) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
-  Welford t{0.f, 0.f, 0.f};
-  for (int s = 0; s < splits; ++s) {
-    const float* p = partial + (static_cast<long long>(s) * C + c) * 3;
-    t = merge(t, Welford{p[0], p[1], p[2]});
+// Merge the splits per channel without per-split divisions: mean = sum(n_i mean_i) / n, then
+// M2 = sum(M2_i + n_i (mean_i - mean)^2).  32 channels x 32 slices of the split list per CTA, fixed order.
+constexpr int kFinSlices = 32;
+__global__ void __launch_bounds__(kCG * kFinSlices) bn_finalize_kernel(const float* __restrict__ partial, int splits, int C,
+                                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                                       float* __restrict__ running_mean, float* __restrict__ running_var,
+                                                                       float momentum, float eps, float* __restrict__ saved) {
+  const int ch = threadIdx.x % kCG, sl = threadIdx.x / kCG;
+  const int c = blockIdx.x * kCG + ch;
+  __shared__ float sh_a[kFinSlices][kCG + 1], sh_b[kFinSlices][kCG + 1];
+  float sn = 0.f, sm = 0.f;
+  if (c < C) {
+#pragma unroll 4
+    for (int s = sl; s < splits; s += kFinSlices) {
+      const float* p = partial + (static_cast<long long>(s) * C + c) * 3;
+      sn += p[0];
+      sm = fmaf(p[0], p[1], sm);
+    }
   }
+  sh_a[sl][ch] = sn; sh_b[sl][ch] = sm;
+  __syncthreads();
+  float n = 0.f, m = 0.f;
+#pragma unroll
+  for (int i = 0; i < kFinSlices; ++i) { n += sh_a[i][ch]; m += sh_b[i][ch]; }
+  const float mean = m / n;
+  __syncthreads();
+  float m2 = 0.f;
+  if (c < C) {
+#pragma unroll 4
+    for (int s = sl; s < splits; s += kFinSlices) {
+      const float* p = partial + (static_cast<long long>(s) * C + c) * 3;
+      const float d = p[1] - mean;
+      m2 += fmaf(p[0] * d, d, p[2]);
+    }
+  }
+  sh_a[sl][ch] = m2;
+  __syncthreads();
+  if (sl != 0 || c >= C) return;
+  m2 = 0.f;
+#pragma unroll
+  for (int i = 0; i < kFinSlices; ++i) m2 += sh_a[i][ch];
+  const Welford t{n, mean, m2};
   const float var = t.m2 / t.n;  // biased: used for normalisation
   const float invstd = rsqrtf(var + eps);
-  save_mean[c] = t.mean;
-  save_invstd[c] = invstd;
   const float g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
-  scale[c] = g * invstd;
-  shift[c] = b - t.mean * g * invstd;
+  const float scale = g * invstd;
+  saved[c] = t.mean;
+  saved[C + c] = invstd;
+  saved[2 * C + c] = scale;
+  saved[3 * C + c] = fmaf(-t.mean, scale, b);
   if (running_mean) {
     const float unbiased = t.n > 1.f ? t.m2 / (t.n - 1.f) : var;
     running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * t.mean;
@@ -80,144 +135,224 @@ __global__ void bn_eval_coeffs_kernel(int C, const float* __restrict__ gamma, co
   if (c >= C) return;
   const float invstd = rsqrtf(rv[c] + eps), g = gamma ? gamma[c] : 1.f, b = beta ? beta[c] : 0.f;
   scale[c] = g * invstd;
-  shift[c] = b - rm[c] * g * invstd;
+  shift[c] = fmaf(-rm[c], g * invstd, b);
 }
 
-// y = x * scale[c] + shift[c]  (+ ReLU); C % 4 == 0
-__global__ void __launch_bounds__(kThreads) bn_apply_kernel(const float4* __restrict__ x, float4* __restrict__ y, const float* __restrict__ scale,
-                                                            const float* __restrict__ shift, long long total4, int C4, int relu) {
+__device__ __forceinline__ int quad_channel(long long i, int C4) {
+  // 32-bit modulo whenever the index fits (64-bit division is ~10x slower and would dominate the kernel)
+  return 4 * ((i >> 32) == 0 ? static_cast<int>(static_cast<unsigned>(i) % static_cast<unsigned>(C4)) : static_cast<int>(i % C4));
+}
+
+// y = act(x * scale[c] + shift[c] [+ res])
+template <bool kRelu, bool kRes>
+__global__ void __launch_bounds__(kThreads) bn_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ res, float4* __restrict__ y,
+                                                            const float* __restrict__ scale, const float* __restrict__ shift, long long total4,
+                                                            int C4) {
   const long long i = blockIdx.x * static_cast<long long>(kThreads) + threadIdx.x;
   if (i >= total4) return;
-  const int c = static_cast<int>(i % C4) * 4;
+  const int c = quad_channel(i, C4);
   const float4 v = x[i], s = *reinterpret_cast<const float4*>(scale + c), h = *reinterpret_cast<const float4*>(shift + c);
   float4 o = make_float4(fmaf(v.x, s.x, h.x), fmaf(v.y, s.y, h.y), fmaf(v.z, s.z, h.z), fmaf(v.w, s.w, h.w));
-  if (relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+  if (kRes) { const float4 r = res[i]; o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
+  if (kRelu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
   y[i] = o;
 }
 
-// partial[(split * C + c) * 2 + {0,1}] = (sum dy, sum dy * xhat) over the rows of the split
+// The gradient that reaches the normalisation: dy through the activation.  kMask 0: no activation; 1: ReLU mask
+// recomputed from x (no residual); 2: ReLU mask from the stored output y.
+template <int kMask>
+__device__ __forceinline__ float4 act_grad(float4 g, float4 v, float4 yv, float4 s, float4 h) {
+  if (kMask == 1) {
+    g.x = fmaf(v.x, s.x, h.x) > 0.f ? g.x : 0.f; g.y = fmaf(v.y, s.y, h.y) > 0.f ? g.y : 0.f;
+    g.z = fmaf(v.z, s.z, h.z) > 0.f ? g.z : 0.f; g.w = fmaf(v.w, s.w, h.w) > 0.f ? g.w : 0.f;
+  } else if (kMask == 2) {
+    g.x = yv.x > 0.f ? g.x : 0.f; g.y = yv.y > 0.f ? g.y : 0.f; g.z = yv.z > 0.f ? g.z : 0.f; g.w = yv.w > 0.f ? g.w : 0.f;
+  }
+  return g;
+}
+
+// partial[(split * C + c) * 2 + {0,1}] = (sum g, sum g * xhat) over the rows of the split
+template <int kMask>
 __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __restrict__ x, const float* __restrict__ dy,
-                                                                const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                                const float* __restrict__ y, const float* __restrict__ saved,
                                                                 float* __restrict__ partial, long long M, int C, long long rows_per_split) {
-  const int cl = threadIdx.x % kCG, rl = threadIdx.x / kCG;
-  const int c = blockIdx.x * kCG + cl;
+  const int ql = threadIdx.x % kQL, rl = threadIdx.x / kQL;
+  const int c = blockIdx.x * kCG + ql * 4;
   const long long r_lo = blockIdx.y * rows_per_split, r_hi = min(M, r_lo + rows_per_split);
-  float s1 = 0.f, s2 = 0.f;
+  __shared__ float a1[kRL][kCG + 1], a2[kRL][kCG + 1];
   if (c < C) {
-    const float mu = mean[c], is = invstd[c];
+    const long long ld = C / 4;
+    const float4* xp = reinterpret_cast<const float4*>(x + c);
+    const float4* gp = reinterpret_cast<const float4*>(dy + c);
+    const float4* yp = reinterpret_cast<const float4*>((kMask == 2 ? y : x) + c);
+    const float4 mu = *reinterpret_cast<const float4*>(saved + c), is = *reinterpret_cast<const float4*>(saved + C + c);
+    const float4 sc = *reinterpret_cast<const float4*>(saved + 2 * C + c), sf = *reinterpret_cast<const float4*>(saved + 3 * C + c);
+    float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f), s2 = s1;
 #pragma unroll 4
     for (long long r = r_lo + rl; r < r_hi; r += kRL) {
-      const float g = dy[r * C + c];
-      s1 += g;
-      s2 = fmaf(g, (x[r * C + c] - mu) * is, s2);
+      const float4 v = __ldg(xp + r * ld);
+      float4 g = __ldg(gp + r * ld);
+      float4 yv = v;
+      if (kMask == 2) yv = __ldg(yp + r * ld);
+      g = act_grad<kMask>(g, v, yv, sc, sf);
+      s1.x += g.x; s1.y += g.y; s1.z += g.z; s1.w += g.w;
+      s2.x = fmaf(g.x, (v.x - mu.x) * is.x, s2.x); s2.y = fmaf(g.y, (v.y - mu.y) * is.y, s2.y);
+      s2.z = fmaf(g.z, (v.z - mu.z) * is.z, s2.z); s2.w = fmaf(g.w, (v.w - mu.w) * is.w, s2.w);
     }
+    a1[rl][ql * 4 + 0] = s1.x; a1[rl][ql * 4 + 1] = s1.y; a1[rl][ql * 4 + 2] = s1.z; a1[rl][ql * 4 + 3] = s1.w;
+    a2[rl][ql * 4 + 0] = s2.x; a2[rl][ql * 4 + 1] = s2.y; a2[rl][ql * 4 + 2] = s2.z; a2[rl][ql * 4 + 3] = s2.w;
   }
-  __shared__ float a1[kRL][kCG], a2[kRL][kCG];
-  a1[rl][cl] = s1; a2[rl][cl] = s2;
   __syncthreads();
-  if (rl == 0 && c < C) {
-    float t1 = 0.f, t2 = 0.f;
+  const int ch = threadIdx.x % kCG, grp = threadIdx.x / kCG;
+  if (grp < 2 && blockIdx.x * kCG + ch < C) {  // warp 0 sums a1, warp 1 sums a2, both in row-lane order
+    float t = 0.f;
 #pragma unroll
-    for (int i = 0; i < kRL; ++i) { t1 += a1[i][cl]; t2 += a2[i][cl]; }
-    float* o = partial + (static_cast<long long>(blockIdx.y) * C + c) * 2;
-    o[0] = t1; o[1] = t2;
+    for (int i = 0; i < kRL; ++i) t += grp == 0 ? a1[i][ch] : a2[i][ch];
+    partial[(static_cast<long long>(blockIdx.y) * C + blockIdx.x * kCG + ch) * 2 + grp] = t;
   }
 }
 
-// dgamma, dbeta and the per-channel coefficients of dx = a*dy + b*x + d
-__global__ void bn_bwd_finalize_kernel(const float* __restrict__ partial, int splits, int C, float M, const float* __restrict__ gamma,
-                                       const float* __restrict__ mean, const float* __restrict__ invstd, float* __restrict__ dgamma,
-                                       float* __restrict__ dbeta, float* __restrict__ ca, float* __restrict__ cb, float* __restrict__ cd) {
-  const int c = blockIdx.x * blockDim.x + threadIdx.x;
-  if (c >= C) return;
+// dgamma, dbeta and the per-channel coefficients of dx = a*g + b*x + d
+__global__ void __launch_bounds__(kCG * kFinSlices) bn_bwd_finalize_kernel(const float* __restrict__ partial, int splits, int C, float M,
+                                                                   const float* __restrict__ gamma, const float* __restrict__ saved,
+                                                                   float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                                   float* __restrict__ coef) {
+  const int ch = threadIdx.x % kCG, sl = threadIdx.x / kCG;
+  const int c = blockIdx.x * kCG + ch;
+  __shared__ float h1[kFinSlices][kCG + 1], h2[kFinSlices][kCG + 1];
   float s1 = 0.f, s2 = 0.f;
-  for (int s = 0; s < splits; ++s) { s1 += partial[(static_cast<long long>(s) * C + c) * 2]; s2 += partial[(static_cast<long long>(s) * C + c) * 2 + 1]; }
+  if (c < C) {
+#pragma unroll 4
+    for (int s = sl; s < splits; s += kFinSlices) {
+      const float2 p = *reinterpret_cast<const float2*>(partial + (static_cast<long long>(s) * C + c) * 2);
+      s1 += p.x; s2 += p.y;
+    }
+  }
+  h1[sl][ch] = s1; h2[sl][ch] = s2;
+  __syncthreads();
+  if (sl != 0 || c >= C) return;
+#pragma unroll
+  for (int i = 1; i < kFinSlices; ++i) { s1 += h1[i][ch]; s2 += h2[i][ch]; }
   if (dgamma) dgamma[c] = s2;
   if (dbeta) dbeta[c] = s1;
   // dx = g*is * (dy - s1/M - xhat * s2/M),  xhat = (x - mu) * is
-  const float g = gamma ? gamma[c] : 1.f, is = invstd[c], mu = mean[c];
+  const float g = gamma ? gamma[c] : 1.f, mu = saved[c], is = saved[C + c];
   const float a = g * is, k = a * is * s2 / M;
-  ca[c] = a;
-  cb[c] = -k;
-  cd[c] = -a * s1 / M + k * mu;
+  coef[c] = a;
+  coef[C + c] = -k;
+  coef[2 * C + c] = -a * s1 / M + k * mu;
 }
 
-__global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ dy, float4* __restrict__ dx,
-                                                                const float* __restrict__ ca, const float* __restrict__ cb,
-                                                                const float* __restrict__ cd, long long total4, int C4) {
+template <int kMask, bool kRes>
+__global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ dy,
+                                                                const float4* __restrict__ y, float4* __restrict__ dx, float4* __restrict__ dres,
+                                                                const float* __restrict__ coef, const float* __restrict__ saved,
+                                                                long long total4, int C4) {
   const long long i = blockIdx.x * static_cast<long long>(kThreads) + threadIdx.x;
   if (i >= total4) return;
-  const int c = static_cast<int>(i % C4) * 4;
-  const float4 v = x[i], g = dy[i];
-  const float4 a = *reinterpret_cast<const float4*>(ca + c), b = *reinterpret_cast<const float4*>(cb + c), d = *reinterpret_cast<const float4*>(cd + c);
+  const int c = quad_channel(i, C4), C = 4 * C4;
+  const float4 v = x[i];
+  float4 g = dy[i], yv = v;
+  if (kMask == 2) yv = y[i];
+  if (kMask != 0) {
+    const float4 sc = *reinterpret_cast<const float4*>(saved + 2 * C + c), sf = *reinterpret_cast<const float4*>(saved + 3 * C + c);
+    g = act_grad<kMask>(g, v, yv, sc, sf);
+  }
+  const float4 a = *reinterpret_cast<const float4*>(coef + c), b = *reinterpret_cast<const float4*>(coef + C + c),
+               d = *reinterpret_cast<const float4*>(coef + 2 * C + c);
   dx[i] = make_float4(fmaf(a.x, g.x, fmaf(b.x, v.x, d.x)), fmaf(a.y, g.y, fmaf(b.y, v.y, d.y)), fmaf(a.z, g.z, fmaf(b.z, v.z, d.z)),
                       fmaf(a.w, g.w, fmaf(b.w, v.w, d.w)));
+  if (kRes) dres[i] = g;
 }
 
 int choose_splits(long long M, int C) {
   const int cgroups = (C + kCG - 1) / kCG;
-  long long s = (4 * 148 + cgroups - 1) / cgroups;
-  const long long by_rows = (M + 63) / 64;
+  long long s = (8 * 148 + cgroups - 1) / cgroups;  // ~8 CTAs per SM in total
+  const long long by_rows = (M + 127) / 128;        // at least 4 rows per thread
   if (s > by_rows) s = by_rows;
   if (s < 1) s = 1;
-  if (s > 64) s = 64;  // the finalize kernel merges the splits serially per channel
+  if (s > 1024) s = 1024;
   return static_cast<int>(s);
+}
+
+int check_c(int C) {
+  if (C % 4) { pdl_set_error("batch norm: channel count %d is not a multiple of 4", C); return -1; }
+  return 0;
+}
+
+template <typename F>
+void launch_apply(F&& f, int relu, bool res) {
+  if (relu) { if (res) f(std::true_type{}, std::true_type{}); else f(std::true_type{}, std::false_type{}); }
+  else      { if (res) f(std::false_type{}, std::true_type{}); else f(std::false_type{}, std::false_type{}); }
+}
+
+void apply(const float* x, const float* residual, float* y, const float* scale, const float* shift, long long M, int C, int relu,
+           cudaStream_t stream) {
+  const long long total4 = M * C / 4;
+  const unsigned blocks = static_cast<unsigned>(pdl_ceil_div(total4, kThreads));
+  launch_apply([&](auto r, auto s) {
+    bn_apply_kernel<decltype(r)::value, decltype(s)::value><<<blocks, kThreads, 0, stream>>>(
+        reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(residual), reinterpret_cast<float4*>(y), scale, shift, total4, C / 4);
+  }, relu, residual != nullptr);
 }
 
 }  // namespace
 
-// floats of scratch the BN entry points need: split partials + 5 per-channel coefficient rows
-PDL_API long long pdl_bn_scratch_floats(long long M, int C) { return static_cast<long long>(choose_splits(M, C)) * C * 3 + 5ll * C; }
+// floats of scratch the BN entry points need: split partials + 3 per-channel coefficient rows
+PDL_API long long pdl_bn_scratch_floats(long long M, int C) { return static_cast<long long>(choose_splits(M, C)) * C * 3 + 3ll * C; }
 
-// Training forward.  save_mean / save_invstd [C] are kept for backward.  relu != 0 fuses the activation.
-PDL_API int pdl_bn_fwd_train(const float* x, const float* gamma, const float* beta, float* running_mean, float* running_var, float momentum,
-                             float eps, float* y, float* save_mean, float* save_invstd, float* scratch, long long M, int C, int relu,
+// Training forward.  saved [4][C] (mean, invstd, scale, shift) is kept for backward.  relu != 0 fuses the
+// activation, residual != nullptr adds the skip connection before it.
+PDL_API int pdl_bn_fwd_train(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean,
+                             float* running_var, float momentum, float eps, float* y, float* saved, float* scratch, long long M, int C, int relu,
                              cudaStream_t stream) {
-  if (C % 4) { pdl_set_error("batch norm: channel count %d is not a multiple of 4", C); return -1; }
+  if (check_c(C)) return -1;
   const int splits = choose_splits(M, C);
   const long long rps = (M + splits - 1) / splits;
-  float* partial = scratch;
-  float* scale = scratch + static_cast<long long>(splits) * C * 3;
-  float* shift = scale + C;
-  bn_stats_kernel<<<dim3((C + kCG - 1) / kCG, splits), kThreads, 0, stream>>>(x, partial, M, C, rps);
-  bn_finalize_kernel<<<(C + 255) / 256, 256, 0, stream>>>(partial, splits, C, gamma, beta, running_mean, running_var, momentum, eps, save_mean,
-                                                          save_invstd, scale, shift);
-  const long long total4 = M * C / 4;
-  bn_apply_kernel<<<pdl_ceil_div(total4, kThreads), kThreads, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), scale,
-                                                                           shift, total4, C / 4, relu);
+  const int cgroups = (C + kCG - 1) / kCG;
+  bn_stats_kernel<<<dim3(cgroups, splits), kThreads, 0, stream>>>(x, scratch, M, C, rps);
+  bn_finalize_kernel<<<cgroups, kCG * kFinSlices, 0, stream>>>(scratch, splits, C, gamma, beta, running_mean, running_var, momentum, eps, saved);
+  apply(x, residual, y, saved + 2ll * C, saved + 3ll * C, M, C, relu, stream);
   PDL_LAUNCH_CHECK();
   return 0;
 }
 
-PDL_API int pdl_bn_fwd_eval(const float* x, const float* gamma, const float* beta, const float* running_mean, const float* running_var, float eps,
-                            float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
-  if (C % 4) { pdl_set_error("batch norm: channel count %d is not a multiple of 4", C); return -1; }
+PDL_API int pdl_bn_fwd_eval(const float* x, const float* residual, const float* gamma, const float* beta, const float* running_mean,
+                            const float* running_var, float eps, float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
+  if (check_c(C)) return -1;
   float* scale = scratch;
   float* shift = scratch + C;
   bn_eval_coeffs_kernel<<<(C + 255) / 256, 256, 0, stream>>>(C, gamma, beta, running_mean, running_var, eps, scale, shift);
-  const long long total4 = M * C / 4;
-  bn_apply_kernel<<<pdl_ceil_div(total4, kThreads), kThreads, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y), scale,
-                                                                           shift, total4, C / 4, relu);
+  apply(x, residual, y, scale, shift, M, C, relu, stream);
   PDL_LAUNCH_CHECK();
   return 0;
 }
 
-// Training backward: dx, dgamma, dbeta from x, dy and the saved statistics.
-PDL_API int pdl_bn_bwd(const float* x, const float* dy, const float* gamma, const float* save_mean, const float* save_invstd, float* dx,
-                       float* dgamma, float* dbeta, float* scratch, long long M, int C, cudaStream_t stream) {
-  if (C % 4) { pdl_set_error("batch norm: channel count %d is not a multiple of 4", C); return -1; }
+// Training backward of y = act(bn(x) [+ residual]): dx, dgamma, dbeta and, when dres != nullptr, the gradient
+// of the residual input (= dy through the activation).  y is only read when relu != 0 and dres != nullptr.
+PDL_API int pdl_bn_bwd(const float* x, const float* dy, const float* y, const float* gamma, const float* saved, float* dx, float* dres,
+                       float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
+  if (check_c(C)) return -1;
   const int splits = choose_splits(M, C);
   const long long rps = (M + splits - 1) / splits;
+  const int cgroups = (C + kCG - 1) / kCG;
   float* partial = scratch;
-  float* ca = scratch + static_cast<long long>(splits) * C * 3;
-  float* cb = ca + C;
-  float* cd = cb + C;
-  bn_bwd_stats_kernel<<<dim3((C + kCG - 1) / kCG, splits), kThreads, 0, stream>>>(x, dy, save_mean, save_invstd, partial, M, C, rps);
-  bn_bwd_finalize_kernel<<<(C + 255) / 256, 256, 0, stream>>>(partial, splits, C, static_cast<float>(M), gamma, save_mean, save_invstd, dgamma, dbeta,
-                                                              ca, cb, cd);
+  float* coef = scratch + static_cast<long long>(splits) * C * 3;
+  const int mask = !relu ? 0 : (dres ? 2 : 1);
+  if (mask == 2 && !y) { pdl_set_error("batch norm backward: the residual+ReLU form needs the forward output"); return -1; }
+  const dim3 grid(cgroups, splits);
+  if (mask == 0) bn_bwd_stats_kernel<0><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps);
+  else if (mask == 1) bn_bwd_stats_kernel<1><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps);
+  else bn_bwd_stats_kernel<2><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps);
+  bn_bwd_finalize_kernel<<<cgroups, kCG * kFinSlices, 0, stream>>>(partial, splits, C, static_cast<float>(M), gamma, saved, dgamma, dbeta, coef);
   const long long total4 = M * C / 4;
-  bn_bwd_apply_kernel<<<pdl_ceil_div(total4, kThreads), kThreads, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(dy),
-                                                                               reinterpret_cast<float4*>(dx), ca, cb, cd, total4, C / 4);
+  const unsigned blocks = static_cast<unsigned>(pdl_ceil_div(total4, kThreads));
+  const float4 *x4 = reinterpret_cast<const float4*>(x), *g4 = reinterpret_cast<const float4*>(dy), *y4 = reinterpret_cast<const float4*>(y);
+  float4 *dx4 = reinterpret_cast<float4*>(dx), *dr4 = reinterpret_cast<float4*>(dres);
+  if (mask == 0 && !dres) bn_bwd_apply_kernel<0, false><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
+  else if (mask == 0) bn_bwd_apply_kernel<0, true><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
+  else if (mask == 1) bn_bwd_apply_kernel<1, false><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
+  else bn_bwd_apply_kernel<2, true><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
   PDL_LAUNCH_CHECK();
   return 0;
 }

@@ -32,6 +32,22 @@ __global__ void add_relu_fwd_kernel(const float* __restrict__ a, const float* __
   if (i < n) y[i] = fmaxf(a[i] + b[i], 0.f);
 }
 
+__global__ void relu_bwd_v4_kernel(const float4* __restrict__ y, const float4* __restrict__ dy, float4* __restrict__ dx, long long n4) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i >= n4) return;
+  const float4 v = y[i], g = dy[i];
+  dx[i] = make_float4(v.x > 0.f ? g.x : 0.f, v.y > 0.f ? g.y : 0.f, v.z > 0.f ? g.z : 0.f, v.w > 0.f ? g.w : 0.f);
+}
+__global__ void add_relu_fwd_v4_kernel(const float4* __restrict__ a, const float4* __restrict__ b, float4* __restrict__ y, long long n4) {
+  long long i = blockIdx.x * static_cast<long long>(blockDim.x) + threadIdx.x;
+  if (i >= n4) return;
+  const float4 u = a[i], v = b[i];
+  y[i] = make_float4(fmaxf(u.x + v.x, 0.f), fmaxf(u.y + v.y, 0.f), fmaxf(u.z + v.z, 0.f), fmaxf(u.w + v.w, 0.f));
+}
+inline bool aligned16(const void* a, const void* b, const void* c) {
+  return ((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b) | reinterpret_cast<uintptr_t>(c)) & 15) == 0;
+}
+
 // y[n,p,q,c] = max over the window; idx = r*k+s of the FIRST maximum in scan order (torch's tie rule).
 __global__ void maxpool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ idx, int N, int H, int W, int C,
                                    int k, int stride, int pad, int P, int Q) {
@@ -84,6 +100,70 @@ __global__ void maxpool_bwd_kernel(const float* __restrict__ dy, const uint8_t* 
       if (q >= Q) continue;
       long long o = ((static_cast<long long>(n) * P + p) * Q + q) * C + c;
       if (idx[o] == r * k + s && (!fuse_relu || pooled[o] > 0.f)) acc += dy[o];
+    }
+  }
+  dx[i] = acc;
+}
+
+// Vector forms of the two pool kernels for C % 4 == 0 and < 2^31 elements: one thread per 4 channels,
+// 32-bit index arithmetic (the scalar kernels above spend their time in 64-bit divisions).
+__device__ __forceinline__ void take_max(float v, int code, float& best, int& arg) {
+  if (arg < 0 || v > best || v != v) { best = v; arg = code; }
+}
+__global__ void __launch_bounds__(kThreads) maxpool_fwd_v4_kernel(const float4* __restrict__ x, float4* __restrict__ y, uchar4* __restrict__ idx,
+                                                                  unsigned total4, int H, int W, int C4, int k, int stride, int pad, int P, int Q) {
+  const unsigned i = blockIdx.x * kThreads + threadIdx.x;
+  if (i >= total4) return;
+  const unsigned c = i % C4;
+  unsigned t = i / C4;
+  const int q = t % Q; t /= Q;
+  const int p = t % P;
+  const unsigned n = t / P;
+  float4 best = make_float4(-INFINITY, -INFINITY, -INFINITY, -INFINITY);
+  int a0 = -1, a1 = -1, a2 = -1, a3 = -1;
+  for (int r = 0; r < k; ++r) {
+    const int h = p * stride - pad + r;
+    if (h < 0 || h >= H) continue;
+    for (int s = 0; s < k; ++s) {
+      const int w = q * stride - pad + s;
+      if (w < 0 || w >= W) continue;
+      const float4 v = __ldg(x + ((n * H + h) * W + w) * C4 + c);
+      const int code = r * k + s;
+      take_max(v.x, code, best.x, a0); take_max(v.y, code, best.y, a1); take_max(v.z, code, best.z, a2); take_max(v.w, code, best.w, a3);
+    }
+  }
+  y[i] = best;
+  idx[i] = make_uchar4(a0, a1, a2, a3);
+}
+__global__ void __launch_bounds__(kThreads) maxpool_bwd_v4_kernel(const float4* __restrict__ dy, const uchar4* __restrict__ idx,
+                                                                  const float4* __restrict__ pooled, float4* __restrict__ dx, unsigned total4, int H,
+                                                                  int W, int C4, int k, int stride, int pad, int P, int Q, int fuse_relu) {
+  const unsigned i = blockIdx.x * kThreads + threadIdx.x;
+  if (i >= total4) return;
+  const unsigned c = i % C4;
+  unsigned t = i / C4;
+  const int w = t % W; t /= W;
+  const int h = t % H;
+  const unsigned n = t / H;
+  float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int r = 0; r < k; ++r) {
+    const int ph = h + pad - r;
+    if (ph < 0 || ph % stride) continue;
+    const int p = ph / stride;
+    if (p >= P) continue;
+    for (int s = 0; s < k; ++s) {
+      const int qw = w + pad - s;
+      if (qw < 0 || qw % stride) continue;
+      const int q = qw / stride;
+      if (q >= Q) continue;
+      const unsigned o = ((n * P + p) * Q + q) * C4 + c;
+      const uchar4 a = __ldg(idx + o);
+      const float4 g = __ldg(dy + o);
+      const int code = r * k + s;
+      float4 pv = make_float4(1.f, 1.f, 1.f, 1.f);
+      if (fuse_relu) pv = __ldg(pooled + o);
+      acc.x += (a.x == code && pv.x > 0.f) ? g.x : 0.f; acc.y += (a.y == code && pv.y > 0.f) ? g.y : 0.f;
+      acc.z += (a.z == code && pv.z > 0.f) ? g.z : 0.f; acc.w += (a.w == code && pv.w > 0.f) ? g.w : 0.f;
     }
   }
   dx[i] = acc;
@@ -202,19 +282,29 @@ PDL_API int pdl_relu_fwd(const float* x, float* y, long long n, cudaStream_t str
   return 0;
 }
 PDL_API int pdl_relu_bwd(const float* y, const float* dy, float* dx, long long n, cudaStream_t stream) {
-  if (n) relu_bwd_kernel<<<launch_1d(n), kThreads, 0, stream>>>(y, dy, dx, n);
+  if (n && n % 4 == 0 && aligned16(y, dy, dx))
+    relu_bwd_v4_kernel<<<launch_1d(n / 4), kThreads, 0, stream>>>(reinterpret_cast<const float4*>(y), reinterpret_cast<const float4*>(dy),
+                                                                  reinterpret_cast<float4*>(dx), n / 4);
+  else if (n) relu_bwd_kernel<<<launch_1d(n), kThreads, 0, stream>>>(y, dy, dx, n);
   PDL_LAUNCH_CHECK();
   return 0;
 }
 PDL_API int pdl_add_relu_fwd(const float* a, const float* b, float* y, long long n, cudaStream_t stream) {
-  if (n) add_relu_fwd_kernel<<<launch_1d(n), kThreads, 0, stream>>>(a, b, y, n);
+  if (n && n % 4 == 0 && aligned16(a, b, y))
+    add_relu_fwd_v4_kernel<<<launch_1d(n / 4), kThreads, 0, stream>>>(reinterpret_cast<const float4*>(a), reinterpret_cast<const float4*>(b),
+                                                                      reinterpret_cast<float4*>(y), n / 4);
+  else if (n) add_relu_fwd_kernel<<<launch_1d(n), kThreads, 0, stream>>>(a, b, y, n);
   PDL_LAUNCH_CHECK();
   return 0;
 }
 PDL_API int pdl_maxpool_fwd(const float* x, float* y, uint8_t* idx, int N, int H, int W, int C, int k, int stride, int pad, cudaStream_t stream) {
   int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
   long long total = static_cast<long long>(N) * P * Q * C;
-  if (total) maxpool_fwd_kernel<<<launch_1d(total), kThreads, 0, stream>>>(x, y, idx, N, H, W, C, k, stride, pad, P, Q);
+  if (total && C % 4 == 0 && static_cast<long long>(N) * H * W * C < (1ll << 31)) {
+    maxpool_fwd_v4_kernel<<<launch_1d(total / 4), kThreads, 0, stream>>>(reinterpret_cast<const float4*>(x), reinterpret_cast<float4*>(y),
+                                                                         reinterpret_cast<uchar4*>(idx), static_cast<unsigned>(total / 4), H, W,
+                                                                         C / 4, k, stride, pad, P, Q);
+  } else if (total) maxpool_fwd_kernel<<<launch_1d(total), kThreads, 0, stream>>>(x, y, idx, N, H, W, C, k, stride, pad, P, Q);
   PDL_LAUNCH_CHECK();
   return 0;
 }
@@ -222,7 +312,11 @@ PDL_API int pdl_maxpool_bwd(const float* dy, const uint8_t* idx, const float* po
                             int pad, int fuse_relu, cudaStream_t stream) {
   int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
   long long total = static_cast<long long>(N) * H * W * C;
-  if (total) maxpool_bwd_kernel<<<launch_1d(total), kThreads, 0, stream>>>(dy, idx, pooled, dx, N, H, W, C, k, stride, pad, P, Q, fuse_relu);
+  if (total && C % 4 == 0 && total < (1ll << 31)) {
+    maxpool_bwd_v4_kernel<<<launch_1d(total / 4), kThreads, 0, stream>>>(
+        reinterpret_cast<const float4*>(dy), reinterpret_cast<const uchar4*>(idx), reinterpret_cast<const float4*>(pooled),
+        reinterpret_cast<float4*>(dx), static_cast<unsigned>(total / 4), H, W, C / 4, k, stride, pad, P, Q, fuse_relu);
+  } else if (total) maxpool_bwd_kernel<<<launch_1d(total), kThreads, 0, stream>>>(dy, idx, pooled, dx, N, H, W, C, k, stride, pad, P, Q, fuse_relu);
   PDL_LAUNCH_CHECK();
   return 0;
 }

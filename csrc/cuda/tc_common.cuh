@@ -132,6 +132,23 @@ __host__ __device__ constexpr uint32_t idesc_tf32(int M, int N, int a_mn_major, 
          (static_cast<uint32_t>(N >> 3) << 17) | (static_cast<uint32_t>(M >> 4) << 24);
 }
 
+// Small-Cin ("stem") convolutions, Cin <= 4 and KW <= 8: the input is copied once into a zero-padded NHWC4
+// image xp[N][Hp][Wp][4].  There the KW taps x 4 channels that output pixel (p, q) needs from filter row r are
+// 32 CONTIGUOUS floats starting at pixel (p*stride + r, q*stride), so a tensor map whose W stride is `stride`
+// pixels (16*stride bytes: consecutive rows overlap) presents every filter row as an ordinary 32-wide K chunk.
+struct StemDims { int P, Q, Hp, Wp; };
+inline StemDims stem_dims(int H, int W, int KH, int KW, int stride, int pad) {
+  StemDims d;
+  d.P = (H + 2 * pad - KH) / stride + 1;
+  d.Q = (W + 2 * pad - KW) / stride + 1;
+  d.Hp = H + 2 * pad;
+  if (d.Hp < (d.P - 1) * stride + KH) d.Hp = (d.P - 1) * stride + KH;
+  d.Wp = W + 2 * pad;
+  if (d.Wp < (d.Q - 1) * stride + 8) d.Wp = (d.Q - 1) * stride + 8;  // the last window reads 8 pixels
+  d.Wp = (d.Wp + 3) / 4 * 4;
+  return d;
+}
+
 __device__ __forceinline__ bool elect_one() {
   uint32_t pred;
   asm volatile(

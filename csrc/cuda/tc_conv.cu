@@ -466,3 +466,103 @@ PDL_API int pdl_tc_conv2d_dgrad(const float* dy, const float* packed_w_bwd, floa
                                 int pad, int* error_flag, cudaStream_t stream) {
   return pdl_tc_conv2d_dgrad_strided(dy, packed_w_bwd, dx, N, H, W, Cin, Cout, KH, KW, 1, pad, error_flag, stream);
 }
+
+// ---------------------------------------------------------------------------------------------------------
+// Small-Cin ("stem") convolutions on the tensor cores: the 7x7/2 3-channel first layer of the ResNets
+// (reference: torchvision resnet18's conv1, example_launch.py:26).  See tc::stem_dims for the layout trick.
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+
+// x (any strides, element units) -> xp[N][Hp][Wp][4], zero halo and zero 4th channel, TF32-rounded
+__global__ void __launch_bounds__(256) stem_pad_kernel(const float* __restrict__ x, long long sn, long long sc, long long sh, long long sw,
+                                                       float4* __restrict__ xp, unsigned total, int C, int H, int W, int Hp, int Wp, int pad) {
+  const unsigned i = blockIdx.x * 256u + threadIdx.x;
+  if (i >= total) return;
+  const int w = i % Wp;
+  unsigned t = i / Wp;
+  const int h = t % Hp;
+  const unsigned n = t / Hp;
+  const int ih = h - pad, iw = w - pad;
+  float v[4] = {0.f, 0.f, 0.f, 0.f};
+  if (ih >= 0 && ih < H && iw >= 0 && iw < W) {
+    const float* src = x + n * sn + ih * sh + iw * sw;
+#pragma unroll
+    for (int c = 0; c < 4; ++c)
+      if (c < C) v[c] = round_tf32(__ldg(src + c * sc));
+  }
+  xp[i] = make_float4(v[0], v[1], v[2], v[3]);
+}
+
+// w[co][c][r][s] -> pk[r][co][s*4 + c] (zero where s >= KW or c >= Cin), TF32-rounded
+__global__ void stem_pack_weights_kernel(const float* __restrict__ w, float* __restrict__ pk, int Cout, int Cin, int KH, int KW) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= KH * Cout * 32) return;
+  const int j = i % 32, co = (i / 32) % Cout, r = i / (32 * Cout);
+  const int s = j / 4, c = j % 4;
+  pk[i] = (s < KW && c < Cin) ? round_tf32(w[((co * Cin + c) * KH + r) * KW + s]) : 0.f;
+}
+
+}  // namespace
+
+PDL_API int pdl_tc_stem_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
+  if (Cin < 1 || Cin > 4 || KW > 8 || KH > 8 || stride < 1 || stride > 2 || !n_gemm_for(Cout)) return 0;
+  const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
+  TcGeom g{};
+  return d.P >= 1 && d.Q >= 1 && choose_box(d.P, d.Q, 0, &g) ? 1 : 0;
+}
+
+// floats of the padded NHWC4 copy of the input
+PDL_API long long pdl_tc_stem_pad_floats(int N, int H, int W, int KH, int KW, int stride, int pad) {
+  const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
+  return 4ll * N * d.Hp * d.Wp;
+}
+
+// x with element strides (sn, sc, sh, sw) -> xp (pdl_tc_stem_pad_floats floats)
+PDL_API int pdl_tc_stem_prepare(const float* x, long long sn, long long sc, long long sh, long long sw, float* xp, int N, int Cin, int H, int W,
+                                int KH, int KW, int stride, int pad, cudaStream_t stream) {
+  const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
+  const long long total = static_cast<long long>(N) * d.Hp * d.Wp;
+  if (total >= (1ll << 31) || Cin > 4) { pdl_set_error("stem conv: input too large or more than 4 channels"); return -3; }
+  stem_pad_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(x, sn, sc, sh, sw, reinterpret_cast<float4*>(xp), static_cast<unsigned>(total), Cin,
+                                                               H, W, d.Hp, d.Wp, pad);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// w[Cout][Cin][KH][KW] -> packed[KH][Cout][32]
+PDL_API int pdl_tc_stem_pack_weights(const float* w, float* packed, int Cout, int Cin, int KH, int KW, cudaStream_t stream) {
+  stem_pack_weights_kernel<<<pdl_ceil_div(KH * Cout * 32, 256), 256, 0, stream>>>(w, packed, Cout, Cin, KH, KW);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// y[N][P][Q][Cout] = conv(x, w) (+ bias, ReLU) from the padded copy and the packed weights.
+PDL_API int pdl_tc_stem_fwd(const float* xp, const float* packed_w, const float* bias, float* y, int N, int H, int W, int Cout, int KH, int KW,
+                            int stride, int pad, int relu, int* error_flag, cudaStream_t stream) {
+  const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
+  TcGeom g{};
+  if (!choose_box(d.P, d.Q, 0, &g)) { pdl_set_error("stem conv: no tile for %dx%d output", d.P, d.Q); return -4; }
+  const int ng = n_gemm_for(Cout);
+  if (!ng) { pdl_set_error("stem conv: unsupported output channels %d", Cout); return -3; }
+  g.in_stride = stride;
+  g.tap_r0 = g.tap_s0 = 0; g.tap_step = 1; g.S_full = 1; g.out_stride = 1; g.out_oh = g.out_ow = 0; g.Hc = d.P;
+  g.n_tiles = Cout / ng; g.ldc = Cout;
+  g.num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * g.n_tiles;
+  g.R = KH; g.S = 1; g.kchunks = 1; g.a_w0 = 0; g.a_h0 = 0; g.tap_sign = 1; g.Nimg = N; g.Hout = d.P; g.Wout = d.Q;
+  EncodeTiledFn enc = encode_tiled();
+  if (!enc) { pdl_set_error("cuTensorMapEncodeTiled is not available"); return -1; }
+  CUtensorMap ta, tb;
+  {
+    // virtual view (32 floats, Q windows, Hp rows, N): window q starts `stride` pixels after window q-1
+    cuuint64_t dims[4] = {32, (cuuint64_t)d.Q, (cuuint64_t)d.Hp, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)16 * stride, (cuuint64_t)d.Wp * 16, (cuuint64_t)d.Hp * d.Wp * 16};
+    cuuint32_t box[4] = {32, (cuuint32_t)g.BW, (cuuint32_t)(g.BH * stride), (cuuint32_t)g.BN};
+    cuuint32_t es[4] = {1, 1, (cuuint32_t)stride, 1};
+    CUresult r = enc(&ta, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(xp), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(stem input, overlapping windows) failed: %d", (int)r); return -2; }
+  }
+  if (int rc = make_weight_map(&tb, packed_w, KH * Cout, 32, ng)) return rc;
+  EpiArgs e{y, nullptr, bias, relu, 0, error_flag, g_trace};
+  return dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream);
+}

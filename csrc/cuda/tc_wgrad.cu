@@ -21,15 +21,16 @@
 namespace {
 
 constexpr int kThreads = 256;
-constexpr int kMaxTapsPerCta = 3;
+constexpr int kMaxTapsPerCta = 7;  // 3 taps of one filter row (generic), or all 7 rows of a small-Cin "stem" filter
 
 struct WgGeom {
   int BW, BH;            // pixel box (BW % 8 == 0), rows = BW*BH in {64, 128}
-  int strips;            // row strips per image
-  int units;             // N * strips  (K work items)
+  int strips, wstrips;   // row strips / column strips per image
+  int units;             // N * strips * wstrips  (K work items)
   int units_per_cta;     // K split
-  int S;                 // taps per filter row (= taps handled by one CTA, <= 3)
-  int pad, stride;
+  int S, RT;             // taps per filter row x filter rows handled by one CTA (S * RT accumulators)
+  int pad, stride;       // stride applies to the row coordinate of x
+  int stride_w;          // multiplier of the column coordinate of x (1 in the stem's virtual layout)
   int layout_type, lbo, sbo, tma_swizzle;  // descriptor knobs (defaults set on the host)
   int Cin, Cout, cin_tiles;  // full channel counts; blockIdx.z = cout_tile * cin_tiles + cin_tile
 };
@@ -55,7 +56,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
   constexpr int A_CHUNKS = M_GEMM / 32, B_CHUNKS = N_GEMM / 32;
   const int a_bytes = A_CHUNKS * chunk_bytes;
   const int b_tap_bytes = B_CHUNKS * chunk_bytes;
-  const int stage_bytes = a_bytes + g.S * b_tap_bytes;
+  const int T = g.S * g.RT;  // accumulators (filter taps) of this CTA
+  const int stage_bytes = a_bytes + T * b_tap_bytes;
   const int stages = (stage_bytes * 4 <= 200 * 1024) ? 4 : (stage_bytes * 3 <= 200 * 1024) ? 3 : 2;
   uint64_t* full = reinterpret_cast<uint64_t*>(smem + stages * stage_bytes);
   uint64_t* empty = full + 4;
@@ -64,7 +66,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
   volatile int* failed = reinterpret_cast<volatile int*>(tmem_slot + 1);
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
-  constexpr uint32_t kCols = (kMaxTapsPerCta * N_GEMM <= 128) ? 128 : 256;
+  const uint32_t need_cols = static_cast<uint32_t>(T * N_GEMM);
+  const uint32_t kCols = need_cols <= 32 ? 32 : need_cols <= 64 ? 64 : need_cols <= 128 ? 128 : need_cols <= 256 ? 256 : 512;
   const int tap_row = blockIdx.x;  // filter row r
   const int split = blockIdx.y;
   const int co0 = (blockIdx.z / g.cin_tiles) * M_GEMM, ci0 = (blockIdx.z % g.cin_tiles) * N_GEMM;  // channel tile origin
@@ -91,13 +94,18 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
       uint32_t phase = 0;
       for (int u = u_begin; u < u_end; ++u) {
         if (!tc::mbar_wait(&empty[stage], phase ^ 1)) { *failed = 1; break; }
-        const int n = u / g.strips, h0 = (u % g.strips) * g.BH;
+        const int per_img = g.strips * g.wstrips;
+        const int n = u / per_img, rem = u % per_img;
+        const int h0 = (rem / g.wstrips) * g.BH, w0 = (rem % g.wstrips) * g.BW;
         uint8_t* base = smem + stage * stage_bytes;
         tc::mbar_expect_tx(&full[stage], static_cast<uint32_t>(stage_bytes));
-        for (int c = 0; c < A_CHUNKS; ++c) tc::tma_load_4d(base + c * chunk_bytes, &tmDy, &full[stage], co0 + c * 32, 0, h0, n);
-        for (int s = 0; s < g.S; ++s)
+        for (int c = 0; c < A_CHUNKS; ++c) tc::tma_load_4d(base + c * chunk_bytes, &tmDy, &full[stage], co0 + c * 32, w0, h0, n);
+        for (int t = 0; t < T; ++t) {
+          const int r = tap_row * g.RT + t / g.S, sx = t % g.S;
           for (int c = 0; c < B_CHUNKS; ++c)
-            tc::tma_load_4d(base + a_bytes + s * b_tap_bytes + c * chunk_bytes, &tmX, &full[stage], ci0 + c * 32, s - g.pad, h0 * g.stride + tap_row - g.pad, n);
+            tc::tma_load_4d(base + a_bytes + t * b_tap_bytes + c * chunk_bytes, &tmX, &full[stage], ci0 + c * 32, w0 * g.stride_w + sx - g.pad,
+                            h0 * g.stride + r - g.pad, n);
+        }
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
@@ -114,9 +122,9 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
         const uint32_t b_addr = a_addr + a_bytes;
         for (int k8 = 0; k8 < rows / 8; ++k8) {  // one MMA = 8 pixels = 8 rows of 128 B
           const uint64_t a_desc = smem_desc_lt(a_addr + k8 * 1024, lbo, sbo, g.layout_type);
-          for (int s = 0; s < g.S; ++s) {
-            const uint64_t b_desc = smem_desc_lt(b_addr + s * b_tap_bytes + k8 * 1024, lbo, sbo, g.layout_type);
-            tc::mma_tf32(tmem_base + s * N_GEMM, a_desc, b_desc, idesc, (u != u_begin) || (k8 != 0));
+          for (int t = 0; t < T; ++t) {
+            const uint64_t b_desc = smem_desc_lt(b_addr + t * b_tap_bytes + k8 * 1024, lbo, sbo, g.layout_type);
+            tc::mma_tf32(tmem_base + t * N_GEMM, a_desc, b_desc, idesc, (u != u_begin) || (k8 != 0));
           }
         }
         tc::mma_commit(&empty[stage]);
@@ -135,9 +143,9 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
     // accumulator row -> output channel: M=128: lane index; M=64: 16 rows per 32-lane quarter
     const int co = (M_GEMM == 128) ? quarter * 32 + lane : quarter * 16 + lane;
     const bool row_valid = (M_GEMM == 128) || lane < 16;
-    for (int s = 0; s < g.S; ++s) {
-      const int tap = tap_row * g.S + s;
-      float* dst = partial + ((static_cast<long long>(split) * (gridDim.x * g.S) + tap) * g.Cout + co0 + co) * g.Cin + ci0;
+    for (int s = 0; s < T; ++s) {
+      const int tap = tap_row * T + s;
+      float* dst = partial + ((static_cast<long long>(split) * (gridDim.x * T) + tap) * g.Cout + co0 + co) * g.Cin + ci0;
 #pragma unroll 1
       for (int c = 0; c < N_GEMM; c += 32) {
         float v[32];
@@ -226,7 +234,8 @@ bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KH, int KW, int pad
   if (bw > 64) return false;
   int bh = 64 / bw;
   if (bh < 1) bh = 1;
-  g->BW = bw; g->BH = bh; g->strips = (P + bh - 1) / bh; g->units = N * g->strips;
+  g->BW = bw; g->BH = bh; g->strips = (P + bh - 1) / bh; g->wstrips = 1; g->units = N * g->strips;
+  g->RT = 1; g->stride_w = 1;
   const int rows = bw * bh;
   const long long stage_bytes = static_cast<long long>(mt / 32 + KW * (nt / 32)) * rows * 128;
   if (stage_bytes * 2 > 200 * 1024) return false;
@@ -295,7 +304,7 @@ PDL_API int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* 
   if (stride != 1 && stride != 2) { pdl_set_error("tc wgrad: stride %d is not supported", stride); return -3; }
   const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
   if (!wg_geometry(N, P, Q, Cin, Cout, KH, KW, pad, &g)) { pdl_set_error("tc wgrad: unsupported shape"); return -3; }
-  g.stride = stride;
+  g.stride = g.stride_w = stride;
   CUtensorMap ta, tb;
   if (int rc = act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.tma_swizzle, 1)) return rc;
   if (int rc = act_map(&tb, x, N, H, W, Cin, g.BW, g.BH, g.tma_swizzle, stride)) return rc;
@@ -308,6 +317,87 @@ PDL_API int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* 
   if (rc) return rc;
   const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
   wgrad_finish_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(scratch, wg_splits(g), KH * KW, Cout, Cin, dw, db_partial, db_blocks, db);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Small-Cin ("stem") weight gradient: same virtual layout as the forward (tc::stem_dims).  GEMM per filter
+// row r: M = Cout, N = 32 (KW taps x 4 channels), K = pixels; one CTA accumulates all KH rows of its K slice.
+// ---------------------------------------------------------------------------------------------------------
+namespace {
+
+// dw[co][c][r][s] = sum_split partial[split][r][co][s*4 + c]
+__global__ void stem_wgrad_finish_kernel(const float* __restrict__ partial, int splits, int Cout, int Cin, int KH, int KW, float* __restrict__ dw) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= Cout * Cin * KH * KW) return;
+  const int s = i % KW, r = (i / KW) % KH, c = (i / (KW * KH)) % Cin, co = i / (KW * KH * Cin);
+  const float* src = partial + (static_cast<long long>(r) * Cout + co) * 32 + s * 4 + c;
+  const long long per_split = static_cast<long long>(KH) * Cout * 32;
+  float acc = 0.f;
+  for (int k = 0; k < splits; ++k) acc += src[k * per_split];
+  dw[i] = acc;
+}
+
+bool stem_wg_geometry(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, WgGeom* g) {
+  const int mt = wg_m_tile(Cout);
+  if (!mt || Cin < 1 || Cin > 4 || KW > 8 || KH > kMaxTapsPerCta || stride < 1 || stride > 2) return false;
+  const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
+  const int wstrips = (d.Q + 63) / 64;
+  const int bw = ((d.Q + wstrips - 1) / wstrips + 7) / 8 * 8;
+  int bh = 64 / bw;
+  if (bh < 1) bh = 1;
+  g->BW = bw; g->BH = bh; g->strips = (d.P + bh - 1) / bh; g->wstrips = wstrips; g->units = N * g->strips * wstrips;
+  const long long stage_bytes = static_cast<long long>(mt / 32 + KH) * bw * bh * 128;
+  if (stage_bytes * 2 > 200 * 1024) return false;
+  g->Cin = 32; g->Cout = Cout; g->cin_tiles = 1;
+  int splits = 2 * 148 / (Cout / mt);
+  if (splits > g->units) splits = g->units;
+  if (splits < 1) splits = 1;
+  g->units_per_cta = (g->units + splits - 1) / splits;
+  g->S = 1; g->RT = KH; g->pad = 0; g->stride = stride; g->stride_w = 1;
+  g->layout_type = 1; g->lbo = 0; g->sbo = 512;
+  g->tma_swizzle = static_cast<int>(CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B);
+  return true;
+}
+
+}  // namespace
+
+PDL_API int pdl_tc_stem_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
+  WgGeom g{};
+  return stem_wg_geometry(N, H, W, Cin, Cout, KH, KW, stride, pad, &g) ? 1 : 0;
+}
+
+PDL_API long long pdl_tc_stem_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
+  WgGeom g{};
+  if (!stem_wg_geometry(N, H, W, Cin, Cout, KH, KW, stride, pad, &g)) return 0;
+  return static_cast<long long>(wg_splits(g)) * KH * Cout * 32 * sizeof(float);
+}
+
+// xp: padded NHWC4 copy made by pdl_tc_stem_prepare; dy[N][P][Q][Cout] -> dw[Cout][Cin][KH][KW]
+PDL_API int pdl_tc_stem_wgrad(const float* xp, const float* dy, float* dw, float* scratch, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                              int stride, int pad, int* error_flag, cudaStream_t stream) {
+  WgGeom g{};
+  if (!stem_wg_geometry(N, H, W, Cin, Cout, KH, KW, stride, pad, &g)) { pdl_set_error("stem wgrad: unsupported shape"); return -3; }
+  const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
+  CUtensorMap ta, tb;
+  if (int rc = act_map(&ta, dy, N, d.P, d.Q, Cout, g.BW, g.BH, g.tma_swizzle, 1)) return rc;
+  {
+    EncodeTiledFn enc = encode_tiled_wg();
+    if (!enc) { pdl_set_error("cuTensorMapEncodeTiled is not available"); return -1; }
+    cuuint64_t dims[4] = {32, (cuuint64_t)d.Q, (cuuint64_t)d.Hp, (cuuint64_t)N};
+    cuuint64_t strides[3] = {(cuuint64_t)16 * stride, (cuuint64_t)d.Wp * 16, (cuuint64_t)d.Hp * d.Wp * 16};
+    cuuint32_t box[4] = {32, (cuuint32_t)g.BW, (cuuint32_t)(g.BH * stride), 1};
+    cuuint32_t es[4] = {1, 1, (cuuint32_t)stride, 1};
+    CUresult r = enc(&tb, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, const_cast<float*>(xp), dims, strides, box, es, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     static_cast<CUtensorMapSwizzle>(g.tma_swizzle), CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(stem wgrad input) failed: %d", (int)r); return -2; }
+  }
+  int rc = wg_m_tile(Cout) == 128 ? launch_wg<128, 32>(ta, tb, g, 1, scratch, error_flag, stream)
+                                  : launch_wg<64, 32>(ta, tb, g, 1, scratch, error_flag, stream);
+  if (rc) return rc;
+  const int total = Cout * Cin * KH * KW;
+  stem_wgrad_finish_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(scratch, wg_splits(g), Cout, Cin, KH, KW, dw);
   PDL_LAUNCH_CHECK();
   return 0;
 }

@@ -104,6 +104,21 @@ int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* dw, floa
                                 cudaStream_t stream); /* stride 1 or 2 */
 void pdl_tc_set_trace(long long* buf); /* profiling aid: clock64() milestones of CTA 0 */
 
+/* ---- small-Cin ("stem") convolutions on the tensor cores: Cin <= 4, KW <= 8, stride 1|2 (reference: the 7x7/2
+ *      3-channel conv1 of torchvision resnet18, example_launch.py:26).  The input is first copied into a zero-padded
+ *      NHWC4 image (pdl_tc_stem_prepare) in which each filter row is a contiguous 32-float K chunk. ---- */
+int pdl_tc_stem_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+long long pdl_tc_stem_pad_floats(int N, int H, int W, int KH, int KW, int stride, int pad);
+int pdl_tc_stem_prepare(const float* x, long long sn, long long sc, long long sh, long long sw, float* xp, int N, int Cin, int H, int W, int KH,
+                        int KW, int stride, int pad, cudaStream_t stream);
+int pdl_tc_stem_pack_weights(const float* w, float* packed, int Cout, int Cin, int KH, int KW, cudaStream_t stream);
+int pdl_tc_stem_fwd(const float* xp, const float* packed_w, const float* bias, float* y, int N, int H, int W, int Cout, int KH, int KW, int stride,
+                    int pad, int relu, int* error_flag, cudaStream_t stream);
+int pdl_tc_stem_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+long long pdl_tc_stem_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+int pdl_tc_stem_wgrad(const float* xp, const float* dy, float* dw, float* scratch, int N, int H, int W, int Cin, int Cout, int KH, int KW,
+                      int stride, int pad, int* error_flag, cudaStream_t stream);
+
 /* ---- fused ConvNet kernels (reference: ConvNet.forward launch_dist.py:35-41 and its autograd) ---- */
 int pdl_convnet_pack(const float* w2, const float* w3, const float* wf, float* p2f, float* p2b, float* p3f, float* p3b, float* wfp,
                      cudaStream_t stream);
@@ -121,14 +136,16 @@ int pdl_pool2_bwd_dbias(const float* da, const uint8_t* idx, const float* pooled
 int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_t* idx1, const float* a1, float* gw1, float* gb1, float* partial, int N,
                           cudaStream_t stream);
 
-/* ---- BatchNorm2d, NHWC rows [M = N*H*W][C] (reference: torchvision resnet18 at example_launch.py:26) ---- */
+/* ---- BatchNorm2d with the block's ReLU / residual add fused in, NHWC rows [M = N*H*W][C]:
+ *      y = act(bn(x) [+ residual]) (reference: torchvision resnet18 at example_launch.py:26).
+ *      saved is [4][C] = mean, invstd, scale, shift; residual / dres / y may be NULL as documented in bn.cu ---- */
 long long pdl_bn_scratch_floats(long long M, int C);
-int pdl_bn_fwd_train(const float* x, const float* gamma, const float* beta, float* running_mean, float* running_var, float momentum, float eps,
-                     float* y, float* save_mean, float* save_invstd, float* scratch, long long M, int C, int relu, cudaStream_t stream);
-int pdl_bn_fwd_eval(const float* x, const float* gamma, const float* beta, const float* running_mean, const float* running_var, float eps,
-                    float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream);
-int pdl_bn_bwd(const float* x, const float* dy, const float* gamma, const float* save_mean, const float* save_invstd, float* dx, float* dgamma,
-               float* dbeta, float* scratch, long long M, int C, cudaStream_t stream);
+int pdl_bn_fwd_train(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean, float* running_var,
+                     float momentum, float eps, float* y, float* saved, float* scratch, long long M, int C, int relu, cudaStream_t stream);
+int pdl_bn_fwd_eval(const float* x, const float* residual, const float* gamma, const float* beta, const float* running_mean,
+                    const float* running_var, float eps, float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream);
+int pdl_bn_bwd(const float* x, const float* dy, const float* y, const float* gamma, const float* saved, float* dx, float* dres, float* dgamma,
+               float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream);
 
 /* ---- element-wise / pooling / linear / loss (reference: nn.ReLU, nn.MaxPool2d, nn.Linear,
  *      nn.CrossEntropyLoss at launch_dist.py:13-32,58; ResNet add+ReLU / avgpool at example_launch.py:26) ---- */

@@ -57,6 +57,15 @@ def declare(L):
     sig("pdl_tc_wgrad_scratch_bytes_strided", [I, I, I, I, I, I, I, I, I], LL)
     sig("pdl_tc_conv2d_wgrad_strided", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv2d_wgrad", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, P, P])
+    # small-Cin ("stem") convolutions on the tensor cores
+    sig("pdl_tc_stem_supported", [I, I, I, I, I, I, I, I])
+    sig("pdl_tc_stem_pad_floats", [I, I, I, I, I, I, I], LL)
+    sig("pdl_tc_stem_prepare", [P, LL, LL, LL, LL, P, I, I, I, I, I, I, I, I, P])
+    sig("pdl_tc_stem_pack_weights", [P, P, I, I, I, I, P])
+    sig("pdl_tc_stem_fwd", [P, P, P, P, I, I, I, I, I, I, I, I, I, P, P])
+    sig("pdl_tc_stem_wgrad_supported", [I, I, I, I, I, I, I, I, I])
+    sig("pdl_tc_stem_wgrad_scratch_bytes", [I, I, I, I, I, I, I, I, I], LL)
+    sig("pdl_tc_stem_wgrad", [P, P, P, P, I, I, I, I, I, I, I, I, I, P, P])
     # fused ConvNet kernels
     sig("pdl_convnet_pack", [P, P, P, P, P, P, P, P, P])
     sig("pdl_conv1_fused_fwd", [P, P, P, P, P, I, P])
@@ -70,9 +79,9 @@ def declare(L):
     sig("pdl_conv1_wgrad_fused", [P, P, P, P, P, P, P, I, P])
     # batch norm
     sig("pdl_bn_scratch_floats", [LL, I], LL)
-    sig("pdl_bn_fwd_train", [P, P, P, P, P, F, F, P, P, P, P, LL, I, I, P])
-    sig("pdl_bn_fwd_eval", [P, P, P, P, P, F, P, P, LL, I, I, P])
-    sig("pdl_bn_bwd", [P, P, P, P, P, P, P, P, P, LL, I, P])
+    sig("pdl_bn_fwd_train", [P, P, P, P, P, P, F, F, P, P, P, LL, I, I, P])
+    sig("pdl_bn_fwd_eval", [P, P, P, P, P, P, F, P, P, LL, I, I, P])
+    sig("pdl_bn_bwd", [P, P, P, P, P, P, P, P, P, P, LL, I, I, P])
     # element-wise / pooling / linear / loss
     sig("pdl_relu_fwd", [P, P, LL, P])
     sig("pdl_relu_bwd", [P, P, P, LL, P])

@@ -11,7 +11,6 @@ ones/zeros for batch-norm).
 from __future__ import annotations
 
 from .. import nn
-from ..nn.modules import add_relu
 
 
 def _conv3x3(cin, cout, stride=1):
@@ -36,12 +35,9 @@ class BasicBlock(nn.Module):
         self.stride = stride
 
     def forward(self, x):
-        identity = x
-        out = self.relu(self.bn1(self.conv1(x)))
-        out = self.bn2(self.conv2(out))
-        if self.downsample is not None:
-            identity = self.downsample(x)
-        return add_relu(out, identity)
+        identity = x if self.downsample is None else self.downsample(x)
+        out = self.bn1(self.conv1(x), relu=True)  # bn + relu, and below bn + add + relu, are single fused passes
+        return self.bn2(self.conv2(out), relu=True, residual=identity)
 
 
 class Bottleneck(nn.Module):
@@ -60,13 +56,10 @@ class Bottleneck(nn.Module):
         self.stride = stride
 
     def forward(self, x):
-        identity = x
-        out = self.relu(self.bn1(self.conv1(x)))
-        out = self.relu(self.bn2(self.conv2(out)))
-        out = self.bn3(self.conv3(out))
-        if self.downsample is not None:
-            identity = self.downsample(x)
-        return add_relu(out, identity)
+        identity = x if self.downsample is None else self.downsample(x)
+        out = self.bn1(self.conv1(x), relu=True)
+        out = self.bn2(self.conv2(out), relu=True)
+        return self.bn3(self.conv3(out), relu=True, residual=identity)
 
 
 class ResNet(nn.Module):
@@ -101,7 +94,7 @@ class ResNet(nn.Module):
         return nn.Sequential(*layers)
 
     def forward(self, x):
-        x = self.maxpool(self.relu(self.bn1(self.conv1(x))))
+        x = self.maxpool(self.bn1(self.conv1(x), relu=True))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = self.avgpool(x)
         x = x.flatten(1)

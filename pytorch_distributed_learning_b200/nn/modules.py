@@ -72,14 +72,21 @@ class CrossEntropyLoss(tnn.CrossEntropyLoss):
 
 
 class BatchNorm2d(tnn.BatchNorm2d):
-    def forward(self, x):
-        if _native(x) and self.affine and self.track_running_stats and self.momentum is not None:
+    """``bn(x)``; the optional arguments fuse what follows it in a ResNet block into the same kernels:
+    ``bn(x, relu=True)`` = ``relu(bn(x))`` and ``bn(x, relu=True, residual=r)`` = ``relu(bn(x) + r)``."""
+
+    def forward(self, x, relu=False, residual=None):
+        if _native(x) and self.affine and self.track_running_stats and self.momentum is not None and (residual is None or _native(residual)):
             from ..ops import functional as NF
 
             if self.training and self.num_batches_tracked is not None:
                 self.num_batches_tracked.add_(1)
-            return NF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum, self.eps)
-        return super().forward(x)
+            return NF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum, self.eps,
+                                 relu, residual)
+        y = super().forward(x)
+        if residual is not None:
+            y = y + residual
+        return torch.relu(y) if relu else y
 
 
 class AdaptiveAvgPool2d(tnn.AdaptiveAvgPool2d):

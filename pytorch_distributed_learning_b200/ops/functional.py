@@ -54,7 +54,6 @@ class _Conv2d(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, b, stride, pad):
         L = _lib.cuda()
-        x = _nhwc(x)
         w = w.contiguous()
         N, Cin, H, W = x.shape
         Cout, _, KH, KW = w.shape
@@ -62,28 +61,40 @@ class _Conv2d(torch.autograd.Function):
         y = torch.empty((N, Cout, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
         from . import tc_conv
 
-        if not tc_conv.conv2d_fwd(x, w, b, y, stride, pad, relu=False):
-            _ok(L.pdl_conv2d_fwd_simt(_p(x), _p(w), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, 0, _stream(x)), "conv2d forward")
-        ctx.save_for_backward(x, w)
         ctx.geom = (stride, pad, b is not None)
+        ctx.x_shape = tuple(x.shape)
+        ctx.stem = tc_conv.stem_supported(x, w, stride, pad)
+        if ctx.stem:  # first layer: the padded NHWC4 copy replaces x for the backward pass (wgrad only needs that)
+            xp = tc_conv.stem_fwd(x, w, b, y, stride, pad)
+            ctx.save_for_backward(xp, w, None)
+            return y
+        x = _nhwc(x)
+        handled, packed_bwd = tc_conv.conv2d_fwd(x, w, b, y, stride, pad, relu=False, want_bwd_pack=ctx.needs_input_grad[0])
+        if not handled:
+            _ok(L.pdl_conv2d_fwd_simt(_p(x), _p(w), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, 0, _stream(x)), "conv2d forward")
+        ctx.save_for_backward(x, w, packed_bwd)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         L = _lib.cuda()
-        x, w = ctx.saved_tensors
+        x, w, packed_bwd = ctx.saved_tensors
         stride, pad, has_bias = ctx.geom
         dy = _nhwc(dy)
-        N, Cin, H, W = x.shape
+        N, Cin, H, W = ctx.x_shape
         Cout, _, KH, KW = w.shape
         dx = dw = db = None
         from . import tc_conv
 
         if ctx.needs_input_grad[0]:
-            dx = torch.empty_like(x, memory_format=_CL)
-            if not tc_conv.conv2d_dgrad(dy, w, dx, stride, pad):
-                _ok(L.pdl_conv2d_dgrad_simt(_p(dy), _p(w), _p(dx), N, H, W, Cin, Cout, KH, KW, stride, pad, _stream(x)), "conv2d dgrad")
-        if ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2]):
+            dx = torch.empty(ctx.x_shape, dtype=dy.dtype, device=dy.device, memory_format=_CL)
+            if not tc_conv.conv2d_dgrad(dy, w, dx, stride, pad, packed_bwd):
+                _ok(L.pdl_conv2d_dgrad_simt(_p(dy), _p(w), _p(dx), N, H, W, Cin, Cout, KH, KW, stride, pad, _stream(dy)), "conv2d dgrad")
+        if ctx.stem and (ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2])):
+            dw = torch.empty_like(w)
+            tc_conv.stem_wgrad(x, dy, dw, ctx.x_shape, stride, pad)  # x is the padded NHWC4 copy here
+            db = dy.sum(dim=(0, 2, 3)) if has_bias else None
+        elif ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2]):
             dw = torch.empty_like(w)
             db = torch.empty(Cout, dtype=w.dtype, device=w.device) if has_bias else None
             if not tc_conv.conv2d_wgrad(x, dy, dw, db, stride, pad):
@@ -203,10 +214,11 @@ def cross_entropy(logits, target):
     return _CrossEntropy.apply(logits, target)
 
 
-def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps):
+def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None):
+    """``act(bn(x) [+ residual])`` in one pass (the tail of every ResNet block)."""
     from . import bn
 
-    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps)
+    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual)
 
 
 class _GlobalAvgPool(torch.autograd.Function):

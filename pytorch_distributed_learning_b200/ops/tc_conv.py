@@ -59,18 +59,61 @@ def pack_weights(w, want_fwd=True, want_bwd=False):
     return fwd, bwd
 
 
-def conv2d_fwd(x, w, b, y, stride, pad, relu=False):
+def dgrad_supported(Cin, Cout, W, stride):
+    return stride in (1, 2) and Cout % 32 == 0 and (Cin in (32, 64) or Cin % 128 == 0) and W <= 128 * stride
+
+
+def conv2d_fwd(x, w, b, y, stride, pad, relu=False, want_bwd_pack=False):
+    """Returns (handled, packed_bwd): with ``want_bwd_pack`` the dgrad operand copy of the weights is produced by
+    the same packing launch and handed back for the backward pass (None when dgrad will not use the tensor cores)."""
+    if not enabled():
+        return False, None
+    N, Cin, H, W = x.shape
+    Cout, _, KH, KW = w.shape
+    L = _lib.cuda()
+    if not L.pdl_tc_conv_supported(H, W, Cin, Cout, KH, KW, stride, pad, 0):
+        return False, None
+    packed, packed_bwd = pack_weights(w, True, want_bwd_pack and dgrad_supported(Cin, Cout, W, stride))
+    _ok(L.pdl_tc_conv2d_fwd_strided(_p(x), _p(packed), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, int(relu),
+                                    _p(error_flag(x.device)), _stream(x)), "tensor-core conv forward")
+    return True, packed_bwd
+
+
+def stem_supported(x, w, stride, pad):
+    """Small-Cin first layer (Cin <= 4, e.g. ResNet's 7x7/2 conv1): forward and wgrad both on the tensor cores."""
     if not enabled():
         return False
     N, Cin, H, W = x.shape
     Cout, _, KH, KW = w.shape
     L = _lib.cuda()
-    if not L.pdl_tc_conv_supported(H, W, Cin, Cout, KH, KW, stride, pad, 0):
-        return False
-    packed, _ = pack_weights(w, True, False)
-    _ok(L.pdl_tc_conv2d_fwd_strided(_p(x), _p(packed), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, int(relu),
-                                    _p(error_flag(x.device)), _stream(x)), "tensor-core conv forward")
-    return True
+    return bool(Cin <= 4 and L.pdl_tc_stem_supported(H, W, Cin, Cout, KH, KW, stride, pad)
+                and L.pdl_tc_stem_wgrad_supported(N, H, W, Cin, Cout, KH, KW, stride, pad))
+
+
+def stem_fwd(x, w, b, y, stride, pad):
+    """x in ANY layout (strides are passed down) -> y (NHWC); returns the padded NHWC4 copy the wgrad reuses."""
+    N, Cin, H, W = x.shape
+    Cout, _, KH, KW = w.shape
+    L = _lib.cuda()
+    xp = torch.empty(L.pdl_tc_stem_pad_floats(N, H, W, KH, KW, stride, pad), dtype=x.dtype, device=x.device)
+    sn, sc, sh, sw = x.stride()
+    _ok(L.pdl_tc_stem_prepare(_p(x), sn, sc, sh, sw, _p(xp), N, Cin, H, W, KH, KW, stride, pad, _stream(x)), "stem input padding")
+    packed = torch.empty((KH, Cout, 32), dtype=w.dtype, device=w.device)
+    _ok(L.pdl_tc_stem_pack_weights(_p(w), _p(packed), Cout, Cin, KH, KW, _stream(x)), "stem weight packing")
+    _ok(L.pdl_tc_stem_fwd(_p(xp), _p(packed), _p(b), _p(y), N, H, W, Cout, KH, KW, stride, pad, 0, _p(error_flag(x.device)), _stream(x)),
+        "tensor-core stem conv forward")
+    return xp
+
+
+def stem_wgrad(xp, dy, dw, x_shape, stride, pad):
+    N, Cin, H, W = x_shape
+    Cout, _, KH, KW = dw.shape
+    L = _lib.cuda()
+    from .functional import scratch
+
+    sc = scratch(L.pdl_tc_stem_wgrad_scratch_bytes(N, H, W, Cin, Cout, KH, KW, stride, pad), dy.device, "tc_wgrad")
+    _ok(L.pdl_tc_stem_wgrad(_p(xp), _p(dy), _p(dw), _p(sc), N, H, W, Cin, Cout, KH, KW, stride, pad, _p(error_flag(dy.device)), _stream(dy)),
+        "tensor-core stem conv wgrad")
 
 
 def conv2d_fwd_relu_pool(x, w, b, pool_stride):
@@ -92,14 +135,13 @@ def conv2d_fwd_relu_pool(x, w, b, pool_stride):
     return y, idx
 
 
-def conv2d_dgrad(dy, w, dx, stride, pad):
-    if not enabled() or stride not in (1, 2):
-        return False
+def conv2d_dgrad(dy, w, dx, stride, pad, packed=None):
     N, Cin, H, W = dx.shape
     Cout, _, KH, KW = w.shape
-    if Cout % 32 or not (Cin in (32, 64) or Cin % 128 == 0) or W > 128 * stride:
+    if not enabled() or not dgrad_supported(Cin, Cout, W, stride):
         return False
-    _, packed = pack_weights(w, False, True)
+    if packed is None:
+        _, packed = pack_weights(w, False, True)
     _ok(_lib.cuda().pdl_tc_conv2d_dgrad_strided(_p(dy), _p(packed), _p(dx), N, H, W, Cin, Cout, KH, KW, stride, pad,
                                                 _p(error_flag(dx.device)), _stream(dx)), "tensor-core conv dgrad")
     return True

@@ -239,6 +239,57 @@ def test_batchnorm_train_fwd_bwd_matches_torch(shape):
         torch.testing.assert_close(ours(x), ref(xr), rtol=1e-4, atol=1e-4)
 
 
+@pytest.mark.parametrize("relu,with_res", [(True, False), (True, True), (False, True)])
+@pytest.mark.parametrize("shape", [(8, 64, 14, 14), (5, 96, 7, 9), (2, 256, 40, 40)])
+def test_batchnorm_fused_relu_residual(shape, relu, with_res):
+    """bn(x, relu=, residual=) against the unfused torch composition, forward, all gradients and eval mode."""
+    torch.manual_seed(7)
+    N, C, H, W = shape
+    x = (torch.randn(shape, device=_dev()) * 1.5 - 0.3).requires_grad_(True)
+    r = torch.randn(shape, device=_dev()).requires_grad_(True) if with_res else None
+    xr = x.detach().clone().requires_grad_(True)
+    rr = r.detach().clone().requires_grad_(True) if with_res else None
+    ours, ref = pdl.nn.BatchNorm2d(C).to(_dev()), torch.nn.BatchNorm2d(C).to(_dev())
+    with torch.no_grad():
+        ours.weight.uniform_(0.5, 1.5)
+        ours.bias.uniform_(-0.5, 0.5)
+    ref.load_state_dict(ours.state_dict())
+
+    def ref_form(inp, res):
+        out = ref(inp)
+        if res is not None:
+            out = out + res
+        return torch.relu(out) if relu else out
+
+    y, yr = ours(x, relu=relu, residual=r), ref_form(xr, rr)
+    torch.testing.assert_close(y, yr, rtol=1e-4, atol=1e-4)
+    # keep the test away from the ReLU kink: elements whose pre-activation is ~0 may legitimately flip
+    safe = (yr.detach().abs() > 1e-4) if relu else torch.ones_like(yr, dtype=torch.bool)
+    dy = torch.randn_like(yr) * safe
+    y.backward(dy)
+    yr.backward(dy)
+    torch.testing.assert_close(x.grad, xr.grad, rtol=1e-3, atol=2e-4)
+    if with_res:
+        torch.testing.assert_close(r.grad * safe, rr.grad * safe, rtol=1e-4, atol=1e-5)
+    torch.testing.assert_close(ours.weight.grad, ref.weight.grad, rtol=1e-3, atol=2e-3)
+    torch.testing.assert_close(ours.bias.grad, ref.bias.grad, rtol=1e-3, atol=2e-3)
+    torch.testing.assert_close(ours.running_var, ref.running_var, rtol=1e-4, atol=1e-5)
+    ours.eval(), ref.eval()
+    with torch.no_grad():
+        torch.testing.assert_close(ours(x, relu=relu, residual=r), ref_form(xr, rr), rtol=1e-4, atol=1e-4)
+
+
+def test_maxpool_vector_path_matches_torch():
+    x = torch.randn(3, 64, 30, 30, device=_dev(), requires_grad=True)
+    xr = x.detach().clone().requires_grad_(True)
+    y, yr = pdl.nn.MaxPool2d(3, 2, 1)(x), torch.nn.functional.max_pool2d(xr, 3, 2, 1)
+    torch.testing.assert_close(y, yr)
+    dy = torch.randn_like(yr)
+    y.backward(dy)
+    yr.backward(dy)
+    torch.testing.assert_close(x.grad, xr.grad)
+
+
 def test_add_relu():
     a = torch.randn(4, 64, 8, 8, device=_dev(), requires_grad=True)
     b = torch.randn(4, 64, 8, 8, device=_dev(), requires_grad=True)

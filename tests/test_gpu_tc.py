@@ -46,7 +46,7 @@ def test_tc_forward_matches_fp32(case):
     b = torch.randn(Cout, device=DEV)
     P = H + 2 * pad - k + 1
     y = torch.empty((N, Cout, P, P), device=DEV).contiguous(memory_format=CL)
-    assert tc_conv.conv2d_fwd(x, w, b, y, 1, pad)
+    assert tc_conv.conv2d_fwd(x, w, b, y, 1, pad)[0]
     tc_conv.check_errors(DEV)
     torch.backends.cudnn.allow_tf32 = False
     ref = F.conv2d(x, w, b, padding=pad)
@@ -124,7 +124,7 @@ def test_tc_forward_stride2(case):
     w = torch.randn(Cout, Cin, k, k, device=DEV) * 0.1
     P = (H + 2 * pad - k) // 2 + 1
     y = torch.empty((N, Cout, P, P), device=DEV).contiguous(memory_format=CL)
-    assert tc_conv.conv2d_fwd(x, w, None, y, 2, pad)
+    assert tc_conv.conv2d_fwd(x, w, None, y, 2, pad)[0]
     tc_conv.check_errors(DEV)
     torch.backends.cudnn.allow_tf32 = False
     ref = F.conv2d(x, w, None, stride=2, padding=pad)

@@ -77,3 +77,33 @@ def test_autograd_conv_stride2_uses_tensor_cores():
     _close(y, yr)
     _close(x.grad, xr.grad)
     _close(w.grad, wr.grad)
+
+
+# (N, Cin, H, W, Cout, k, stride, pad): small-Cin first layers; the first is ResNet's 7x7/2 stem at ImageNet size
+STEMS = [(2, 3, 224, 224, 64, 7, 2, 3), (3, 3, 32, 32, 64, 7, 2, 3), (2, 1, 28, 28, 64, 5, 1, 1), (2, 3, 32, 32, 64, 3, 1, 1),
+         (1, 4, 37, 53, 128, 5, 2, 2)]
+
+
+@pytest.mark.parametrize("case", STEMS)
+@pytest.mark.parametrize("channels_last", [False, True])
+def test_stem_conv_fwd_wgrad(case, channels_last):
+    """Cin <= 4 convolutions on the tensor cores through the padded NHWC4 virtual layout (overlapping TMA windows)."""
+    N, Cin, H, W, Cout, k, stride, pad = case
+    torch.manual_seed(9)
+    x = torch.randn(N, Cin, H, W, device=DEV)
+    if channels_last:
+        x = x.contiguous(memory_format=CL)
+    w = (torch.randn(Cout, Cin, k, k, device=DEV) * 0.1).requires_grad_(True)
+    assert tc_conv.stem_supported(x, w, stride, pad)
+    y = NF.conv2d(x, w, None, stride, pad)
+    tc_conv.check_errors(DEV)
+    dy = torch.randn_like(y)
+    y.backward(dy)
+    tc_conv.check_errors(DEV)
+    torch.backends.cudnn.allow_tf32 = False
+    wr = w.detach().clone().requires_grad_(True)
+    yr = F.conv2d(x, wr, None, stride, pad)
+    yr.backward(dy)
+    torch.backends.cudnn.allow_tf32 = True
+    _close(y, yr)
+    _close(w.grad, wr.grad)
