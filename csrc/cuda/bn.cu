@@ -78,7 +78,9 @@ constexpr int kFinSlices = 32;
 __global__ void __launch_bounds__(kCG * kFinSlices) bn_finalize_kernel(const float* __restrict__ partial, int splits, int C,
                                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
                                                                        float* __restrict__ running_mean, float* __restrict__ running_var,
-                                                                       float momentum, float eps, float* __restrict__ saved) {
+                                                                       float momentum, float eps, float* __restrict__ saved,
+                                                                       long long* __restrict__ num_batches_tracked) {
+  if (num_batches_tracked && blockIdx.x == 0 && threadIdx.x == 0) *num_batches_tracked += 1;  // nn.BatchNorm2d's step counter
   const int ch = threadIdx.x % kCG, sl = threadIdx.x / kCG;
   const int c = blockIdx.x * kCG + ch;
   __shared__ float sh_a[kFinSlices][kCG + 1], sh_b[kFinSlices][kCG + 1];
@@ -301,17 +303,18 @@ void apply(const float* x, const float* residual, float* y, const float* scale, 
 // floats of scratch the BN entry points need: split partials + 3 per-channel coefficient rows
 PDL_API long long pdl_bn_scratch_floats(long long M, int C) { return static_cast<long long>(choose_splits(M, C)) * C * 3 + 3ll * C; }
 
-// Training forward.  saved [4][C] (mean, invstd, scale, shift) is kept for backward.  relu != 0 fuses the
+// Training forward.  num_batches_tracked (may be NULL) is incremented on the device.  saved [4][C] (mean, invstd, scale, shift) is kept for backward.  relu != 0 fuses the
 // activation, residual != nullptr adds the skip connection before it.
 PDL_API int pdl_bn_fwd_train(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean,
-                             float* running_var, float momentum, float eps, float* y, float* saved, float* scratch, long long M, int C, int relu,
-                             cudaStream_t stream) {
+                             float* running_var, long long* num_batches_tracked, float momentum, float eps, float* y, float* saved,
+                             float* scratch, long long M, int C, int relu, cudaStream_t stream) {
   if (check_c(C)) return -1;
   const int splits = choose_splits(M, C);
   const long long rps = (M + splits - 1) / splits;
   const int cgroups = (C + kCG - 1) / kCG;
   bn_stats_kernel<<<dim3(cgroups, splits), kThreads, 0, stream>>>(x, scratch, M, C, rps);
-  bn_finalize_kernel<<<cgroups, kCG * kFinSlices, 0, stream>>>(scratch, splits, C, gamma, beta, running_mean, running_var, momentum, eps, saved);
+  bn_finalize_kernel<<<cgroups, kCG * kFinSlices, 0, stream>>>(scratch, splits, C, gamma, beta, running_mean, running_var, momentum, eps, saved,
+                                                                   num_batches_tracked);
   apply(x, residual, y, saved + 2ll * C, saved + 3ll * C, M, C, relu, stream);
   PDL_LAUNCH_CHECK();
   return 0;

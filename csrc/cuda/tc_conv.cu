@@ -12,9 +12,10 @@
 #include "common.cuh"
 #include "tc_common.cuh"
 
+#include <cstdlib>
+
 namespace {
 
-constexpr int kStages = 4;
 constexpr int kThreads = 384;   // 4 control warps (TMA, MMA, TMEM alloc, spare) + 8 epilogue warps
 constexpr int kEpiWarps = 8;
 constexpr int A_BYTES = 128 * 128;  // 128 rows x 32 tf32
@@ -41,6 +42,7 @@ struct EpiArgs {
   const float* bias;
   int relu;
   int pool_stride;
+  int tma_store;     // EPI_STORE: hand the tile to TMA through the swizzled staging buffer (dense outputs only)
   int* error;
   long long* trace;  // optional: clock64() of CTA 0 at pipeline milestones (profiling aid)
 };
@@ -49,16 +51,19 @@ template <int N_GEMM>
 struct Smem {
   static constexpr int B_BYTES = N_GEMM * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int STAGES = N_GEMM == 128 ? 4 : (N_GEMM == 64 ? 6 : 8);  // what fits next to the staging tile
   static constexpr int STAGING_LD = N_GEMM + 4;
   static constexpr int STAGING_BYTES = 128 * STAGING_LD * 4;
-  static constexpr int BAR_OFFSET = kStages * STAGE_BYTES + STAGING_BYTES;
-  static constexpr int TOTAL = BAR_OFFSET + 128 + 512 + 512 + 1024;  // + barriers + bias row + pool table + alignment slack
+  static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + STAGING_BYTES;
+  static constexpr int TOTAL = BAR_OFFSET + 256 + 512 + 512 + 1024;  // + barriers + bias row + pool table + alignment slack
 };
 
 template <int N_GEMM, int EPI>
 __global__ void __launch_bounds__(kThreads, 1)
-tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const TcGeom g, const EpiArgs e) {
+tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
+               const TcGeom g, const EpiArgs e) {
   using SM = Smem<N_GEMM>;
+  constexpr int kStages = SM::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~static_cast<uintptr_t>(1023));
   float* staging = reinterpret_cast<float*>(smem + kStages * SM::STAGE_BYTES);
@@ -68,8 +73,8 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   volatile int* failed = reinterpret_cast<volatile int*>(tmem_slot + 1);
-  float* sbias = reinterpret_cast<float*>(smem + SM::BAR_OFFSET + 128);       // N_GEMM floats
-  int* pool_row = reinterpret_cast<int*>(smem + SM::BAR_OFFSET + 128 + 512);   // <= 128 pooled pixels -> staging row
+  float* sbias = reinterpret_cast<float*>(smem + SM::BAR_OFFSET + 256);       // N_GEMM floats
+  int* pool_row = reinterpret_cast<int*>(smem + SM::BAR_OFFSET + 256 + 512);   // <= 128 pooled pixels -> staging row
 
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
 #define PDL_TRACE(slot) do { if (e.trace && blockIdx.x == 0) e.trace[slot] = clock64(); } while (0)
@@ -79,6 +84,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   if (threadIdx.x == 0) {
     tc::prefetch_tmap(&tmA);
     tc::prefetch_tmap(&tmB);
+    if (EPI == EPI_STORE && e.tma_store) tc::prefetch_tmap(&tmOut);
     for (int i = 0; i < kStages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { tc::mbar_init(&tfull[i], 1); tc::mbar_init(&tempty[i], kEpiWarps); }
     *failed = 0;
@@ -179,7 +185,39 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int n0 = g.BN > 1 ? mt * g.BN : mt / g.tiles_per_img;
       const int h0 = g.BN > 1 ? 0 : (mt % g.tiles_per_img) * g.BH;
       const uint32_t t_row = tmem_base + acc * N_GEMM + half * HALF + (static_cast<uint32_t>(quarter * 32) << 16);
-      if (EPI == EPI_STORE) {
+      if (EPI == EPI_STORE && e.tma_store) {
+        // registers -> swizzled staging tile (one [128 rows][128 B] block per 32 channels) -> one TMA store per block.
+        // The store clips rows / images past the tensor edge, so no per-row predicate is needed.
+        if (et == 0) tc::bulk_wait_read_all();  // the previous tile's stores have drained the staging buffer
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        const float* bias_t = e.bias ? e.bias + nt * N_GEMM + half * HALF : nullptr;
+#pragma unroll 1
+        for (int c = 0; c < HALF; c += CH) {
+          float v[CH];
+          tc::tmem_ld<CH>(t_row + c, v);
+          const int col0 = half * HALF + c;
+          uint8_t* dst_row = reinterpret_cast<uint8_t*>(staging) + (col0 / 32) * A_BYTES + row * 128;
+          const int j0 = (col0 % 32) / 4;
+#pragma unroll
+          for (int j = 0; j < CH; j += 4) {
+            const float4 bb = bias_t ? *reinterpret_cast<const float4*>(bias_t + c + j) : make_float4(0.f, 0.f, 0.f, 0.f);
+            float4 o = make_float4(v[j] + bb.x, v[j + 1] + bb.y, v[j + 2] + bb.z, v[j + 3] + bb.w);
+            if (e.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
+            *reinterpret_cast<float4*>(dst_row + (((j0 + j / 4) ^ (row & 7)) << 4)) = o;
+          }
+        }
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&tempty[acc]);  // accumulator drained: the next tile's MMAs may start
+        tc::fence_proxy_async_smem();
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (et == 0) {
+#pragma unroll
+          for (int cc = 0; cc < N_GEMM / 32; ++cc)
+            tc::tma_store_4d(&tmOut, reinterpret_cast<uint8_t*>(staging) + cc * A_BYTES, nt * N_GEMM + cc * 32, 0, h0, n0);
+          tc::bulk_commit();
+        }
+      } else if (EPI == EPI_STORE) {
         const int bw = row % g.BW, t2 = row / g.BW, bh = t2 % g.BH, bn = t2 / g.BH;
         // output pixel of this row: the tile grid (Hc x BW) is the full image, or one parity class of it (strided dgrad)
         const int oh = (h0 + bh) * g.out_stride + g.out_oh, ow = bw * g.out_stride + g.out_ow;
@@ -256,6 +294,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (tile == blockIdx.x && et == 0) PDL_TRACE(7);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (EPI == EPI_STORE && e.tma_store && et == 0) tc::bulk_wait_read_all();  // smem must outlive the last store's reads
   }
 
   tc::tc_fence_before();
@@ -309,8 +348,18 @@ int make_weight_map(CUtensorMap* m, const float* base, int rows, int K, int box_
   return 0;
 }
 
+// Dense NHWC output [N][H][W][C] for the TMA-store epilogue: box = (32, bw, bh, bn), same row order as the A box.
+int make_out_map(CUtensorMap* m, float* base, int N, int H, int W, int C, int bw, int bh, int bn) {
+  return make_act_map(m, base, N, H, W, C, bw, bh, bn, 1);
+}
+inline bool use_tma_store() {
+  static int v = -1;
+  if (v < 0) { const char* s = getenv("PDL_TC_TMA_STORE"); v = s ? atoi(s) : 1; }
+  return v != 0;
+}
+
 template <int N_GEMM, int EPI>
-int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const TcGeom& g, const EpiArgs& e, cudaStream_t stream) {
+int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& o, const TcGeom& g, const EpiArgs& e, cudaStream_t stream) {
   static bool configured = false;
   auto kernel = tc_conv_kernel<N_GEMM, EPI>;
   if (!configured) {
@@ -318,17 +367,18 @@ int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const TcGeom& g, const
     configured = true;
   }
   int grid = g.num_tiles < 148 ? g.num_tiles : 148;
-  kernel<<<grid, kThreads, Smem<N_GEMM>::TOTAL, stream>>>(a, b, g, e);
+  kernel<<<grid, kThreads, Smem<N_GEMM>::TOTAL, stream>>>(a, b, o, g, e);
   PDL_LAUNCH_CHECK();
   return 0;
 }
 
 template <int EPI>
-int dispatch_n(int n_gemm, const CUtensorMap& a, const CUtensorMap& b, const TcGeom& g, const EpiArgs& e, cudaStream_t stream) {
+int dispatch_n(int n_gemm, const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& o, const TcGeom& g, const EpiArgs& e,
+               cudaStream_t stream) {
   switch (n_gemm) {
-    case 32: return launch_tc<32, EPI>(a, b, g, e, stream);
-    case 64: return launch_tc<64, EPI>(a, b, g, e, stream);
-    case 128: return launch_tc<128, EPI>(a, b, g, e, stream);
+    case 32: return launch_tc<32, EPI>(a, b, o, g, e, stream);
+    case 64: return launch_tc<64, EPI>(a, b, o, g, e, stream);
+    case 128: return launch_tc<128, EPI>(a, b, o, g, e, stream);
     default: pdl_set_error("tc_conv: unsupported GEMM N %d", n_gemm); return -3;
   }
 }
@@ -402,8 +452,11 @@ static int tc_fwd_impl(const float* x, const float* packed_w, const float* bias,
   CUtensorMap ta, tb;
   if (int rc = make_act_map(&ta, x, N, H, W, Cin, g.BW, g.BH, g.BN, stride)) return rc;
   if (int rc = make_weight_map(&tb, packed_w, KH * KW * Cout, Cin, ng)) return rc;
-  EpiArgs e{y, idx, bias, relu, pool_stride, error_flag, g_trace};
-  return pool_stride > 0 ? dispatch_n<EPI_RELU_POOL>(ng, ta, tb, g, e, stream) : dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream);
+  const int tma_store = pool_stride == 0 && use_tma_store();
+  CUtensorMap to = ta;
+  if (tma_store) { if (int rc = make_out_map(&to, y, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc; }
+  EpiArgs e{y, idx, bias, relu, pool_stride, tma_store, error_flag, g_trace};
+  return pool_stride > 0 ? dispatch_n<EPI_RELU_POOL>(ng, ta, tb, to, g, e, stream) : dispatch_n<EPI_STORE>(ng, ta, tb, to, g, e, stream);
 }
 
 PDL_API int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin,
@@ -455,8 +508,11 @@ PDL_API int pdl_tc_conv2d_dgrad_strided(const float* dy, const float* packed_w_b
       g.Nimg = N; g.Hout = H; g.Wout = W;
       CUtensorMap ta;
       if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
-      EpiArgs e{dx, nullptr, nullptr, 0, 0, error_flag, g_trace};
-      if (int rc = dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream)) return rc;
+      const int tma_store = stride == 1 && use_tma_store();  // parity classes scatter with a stride: direct stores
+      CUtensorMap to = ta;
+      if (tma_store) { if (int rc = make_out_map(&to, dx, N, H, W, Cin, g.BW, g.BH, g.BN)) return rc; }
+      EpiArgs e{dx, nullptr, nullptr, 0, 0, tma_store, error_flag, g_trace};
+      if (int rc = dispatch_n<EPI_STORE>(ng, ta, tb, to, g, e, stream)) return rc;
     }
   return 0;
 }
@@ -563,6 +619,9 @@ PDL_API int pdl_tc_stem_fwd(const float* xp, const float* packed_w, const float*
     if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(stem input, overlapping windows) failed: %d", (int)r); return -2; }
   }
   if (int rc = make_weight_map(&tb, packed_w, KH * Cout, 32, ng)) return rc;
-  EpiArgs e{y, nullptr, bias, relu, 0, error_flag, g_trace};
-  return dispatch_n<EPI_STORE>(ng, ta, tb, g, e, stream);
+  const int tma_store = use_tma_store();
+  CUtensorMap to = ta;
+  if (tma_store) { if (int rc = make_out_map(&to, y, N, d.P, d.Q, Cout, g.BW, g.BH, g.BN)) return rc; }
+  EpiArgs e{y, nullptr, bias, relu, 0, tma_store, error_flag, g_trace};
+  return dispatch_n<EPI_STORE>(ng, ta, tb, to, g, e, stream);
 }

@@ -141,7 +141,8 @@ int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_t* idx1,
  *      saved is [4][C] = mean, invstd, scale, shift; residual / dres / y may be NULL as documented in bn.cu ---- */
 long long pdl_bn_scratch_floats(long long M, int C);
 int pdl_bn_fwd_train(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean, float* running_var,
-                     float momentum, float eps, float* y, float* saved, float* scratch, long long M, int C, int relu, cudaStream_t stream);
+                     long long* num_batches_tracked, float momentum, float eps, float* y, float* saved, float* scratch, long long M, int C,
+                     int relu, cudaStream_t stream);
 int pdl_bn_fwd_eval(const float* x, const float* residual, const float* gamma, const float* beta, const float* running_mean,
                     const float* running_var, float eps, float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream);
 int pdl_bn_bwd(const float* x, const float* dy, const float* y, const float* gamma, const float* saved, float* dx, float* dres, float* dgamma,

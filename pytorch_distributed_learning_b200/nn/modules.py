@@ -79,10 +79,8 @@ class BatchNorm2d(tnn.BatchNorm2d):
         if _native(x) and self.affine and self.track_running_stats and self.momentum is not None and (residual is None or _native(residual)):
             from ..ops import functional as NF
 
-            if self.training and self.num_batches_tracked is not None:
-                self.num_batches_tracked.add_(1)
             return NF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum, self.eps,
-                                 relu, residual)
+                                 relu, residual, self.num_batches_tracked)  # the step counter is bumped by the finalize kernel
         y = super().forward(x)
         if residual is not None:
             y = y + residual

@@ -16,7 +16,7 @@ _CL = torch.channels_last
 
 class _BatchNormAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, weight, bias, running_mean, running_var, momentum, eps, relu):
+    def forward(ctx, x, residual, weight, bias, running_mean, running_var, num_batches_tracked, momentum, eps, relu):
         L = _lib.cuda()
         x = _nhwc(x)
         if residual is not None:
@@ -26,8 +26,8 @@ class _BatchNormAct(torch.autograd.Function):
         y = torch.empty_like(x, memory_format=_CL)
         saved = torch.empty((4, C), dtype=x.dtype, device=x.device)
         sc = scratch(L.pdl_bn_scratch_floats(M, C) * 4, x.device, "bn")
-        _ok(L.pdl_bn_fwd_train(_p(x), _p(residual), _p(weight), _p(bias), _p(running_mean), _p(running_var), float(momentum), float(eps), _p(y),
-                               _p(saved), _p(sc), M, C, int(relu), _stream(x)), "batch norm forward")
+        _ok(L.pdl_bn_fwd_train(_p(x), _p(residual), _p(weight), _p(bias), _p(running_mean), _p(running_var), _p(num_batches_tracked), float(momentum),
+                               float(eps), _p(y), _p(saved), _p(sc), M, C, int(relu), _stream(x)), "batch norm forward")
         ctx.relu, ctx.has_res = bool(relu), residual is not None
         # the ReLU mask is recomputed from x unless a residual was added (then it comes from y)
         ctx.save_for_backward(x, weight, saved, y if (ctx.relu and ctx.has_res) else None)
@@ -47,15 +47,18 @@ class _BatchNormAct(torch.autograd.Function):
         sc = scratch(L.pdl_bn_scratch_floats(M, C) * 4, x.device, "bn")
         _ok(L.pdl_bn_bwd(_p(x), _p(dy), _p(y), _p(weight), _p(saved), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(sc), M, C, int(ctx.relu),
                          _stream(x)), "batch norm backward")
-        return dx, dres, dgamma, dbeta, None, None, None, None, None
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None
 
 
-def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None):
+def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None, num_batches_tracked=None):
+    """``num_batches_tracked`` (int64 tensor or None) is incremented by the training forward, on the device."""
     C = x.shape[1]
     if C % 4 != 0:
+        if training and num_batches_tracked is not None:
+            num_batches_tracked.add_(1)
         return _torch_form(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual)
     if training:
-        return _BatchNormAct.apply(x, residual, weight, bias, running_mean, running_var, momentum, eps, relu)
+        return _BatchNormAct.apply(x, residual, weight, bias, running_mean, running_var, num_batches_tracked, momentum, eps, relu)
     # eval mode: an affine map of the input; gradients (if any) flow through plain tensor ops
     if torch.is_grad_enabled() and (x.requires_grad or weight.requires_grad or (residual is not None and residual.requires_grad)):
         return _torch_form(x, weight, bias, running_mean, running_var, False, momentum, eps, relu, residual)

@@ -214,11 +214,11 @@ def cross_entropy(logits, target):
     return _CrossEntropy.apply(logits, target)
 
 
-def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None):
+def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None, num_batches_tracked=None):
     """``act(bn(x) [+ residual])`` in one pass (the tail of every ResNet block)."""
     from . import bn
 
-    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual)
+    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual, num_batches_tracked)
 
 
 class _GlobalAvgPool(torch.autograd.Function):

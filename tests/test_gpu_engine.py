@@ -61,8 +61,11 @@ def test_graphed_trainstep_matches_torch(opt_kw, batch):
     losses = [step(x, y).item() for x, y in batches]
     ref, ref_losses = _reference_run(state, batches, opt_kw)
     torch.testing.assert_close(torch.tensor(losses), torch.tensor(ref_losses), rtol=1e-4, atol=1e-5)
+    # atol: two fp32 implementations can pick different arg-maxes for pool windows whose candidates differ by an ulp
+    # (each implementation disagrees with an fp64 oracle about once per ~1e6 windows, scripts/dbg_strict.py); one such
+    # flip moves a few weight gradients by ~5e-5, i.e. a parameter by lr/(1-momentum) times that
     for (n, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
-        torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5, msg=lambda m, n=n: "%s: %s" % (n, m))
+        torch.testing.assert_close(a, b, rtol=1e-4, atol=5e-5, msg=lambda m, n=n: "%s: %s" % (n, m))
     assert step.kernels_per_step() > 0
     # state_dict keys are the reference model's
     assert list(model.state_dict().keys())[0] == "conv1.weight"
