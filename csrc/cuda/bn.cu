@@ -34,8 +34,31 @@ __device__ __forceinline__ Welford from_shifted(float n, float pivot, float s, f
 }
 
 // partial[(split * C + c) * 3 + {0,1,2}] = (count, mean, M2) of x[rows of this split][c]
+struct FinalizeArgs {
+  const float* gamma; const float* beta; float* running_mean; float* running_var; float momentum, eps; float* saved;
+  long long* num_batches_tracked;
+};
+__device__ void finalize_group(const float* partial, int splits, int C, int cgroup, const FinalizeArgs& f);
+__device__ unsigned int g_bn_done[2048];  // per channel group: CTAs of the running statistics kernel that have published their partials
+
+// Returns true in the LAST CTA of this channel group to finish (its reads of the other CTAs' partials are ordered
+// after their writes); resets the counter for the next launch.  Launches are stream-ordered, so one array suffices.
+__device__ __forceinline__ bool last_cta_of_group() {
+  __shared__ bool is_last;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const unsigned done = atomicAdd(&g_bn_done[blockIdx.x], 1u);
+    is_last = done == gridDim.y - 1;
+    if (is_last) g_bn_done[blockIdx.x] = 0;
+    __threadfence();
+  }
+  __syncthreads();
+  return is_last;
+}
+
 __global__ void __launch_bounds__(kThreads) bn_stats_kernel(const float* __restrict__ x, float* __restrict__ partial, long long M, int C,
-                                                            long long rows_per_split) {
+                                                            long long rows_per_split, const FinalizeArgs fin) {
   const int ql = threadIdx.x % kQL, rl = threadIdx.x / kQL;
   const int c = blockIdx.x * kCG + ql * 4;
   const long long r_lo = blockIdx.y * rows_per_split, r_hi = min(M, r_lo + rows_per_split);
@@ -70,27 +93,29 @@ __global__ void __launch_bounds__(kThreads) bn_stats_kernel(const float* __restr
     float* o = partial + (static_cast<long long>(blockIdx.y) * C + blockIdx.x * kCG + ch) * 3;
     o[0] = t.n; o[1] = t.mean; o[2] = t.m2;
   }
+  if (last_cta_of_group()) finalize_group(partial, gridDim.y, C, blockIdx.x, fin);
 }
 
-// Merge the splits per channel without per-split divisions: mean = sum(n_i mean_i) / n, then
-// M2 = sum(M2_i + n_i (mean_i - mean)^2).  32 channels x 32 slices of the split list per CTA, fixed order.
-constexpr int kFinSlices = 32;
-__global__ void __launch_bounds__(kCG * kFinSlices) bn_finalize_kernel(const float* __restrict__ partial, int splits, int C,
-                                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                                       float* __restrict__ running_mean, float* __restrict__ running_var,
-                                                                       float momentum, float eps, float* __restrict__ saved,
-                                                                       long long* __restrict__ num_batches_tracked) {
-  if (num_batches_tracked && blockIdx.x == 0 && threadIdx.x == 0) *num_batches_tracked += 1;  // nn.BatchNorm2d's step counter
+// Merge the splits of one channel group without per-split divisions: mean = sum(n_i mean_i) / n, then
+// M2 = sum(M2_i + n_i (mean_i - mean)^2).  Runs in the last CTA of the group: 32 channels x 8 slices of the split
+// list, fixed order; partials come from other CTAs, so they are read through L2 (__ldcg).
+constexpr int kFinSlices = kThreads / kCG;
+__device__ void finalize_group(const float* partial, int splits, int C, int cgroup, const FinalizeArgs& f) {
+  const float* gamma = f.gamma; const float* beta = f.beta;
+  float* running_mean = f.running_mean; float* running_var = f.running_var; float* saved = f.saved;
+  const float momentum = f.momentum, eps = f.eps;
+  if (f.num_batches_tracked && cgroup == 0 && threadIdx.x == 0) *f.num_batches_tracked += 1;  // nn.BatchNorm2d's step counter
   const int ch = threadIdx.x % kCG, sl = threadIdx.x / kCG;
-  const int c = blockIdx.x * kCG + ch;
+  const int c = cgroup * kCG + ch;
   __shared__ float sh_a[kFinSlices][kCG + 1], sh_b[kFinSlices][kCG + 1];
   float sn = 0.f, sm = 0.f;
   if (c < C) {
-#pragma unroll 4
+#pragma unroll 8
     for (int s = sl; s < splits; s += kFinSlices) {
       const float* p = partial + (static_cast<long long>(s) * C + c) * 3;
-      sn += p[0];
-      sm = fmaf(p[0], p[1], sm);
+      const float pn = __ldcg(p);
+      sn += pn;
+      sm = fmaf(pn, __ldcg(p + 1), sm);
     }
   }
   sh_a[sl][ch] = sn; sh_b[sl][ch] = sm;
@@ -102,11 +127,11 @@ __global__ void __launch_bounds__(kCG * kFinSlices) bn_finalize_kernel(const flo
   __syncthreads();
   float m2 = 0.f;
   if (c < C) {
-#pragma unroll 4
+#pragma unroll 8
     for (int s = sl; s < splits; s += kFinSlices) {
       const float* p = partial + (static_cast<long long>(s) * C + c) * 3;
-      const float d = p[1] - mean;
-      m2 += fmaf(p[0] * d, d, p[2]);
+      const float d = __ldcg(p + 1) - mean;
+      m2 += fmaf(__ldcg(p) * d, d, __ldcg(p + 2));
     }
   }
   sh_a[sl][ch] = m2;
@@ -173,11 +198,15 @@ __device__ __forceinline__ float4 act_grad(float4 g, float4 v, float4 yv, float4
   return g;
 }
 
+struct BwdFinalizeArgs { float M; const float* gamma; float* dgamma; float* dbeta; float* coef; };
+__device__ void bwd_finalize_group(const float* partial, int splits, int C, int cgroup, const float* saved, const BwdFinalizeArgs& f);
+
 // partial[(split * C + c) * 2 + {0,1}] = (sum g, sum g * xhat) over the rows of the split
 template <int kMask>
 __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __restrict__ x, const float* __restrict__ dy,
                                                                 const float* __restrict__ y, const float* __restrict__ saved,
-                                                                float* __restrict__ partial, long long M, int C, long long rows_per_split) {
+                                                                float* __restrict__ partial, long long M, int C, long long rows_per_split,
+                                                                const BwdFinalizeArgs fin) {
   const int ql = threadIdx.x % kQL, rl = threadIdx.x / kQL;
   const int c = blockIdx.x * kCG + ql * 4;
   const long long r_lo = blockIdx.y * rows_per_split, r_hi = min(M, r_lo + rows_per_split);
@@ -212,21 +241,20 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __r
     for (int i = 0; i < kRL; ++i) t += grp == 0 ? a1[i][ch] : a2[i][ch];
     partial[(static_cast<long long>(blockIdx.y) * C + blockIdx.x * kCG + ch) * 2 + grp] = t;
   }
+  if (last_cta_of_group()) bwd_finalize_group(partial, gridDim.y, C, blockIdx.x, saved, fin);
 }
 
-// dgamma, dbeta and the per-channel coefficients of dx = a*g + b*x + d
-__global__ void __launch_bounds__(kCG * kFinSlices) bn_bwd_finalize_kernel(const float* __restrict__ partial, int splits, int C, float M,
-                                                                   const float* __restrict__ gamma, const float* __restrict__ saved,
-                                                                   float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                                   float* __restrict__ coef) {
+// dgamma, dbeta and the per-channel coefficients of dx = a*g + b*x + d (last CTA of the channel group)
+__device__ void bwd_finalize_group(const float* partial, int splits, int C, int cgroup, const float* saved, const BwdFinalizeArgs& f) {
+  const float M = f.M; const float* gamma = f.gamma; float* dgamma = f.dgamma; float* dbeta = f.dbeta; float* coef = f.coef;
   const int ch = threadIdx.x % kCG, sl = threadIdx.x / kCG;
-  const int c = blockIdx.x * kCG + ch;
+  const int c = cgroup * kCG + ch;
   __shared__ float h1[kFinSlices][kCG + 1], h2[kFinSlices][kCG + 1];
   float s1 = 0.f, s2 = 0.f;
   if (c < C) {
-#pragma unroll 4
+#pragma unroll 8
     for (int s = sl; s < splits; s += kFinSlices) {
-      const float2 p = *reinterpret_cast<const float2*>(partial + (static_cast<long long>(s) * C + c) * 2);
+      const float2 p = __ldcg(reinterpret_cast<const float2*>(partial + (static_cast<long long>(s) * C + c) * 2));
       s1 += p.x; s2 += p.y;
     }
   }
@@ -269,11 +297,13 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const float4* __
 
 int choose_splits(long long M, int C) {
   const int cgroups = (C + kCG - 1) / kCG;
-  long long s = (8 * 148 + cgroups - 1) / cgroups;  // ~8 CTAs per SM in total
-  const long long by_rows = (M + 127) / 128;        // at least 4 rows per thread
+  // ~4 CTAs per SM in total (128 KB of loads in flight per SM) but few enough splits that the merge in each
+  // channel group's last CTA (8 slices over the split list) stays a small tail of the kernel
+  long long s = (4 * 148 + cgroups - 1) / cgroups;
+  const long long by_rows = (M + 127) / 128;  // at least 4 rows per thread
   if (s > by_rows) s = by_rows;
   if (s < 1) s = 1;
-  if (s > 1024) s = 1024;
+  if (s > 296) s = 296;
   return static_cast<int>(s);
 }
 
@@ -312,9 +342,8 @@ PDL_API int pdl_bn_fwd_train(const float* x, const float* residual, const float*
   const int splits = choose_splits(M, C);
   const long long rps = (M + splits - 1) / splits;
   const int cgroups = (C + kCG - 1) / kCG;
-  bn_stats_kernel<<<dim3(cgroups, splits), kThreads, 0, stream>>>(x, scratch, M, C, rps);
-  bn_finalize_kernel<<<cgroups, kCG * kFinSlices, 0, stream>>>(scratch, splits, C, gamma, beta, running_mean, running_var, momentum, eps, saved,
-                                                                   num_batches_tracked);
+  const FinalizeArgs fin{gamma, beta, running_mean, running_var, momentum, eps, saved, num_batches_tracked};
+  bn_stats_kernel<<<dim3(cgroups, splits), kThreads, 0, stream>>>(x, scratch, M, C, rps, fin);  // + finalize in each group's last CTA
   apply(x, residual, y, saved + 2ll * C, saved + 3ll * C, M, C, relu, stream);
   PDL_LAUNCH_CHECK();
   return 0;
@@ -339,15 +368,16 @@ PDL_API int pdl_bn_bwd(const float* x, const float* dy, const float* y, const fl
   const int splits = choose_splits(M, C);
   const long long rps = (M + splits - 1) / splits;
   const int cgroups = (C + kCG - 1) / kCG;
+  if (cgroups > 2048) { pdl_set_error("batch norm: more than 65536 channels"); return -1; }
   float* partial = scratch;
   float* coef = scratch + static_cast<long long>(splits) * C * 3;
   const int mask = !relu ? 0 : (dres ? 2 : 1);
   if (mask == 2 && !y) { pdl_set_error("batch norm backward: the residual+ReLU form needs the forward output"); return -1; }
   const dim3 grid(cgroups, splits);
-  if (mask == 0) bn_bwd_stats_kernel<0><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps);
-  else if (mask == 1) bn_bwd_stats_kernel<1><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps);
-  else bn_bwd_stats_kernel<2><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps);
-  bn_bwd_finalize_kernel<<<cgroups, kCG * kFinSlices, 0, stream>>>(partial, splits, C, static_cast<float>(M), gamma, saved, dgamma, dbeta, coef);
+  const BwdFinalizeArgs fin{static_cast<float>(M), gamma, dgamma, dbeta, coef};
+  if (mask == 0) bn_bwd_stats_kernel<0><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
+  else if (mask == 1) bn_bwd_stats_kernel<1><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
+  else bn_bwd_stats_kernel<2><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
   const long long total4 = M * C / 4;
   const unsigned blocks = static_cast<unsigned>(pdl_ceil_div(total4, kThreads));
   const float4 *x4 = reinterpret_cast<const float4*>(x), *g4 = reinterpret_cast<const float4*>(dy), *y4 = reinterpret_cast<const float4*>(y);

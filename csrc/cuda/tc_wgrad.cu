@@ -223,16 +223,25 @@ int act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int b
 
 int env_int(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
 
-// Channel tiles: M (= Cout) tile 128 (64 when Cout == 64), N (= Cin) tile 64 (32 when Cin == 32).
+// Channel tiles: M (= Cout) tile 128 (64 when Cout == 64).  N (= Cin) tile as wide as the TMEM budget allows --
+// every operand byte comes through L2 (~42 B/clk/SM), so FLOPs per loaded byte is what bounds this kernel:
+// 1x1 filters take 256 / 128 columns, filter rows of up to 3 taps 128 (3 accumulators = 384 TMEM columns).
 int wg_m_tile(int Cout) { return Cout == 64 ? 64 : (Cout % 128 == 0 ? 128 : 0); }
-int wg_n_tile(int Cin) { return Cin == 32 ? 32 : (Cin % 64 == 0 ? 64 : 0); }
+int wg_n_tile(int Cin, int KW = 3) {
+  if (Cin == 32) return 32;
+  if (KW == 1 && Cin % 256 == 0) return 256;
+  if (Cin % 128 == 0) return 128;
+  return Cin % 64 == 0 ? 64 : 0;
+}
 
 bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KH, int KW, int pad, WgGeom* g) {
-  const int mt = wg_m_tile(Cout), nt = wg_n_tile(Cin);
-  if (!mt || !nt || KW > kMaxTapsPerCta) return false;
+  const int mt = wg_m_tile(Cout), nt = wg_n_tile(Cin, KW);
+  if (!mt || !nt || KW > 3) return false;
   int bw = (Q + 7) / 8 * 8;  // K stage = bw x bh pixels, a multiple of 8 rows (one MMA = 8 pixels)
   if (bw > 64) return false;
-  int bh = 64 / bw;
+  // wide channel tiles take 32-pixel stages so that 3-4 stages still fit in shared memory
+  const int stage_rows = (mt / 32 + KW * (nt / 32)) > 10 ? 32 : 64;
+  int bh = stage_rows / bw;
   if (bh < 1) bh = 1;
   g->BW = bw; g->BH = bh; g->strips = (P + bh - 1) / bh; g->wstrips = 1; g->units = N * g->strips;
   g->RT = 1; g->stride_w = 1;
@@ -243,6 +252,7 @@ bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KH, int KW, int pad
   // K split: enough CTAs to occupy the chip (grid = KH x splits x channel tiles), few enough that the partial sums stay cheap
   const int tiles = (Cout / mt) * (Cin / nt);
   int splits = (2 * 148 + KH * tiles - 1) / (KH * tiles);
+  if (KH * tiles < 74) splits = 148 / (KH * tiles);  // few big tiles: one wave, each split costs a full dW of partial traffic
   if (splits > 48) splits = 48;
   if (splits > g->units) splits = g->units;
   if (splits < 1) splits = 1;
@@ -309,8 +319,12 @@ PDL_API int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* 
   if (int rc = act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.tma_swizzle, 1)) return rc;
   if (int rc = act_map(&tb, x, N, H, W, Cin, g.BW, g.BH, g.tma_swizzle, stride)) return rc;
   int rc = -3;
-  const int mt = wg_m_tile(Cout), nt = wg_n_tile(Cin);
-  if (mt == 128 && nt == 64) rc = launch_wg<128, 64>(ta, tb, g, KH, scratch, error_flag, stream);
+  const int mt = wg_m_tile(Cout), nt = wg_n_tile(Cin, KW);
+  if (mt == 128 && nt == 256) rc = launch_wg<128, 256>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (mt == 128 && nt == 128) rc = launch_wg<128, 128>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (mt == 64 && nt == 256) rc = launch_wg<64, 256>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (mt == 64 && nt == 128) rc = launch_wg<64, 128>(ta, tb, g, KH, scratch, error_flag, stream);
+  else if (mt == 128 && nt == 64) rc = launch_wg<128, 64>(ta, tb, g, KH, scratch, error_flag, stream);
   else if (mt == 128 && nt == 32) rc = launch_wg<128, 32>(ta, tb, g, KH, scratch, error_flag, stream);
   else if (mt == 64 && nt == 32) rc = launch_wg<64, 32>(ta, tb, g, KH, scratch, error_flag, stream);
   else if (mt == 64 && nt == 64) rc = launch_wg<64, 64>(ta, tb, g, KH, scratch, error_flag, stream);
