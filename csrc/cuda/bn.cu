@@ -174,26 +174,28 @@ __device__ __forceinline__ int quad_channel(long long i, int C4) {
 template <bool kRelu, bool kRes>
 __global__ void __launch_bounds__(kThreads) bn_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ res, float4* __restrict__ y,
                                                             const float* __restrict__ scale, const float* __restrict__ shift, long long total4,
-                                                            int C4) {
+                                                            int C4, uint8_t* __restrict__ relu_mask) {
   const long long i = blockIdx.x * static_cast<long long>(kThreads) + threadIdx.x;
   if (i >= total4) return;
   const int c = quad_channel(i, C4);
   const float4 v = x[i], s = *reinterpret_cast<const float4*>(scale + c), h = *reinterpret_cast<const float4*>(shift + c);
   float4 o = make_float4(fmaf(v.x, s.x, h.x), fmaf(v.y, s.y, h.y), fmaf(v.z, s.z, h.z), fmaf(v.w, s.w, h.w));
   if (kRes) { const float4 r = res[i]; o.x += r.x; o.y += r.y; o.z += r.z; o.w += r.w; }
+  if (kRelu && kRes && relu_mask)  // one byte per 4 elements: what backward needs of y, at 1/16 of its size
+    relu_mask[i] = static_cast<uint8_t>((o.x > 0.f) | ((o.y > 0.f) << 1) | ((o.z > 0.f) << 2) | ((o.w > 0.f) << 3));
   if (kRelu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
   y[i] = o;
 }
 
 // The gradient that reaches the normalisation: dy through the activation.  kMask 0: no activation; 1: ReLU mask
-// recomputed from x (no residual); 2: ReLU mask from the stored output y.
+// recomputed from x (no residual); 2: ReLU mask bits `m` stored by the forward pass (residual form).
 template <int kMask>
-__device__ __forceinline__ float4 act_grad(float4 g, float4 v, float4 yv, float4 s, float4 h) {
+__device__ __forceinline__ float4 act_grad(float4 g, float4 v, unsigned m, float4 s, float4 h) {
   if (kMask == 1) {
     g.x = fmaf(v.x, s.x, h.x) > 0.f ? g.x : 0.f; g.y = fmaf(v.y, s.y, h.y) > 0.f ? g.y : 0.f;
     g.z = fmaf(v.z, s.z, h.z) > 0.f ? g.z : 0.f; g.w = fmaf(v.w, s.w, h.w) > 0.f ? g.w : 0.f;
   } else if (kMask == 2) {
-    g.x = yv.x > 0.f ? g.x : 0.f; g.y = yv.y > 0.f ? g.y : 0.f; g.z = yv.z > 0.f ? g.z : 0.f; g.w = yv.w > 0.f ? g.w : 0.f;
+    g.x = (m & 1u) ? g.x : 0.f; g.y = (m & 2u) ? g.y : 0.f; g.z = (m & 4u) ? g.z : 0.f; g.w = (m & 8u) ? g.w : 0.f;
   }
   return g;
 }
@@ -204,7 +206,7 @@ __device__ void bwd_finalize_group(const float* partial, int splits, int C, int 
 // partial[(split * C + c) * 2 + {0,1}] = (sum g, sum g * xhat) over the rows of the split
 template <int kMask>
 __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __restrict__ x, const float* __restrict__ dy,
-                                                                const float* __restrict__ y, const float* __restrict__ saved,
+                                                                const uint8_t* __restrict__ relu_mask, const float* __restrict__ saved,
                                                                 float* __restrict__ partial, long long M, int C, long long rows_per_split,
                                                                 const BwdFinalizeArgs fin) {
   const int ql = threadIdx.x % kQL, rl = threadIdx.x / kQL;
@@ -215,7 +217,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __r
     const long long ld = C / 4;
     const float4* xp = reinterpret_cast<const float4*>(x + c);
     const float4* gp = reinterpret_cast<const float4*>(dy + c);
-    const float4* yp = reinterpret_cast<const float4*>((kMask == 2 ? y : x) + c);
+    const uint8_t* mp = relu_mask + c / 4;
     const float4 mu = *reinterpret_cast<const float4*>(saved + c), is = *reinterpret_cast<const float4*>(saved + C + c);
     const float4 sc = *reinterpret_cast<const float4*>(saved + 2 * C + c), sf = *reinterpret_cast<const float4*>(saved + 3 * C + c);
     float4 s1 = make_float4(0.f, 0.f, 0.f, 0.f), s2 = s1;
@@ -223,9 +225,9 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __r
     for (long long r = r_lo + rl; r < r_hi; r += kRL) {
       const float4 v = __ldg(xp + r * ld);
       float4 g = __ldg(gp + r * ld);
-      float4 yv = v;
-      if (kMask == 2) yv = __ldg(yp + r * ld);
-      g = act_grad<kMask>(g, v, yv, sc, sf);
+      unsigned m = 0;
+      if (kMask == 2) m = __ldg(mp + r * ld);
+      g = act_grad<kMask>(g, v, m, sc, sf);
       s1.x += g.x; s1.y += g.y; s1.z += g.z; s1.w += g.w;
       s2.x = fmaf(g.x, (v.x - mu.x) * is.x, s2.x); s2.y = fmaf(g.y, (v.y - mu.y) * is.y, s2.y);
       s2.z = fmaf(g.z, (v.z - mu.z) * is.z, s2.z); s2.w = fmaf(g.w, (v.w - mu.w) * is.w, s2.w);
@@ -275,18 +277,19 @@ __device__ void bwd_finalize_group(const float* partial, int splits, int C, int 
 
 template <int kMask, bool kRes>
 __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ dy,
-                                                                const float4* __restrict__ y, float4* __restrict__ dx, float4* __restrict__ dres,
-                                                                const float* __restrict__ coef, const float* __restrict__ saved,
-                                                                long long total4, int C4) {
+                                                                const uint8_t* __restrict__ relu_mask, float4* __restrict__ dx,
+                                                                float4* __restrict__ dres, const float* __restrict__ coef,
+                                                                const float* __restrict__ saved, long long total4, int C4) {
   const long long i = blockIdx.x * static_cast<long long>(kThreads) + threadIdx.x;
   if (i >= total4) return;
   const int c = quad_channel(i, C4), C = 4 * C4;
   const float4 v = x[i];
-  float4 g = dy[i], yv = v;
-  if (kMask == 2) yv = y[i];
+  float4 g = dy[i];
+  unsigned m = 0;
+  if (kMask == 2) m = relu_mask[i];
   if (kMask != 0) {
     const float4 sc = *reinterpret_cast<const float4*>(saved + 2 * C + c), sf = *reinterpret_cast<const float4*>(saved + 3 * C + c);
-    g = act_grad<kMask>(g, v, yv, sc, sf);
+    g = act_grad<kMask>(g, v, m, sc, sf);
   }
   const float4 a = *reinterpret_cast<const float4*>(coef + c), b = *reinterpret_cast<const float4*>(coef + C + c),
                d = *reinterpret_cast<const float4*>(coef + 2 * C + c);
@@ -319,12 +322,13 @@ void launch_apply(F&& f, int relu, bool res) {
 }
 
 void apply(const float* x, const float* residual, float* y, const float* scale, const float* shift, long long M, int C, int relu,
-           cudaStream_t stream) {
+           uint8_t* relu_mask, cudaStream_t stream) {
   const long long total4 = M * C / 4;
   const unsigned blocks = static_cast<unsigned>(pdl_ceil_div(total4, kThreads));
   launch_apply([&](auto r, auto s) {
     bn_apply_kernel<decltype(r)::value, decltype(s)::value><<<blocks, kThreads, 0, stream>>>(
-        reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(residual), reinterpret_cast<float4*>(y), scale, shift, total4, C / 4);
+        reinterpret_cast<const float4*>(x), reinterpret_cast<const float4*>(residual), reinterpret_cast<float4*>(y), scale, shift, total4, C / 4,
+        relu_mask);
   }, relu, residual != nullptr);
 }
 
@@ -333,18 +337,19 @@ void apply(const float* x, const float* residual, float* y, const float* scale, 
 // floats of scratch the BN entry points need: split partials + 3 per-channel coefficient rows
 PDL_API long long pdl_bn_scratch_floats(long long M, int C) { return static_cast<long long>(choose_splits(M, C)) * C * 3 + 3ll * C; }
 
-// Training forward.  num_batches_tracked (may be NULL) is incremented on the device.  saved [4][C] (mean, invstd, scale, shift) is kept for backward.  relu != 0 fuses the
-// activation, residual != nullptr adds the skip connection before it.
+// Training forward.  num_batches_tracked (may be NULL) is incremented on the device.  saved [4][C] (mean, invstd,
+// scale, shift) is kept for backward.  relu != 0 fuses the activation, residual != nullptr adds the skip connection
+// before it; with both, relu_mask (M*C/4 bytes, 4 sign bits each) receives what backward needs of the output.
 PDL_API int pdl_bn_fwd_train(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean,
                              float* running_var, long long* num_batches_tracked, float momentum, float eps, float* y, float* saved,
-                             float* scratch, long long M, int C, int relu, cudaStream_t stream) {
+                             uint8_t* relu_mask, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
   if (check_c(C)) return -1;
   const int splits = choose_splits(M, C);
   const long long rps = (M + splits - 1) / splits;
   const int cgroups = (C + kCG - 1) / kCG;
   const FinalizeArgs fin{gamma, beta, running_mean, running_var, momentum, eps, saved, num_batches_tracked};
   bn_stats_kernel<<<dim3(cgroups, splits), kThreads, 0, stream>>>(x, scratch, M, C, rps, fin);  // + finalize in each group's last CTA
-  apply(x, residual, y, saved + 2ll * C, saved + 3ll * C, M, C, relu, stream);
+  apply(x, residual, y, saved + 2ll * C, saved + 3ll * C, M, C, relu, relu_mask, stream);
   PDL_LAUNCH_CHECK();
   return 0;
 }
@@ -355,15 +360,16 @@ PDL_API int pdl_bn_fwd_eval(const float* x, const float* residual, const float* 
   float* scale = scratch;
   float* shift = scratch + C;
   bn_eval_coeffs_kernel<<<(C + 255) / 256, 256, 0, stream>>>(C, gamma, beta, running_mean, running_var, eps, scale, shift);
-  apply(x, residual, y, scale, shift, M, C, relu, stream);
+  apply(x, residual, y, scale, shift, M, C, relu, nullptr, stream);
   PDL_LAUNCH_CHECK();
   return 0;
 }
 
 // Training backward of y = act(bn(x) [+ residual]): dx, dgamma, dbeta and, when dres != nullptr, the gradient
-// of the residual input (= dy through the activation).  y is only read when relu != 0 and dres != nullptr.
-PDL_API int pdl_bn_bwd(const float* x, const float* dy, const float* y, const float* gamma, const float* saved, float* dx, float* dres,
-                       float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
+// of the residual input (= dy through the activation).  relu_mask (written by the forward pass) is only read when
+// relu != 0 and dres != nullptr; the plain ReLU form recomputes the mask from x.
+PDL_API int pdl_bn_bwd(const float* x, const float* dy, const uint8_t* relu_mask, const float* gamma, const float* saved, float* dx,
+                       float* dres, float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
   if (check_c(C)) return -1;
   const int splits = choose_splits(M, C);
   const long long rps = (M + splits - 1) / splits;
@@ -372,15 +378,17 @@ PDL_API int pdl_bn_bwd(const float* x, const float* dy, const float* y, const fl
   float* partial = scratch;
   float* coef = scratch + static_cast<long long>(splits) * C * 3;
   const int mask = !relu ? 0 : (dres ? 2 : 1);
-  if (mask == 2 && !y) { pdl_set_error("batch norm backward: the residual+ReLU form needs the forward output"); return -1; }
+  if (mask == 2 && !relu_mask) { pdl_set_error("batch norm backward: the residual+ReLU form needs the forward pass's mask"); return -1; }
   const dim3 grid(cgroups, splits);
   const BwdFinalizeArgs fin{static_cast<float>(M), gamma, dgamma, dbeta, coef};
+  const uint8_t* y = relu_mask;
+  const uint8_t* y4 = relu_mask;
   if (mask == 0) bn_bwd_stats_kernel<0><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
   else if (mask == 1) bn_bwd_stats_kernel<1><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
   else bn_bwd_stats_kernel<2><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
   const long long total4 = M * C / 4;
   const unsigned blocks = static_cast<unsigned>(pdl_ceil_div(total4, kThreads));
-  const float4 *x4 = reinterpret_cast<const float4*>(x), *g4 = reinterpret_cast<const float4*>(dy), *y4 = reinterpret_cast<const float4*>(y);
+  const float4 *x4 = reinterpret_cast<const float4*>(x), *g4 = reinterpret_cast<const float4*>(dy);
   float4 *dx4 = reinterpret_cast<float4*>(dx), *dr4 = reinterpret_cast<float4*>(dres);
   if (mask == 0 && !dres) bn_bwd_apply_kernel<0, false><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
   else if (mask == 0) bn_bwd_apply_kernel<0, true><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);

@@ -135,9 +135,12 @@ __global__ void __launch_bounds__(kThreads) maxpool_fwd_v4_kernel(const float4* 
   y[i] = best;
   idx[i] = make_uchar4(a0, a1, a2, a3);
 }
+// kStride > 0 fixes the stride at compile time (the window search is otherwise bound by integer divisions)
+template <int kStride>
 __global__ void __launch_bounds__(kThreads) maxpool_bwd_v4_kernel(const float4* __restrict__ dy, const uchar4* __restrict__ idx,
                                                                   const float4* __restrict__ pooled, float4* __restrict__ dx, unsigned total4, int H,
-                                                                  int W, int C4, int k, int stride, int pad, int P, int Q, int fuse_relu) {
+                                                                  int W, int C4, int k, int stride_rt, int pad, int P, int Q, int fuse_relu) {
+  const int stride = kStride > 0 ? kStride : stride_rt;
   const unsigned i = blockIdx.x * kThreads + threadIdx.x;
   if (i >= total4) return;
   const unsigned c = i % C4;
@@ -313,7 +316,8 @@ PDL_API int pdl_maxpool_bwd(const float* dy, const uint8_t* idx, const float* po
   int P = (H + 2 * pad - k) / stride + 1, Q = (W + 2 * pad - k) / stride + 1;
   long long total = static_cast<long long>(N) * H * W * C;
   if (total && C % 4 == 0 && total < (1ll << 31)) {
-    maxpool_bwd_v4_kernel<<<launch_1d(total / 4), kThreads, 0, stream>>>(
+    auto kern = stride == 1 ? maxpool_bwd_v4_kernel<1> : stride == 2 ? maxpool_bwd_v4_kernel<2> : maxpool_bwd_v4_kernel<0>;
+    kern<<<launch_1d(total / 4), kThreads, 0, stream>>>(
         reinterpret_cast<const float4*>(dy), reinterpret_cast<const uchar4*>(idx), reinterpret_cast<const float4*>(pooled),
         reinterpret_cast<float4*>(dx), static_cast<unsigned>(total / 4), H, W, C / 4, k, stride, pad, P, Q, fuse_relu);
   } else if (total) maxpool_bwd_kernel<<<launch_1d(total), kThreads, 0, stream>>>(dy, idx, pooled, dx, N, H, W, C, k, stride, pad, P, Q, fuse_relu);

@@ -178,7 +178,8 @@ __global__ void wgrad_finish_kernel(const float* __restrict__ partial, int split
     const int tap = i % taps, ci = (i / taps) % Cin, co = i / (taps * Cin);
     const float* src = partial + (static_cast<long long>(tap) * Cout + co) * Cin + ci;
     float acc = 0.f;
-    for (int s = 0; s < splits; ++s) acc += src[static_cast<long long>(s) * per_split];
+#pragma unroll 8
+    for (int s = 0; s < splits; ++s) acc += __ldg(src + static_cast<long long>(s) * per_split);  // independent loads, fixed order
     dw[i] = acc;
   }
   // bias gradient: one warp per channel, lanes stride over the partial rows, fixed shuffle tree (deterministic)
@@ -253,7 +254,7 @@ bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KH, int KW, int pad
   const int tiles = (Cout / mt) * (Cin / nt);
   int splits = (2 * 148 + KH * tiles - 1) / (KH * tiles);
   if (KH * tiles < 74) splits = 148 / (KH * tiles);  // few big tiles: one wave, each split costs a full dW of partial traffic
-  if (splits > 48) splits = 48;
+  if (splits > 148) splits = 148;
   if (splits > g->units) splits = g->units;
   if (splits < 1) splits = 1;
   g->units_per_cta = (g->units + splits - 1) / splits;
@@ -349,7 +350,8 @@ __global__ void stem_wgrad_finish_kernel(const float* __restrict__ partial, int 
   const float* src = partial + (static_cast<long long>(r) * Cout + co) * 32 + s * 4 + c;
   const long long per_split = static_cast<long long>(KH) * Cout * 32;
   float acc = 0.f;
-  for (int k = 0; k < splits; ++k) acc += src[k * per_split];
+#pragma unroll 8
+  for (int k = 0; k < splits; ++k) acc += __ldg(src + k * per_split);
   dw[i] = acc;
 }
 

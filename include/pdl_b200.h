@@ -141,12 +141,12 @@ int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_t* idx1,
  *      saved is [4][C] = mean, invstd, scale, shift; residual / dres / y may be NULL as documented in bn.cu ---- */
 long long pdl_bn_scratch_floats(long long M, int C);
 int pdl_bn_fwd_train(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean, float* running_var,
-                     long long* num_batches_tracked, float momentum, float eps, float* y, float* saved, float* scratch, long long M, int C,
-                     int relu, cudaStream_t stream);
+                     long long* num_batches_tracked, float momentum, float eps, float* y, float* saved, uint8_t* relu_mask, float* scratch,
+                     long long M, int C, int relu, cudaStream_t stream); /* relu_mask: M*C/4 bytes, written for the residual+ReLU form */
 int pdl_bn_fwd_eval(const float* x, const float* residual, const float* gamma, const float* beta, const float* running_mean,
                     const float* running_var, float eps, float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream);
-int pdl_bn_bwd(const float* x, const float* dy, const float* y, const float* gamma, const float* saved, float* dx, float* dres, float* dgamma,
-               float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream);
+int pdl_bn_bwd(const float* x, const float* dy, const uint8_t* relu_mask, const float* gamma, const float* saved, float* dx, float* dres,
+               float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream);
 
 /* ---- element-wise / pooling / linear / loss (reference: nn.ReLU, nn.MaxPool2d, nn.Linear,
  *      nn.CrossEntropyLoss at launch_dist.py:13-32,58; ResNet add+ReLU / avgpool at example_launch.py:26) ---- */

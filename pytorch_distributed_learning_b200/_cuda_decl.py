@@ -79,7 +79,7 @@ def declare(L):
     sig("pdl_conv1_wgrad_fused", [P, P, P, P, P, P, P, I, P])
     # batch norm
     sig("pdl_bn_scratch_floats", [LL, I], LL)
-    sig("pdl_bn_fwd_train", [P, P, P, P, P, P, P, F, F, P, P, P, LL, I, I, P])
+    sig("pdl_bn_fwd_train", [P, P, P, P, P, P, P, F, F, P, P, P, P, LL, I, I, P])
     sig("pdl_bn_fwd_eval", [P, P, P, P, P, P, F, P, P, LL, I, I, P])
     sig("pdl_bn_bwd", [P, P, P, P, P, P, P, P, P, P, LL, I, I, P])
     # element-wise / pooling / linear / loss

@@ -25,18 +25,20 @@ class _BatchNormAct(torch.autograd.Function):
         M = N * H * W
         y = torch.empty_like(x, memory_format=_CL)
         saved = torch.empty((4, C), dtype=x.dtype, device=x.device)
+        ctx.relu, ctx.has_res = bool(relu), residual is not None
+        # backward recomputes the ReLU mask from x, unless a residual was added: then the forward kernel leaves 4 sign
+        # bits per 4 outputs (1/16 of the tensor) so that the output itself need not be re-read
+        mask = torch.empty(M * C // 4, dtype=torch.uint8, device=x.device) if (ctx.relu and ctx.has_res) else None
         sc = scratch(L.pdl_bn_scratch_floats(M, C) * 4, x.device, "bn")
         _ok(L.pdl_bn_fwd_train(_p(x), _p(residual), _p(weight), _p(bias), _p(running_mean), _p(running_var), _p(num_batches_tracked), float(momentum),
-                               float(eps), _p(y), _p(saved), _p(sc), M, C, int(relu), _stream(x)), "batch norm forward")
-        ctx.relu, ctx.has_res = bool(relu), residual is not None
-        # the ReLU mask is recomputed from x unless a residual was added (then it comes from y)
-        ctx.save_for_backward(x, weight, saved, y if (ctx.relu and ctx.has_res) else None)
+                               float(eps), _p(y), _p(saved), _p(mask), _p(sc), M, C, int(relu), _stream(x)), "batch norm forward")
+        ctx.save_for_backward(x, weight, saved, mask)
         return y
 
     @staticmethod
     def backward(ctx, dy):
         L = _lib.cuda()
-        x, weight, saved, y = ctx.saved_tensors
+        x, weight, saved, mask = ctx.saved_tensors
         dy = _nhwc(dy)
         N, C, H, W = x.shape
         M = N * H * W
@@ -45,7 +47,7 @@ class _BatchNormAct(torch.autograd.Function):
         dgamma = torch.empty(C, dtype=x.dtype, device=x.device)
         dbeta = torch.empty(C, dtype=x.dtype, device=x.device)
         sc = scratch(L.pdl_bn_scratch_floats(M, C) * 4, x.device, "bn")
-        _ok(L.pdl_bn_bwd(_p(x), _p(dy), _p(y), _p(weight), _p(saved), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(sc), M, C, int(ctx.relu),
+        _ok(L.pdl_bn_bwd(_p(x), _p(dy), _p(mask), _p(weight), _p(saved), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(sc), M, C, int(ctx.relu),
                          _stream(x)), "batch norm backward")
         return dx, dres, dgamma, dbeta, None, None, None, None, None, None
 
