@@ -7,7 +7,7 @@ The examples mirror the reference's four entry points (same flags, same prints, 
   resnet_launch.py   <- example_launch.py (ResNet-18 / CIFAR-10, launcher)
 Only the imports differ: everything comes from this package instead of torch.distributed / torch.nn /
 torchvision.  The training boxes have no network, so datasets are synthetic by default; pass --data-root to
-use torchvision's MNIST / CIFAR-10 from disk.
+read MNIST (IDX files) / CIFAR-10 (python pickles) from disk with this package's own readers and transforms.
 """
 from __future__ import annotations
 
@@ -37,23 +37,18 @@ def backend_for(device):
 
 
 def mnist_dataset(data_root=None, length=60000):
+    """launch_dist.py:64-65 with this package's MNIST reader + transforms (IDX files under ``data_root``)."""
     if data_root:
-        import torchvision
-        import torchvision.transforms as T
-
-        tf = T.Compose([T.ToTensor(), T.Normalize((0.1307,), (0.3081,))])
-        return torchvision.datasets.MNIST(data_root, train=True, download=False, transform=tf)
+        T = pdl.utils.data.transforms
+        return pdl.utils.data.MNIST(root=data_root, train=True, download=True, transform=T.mnist_transform(), synthetic_length=length)
     return pdl.utils.data.SyntheticMNIST(length)
 
 
 def cifar_dataset(data_root=None, length=50000):
+    """example_launch.py:32-48 with this package's CIFAR10 reader + transforms (``cifar-10-batches-py`` under ``data_root``)."""
     if data_root:
-        import torchvision
-        import torchvision.transforms as T
-
-        tf = T.Compose([T.RandomCrop(32, padding=4), T.RandomHorizontalFlip(), T.ToTensor(),
-                        T.Normalize((0.4914, 0.4822, 0.4465), (0.2023, 0.1994, 0.2010))])
-        return torchvision.datasets.CIFAR10(root=data_root, train=True, download=False, transform=tf)
+        T = pdl.utils.data.transforms
+        return pdl.utils.data.CIFAR10(root=data_root, train=True, download=False, transform=T.cifar10_train_transform(), synthetic_length=length)
     return pdl.utils.data.SyntheticCIFAR10(length)
 
 

@@ -65,6 +65,31 @@ class _Bucket:
         self.grads = {}
 
 
+class GradBucket:
+    """What a communication hook receives (torch.distributed.GradBucket's accessors)."""
+
+    def __init__(self, index, flat, is_last, grads, params):
+        self._index, self._flat, self._is_last, self._grads, self._params = index, flat, is_last, grads, params
+
+    def index(self):
+        return self._index
+
+    def buffer(self):
+        return self._flat
+
+    def is_last(self):
+        return self._is_last
+
+    def gradients(self):
+        return list(self._grads)
+
+    def parameters(self):
+        return list(self._params)
+
+    def set_buffer(self, tensor):
+        self._flat.copy_(tensor.reshape(-1))
+
+
 def _align(n, a=_ALIGN_ELEMS):
     return (n + a - 1) // a * a
 
@@ -113,6 +138,7 @@ class DistributedDataParallel(nn.Module):
         self._arrival = []
         self._rebuilt = False
         self._callback_queued = False
+        self._comm_hook, self._hook_results = None, []
         self._stats = {"buckets_launched": 0, "fused_buckets": 0, "rebuilds": 0}
 
         self._verify_params_across_processes()
@@ -276,6 +302,9 @@ class DistributedDataParallel(nn.Module):
                 dsts.append(view)
         if dsts:
             torch._foreach_copy_(dsts, srcs)
+        if self._comm_hook is not None:
+            self._run_comm_hook(bk)
+            return
         if not self._fused_checked:
             self._resolve_fused_optimizers()
         self._backend.reduce_bucket(bk, self._world, self.algorithm)
@@ -296,8 +325,55 @@ class DistributedDataParallel(nn.Module):
             for bk in self._buckets[self._next_bucket:]:
                 bk.pending = 0
             self._launch_ready_buckets()
-        self._backend.finish(self._buckets)
+        if self._comm_hook is not None:
+            self._finish_comm_hook()
+        else:
+            self._backend.finish(self._buckets)
         self._iteration += 1
+
+    # ------------------------------------------------------------------ communication hook
+    def register_comm_hook(self, state, hook):
+        """``hook(state, bucket) -> tensor | future`` takes over the reduction of every gradient bucket (same contract
+        as torch's DDP: the bucket holds the UN-divided local gradients, the hook returns -- directly, or through an
+        object with ``wait()`` / ``value()`` -- the tensor that becomes the gradients, e.g. the allreduced sum divided
+        by the world size).  With a hook installed the built-in bucket kernel and its fused SGD update are bypassed;
+        the optimizer's ``step()`` then performs the whole update.  May be registered once, before the first backward."""
+        if not callable(hook):
+            raise TypeError("communication hook must be callable")
+        if self._comm_hook is not None:
+            raise RuntimeError("register_comm_hook can only be called once")
+        if self._iteration > 0:
+            raise RuntimeError("register_comm_hook must be called before the first backward pass")
+        self._comm_hook = (state, hook)
+        self._hook_results = []
+
+    def _run_comm_hook(self, bk):
+        state, hook = self._comm_hook
+        flat = self._backend.g_in[bk.offset:bk.offset + bk.numel]
+        out = hook(state, GradBucket(bk.index, flat, bk.index == len(self._buckets) - 1,
+                                     [self._in_views[i] for i in bk.param_ids], [self._params[i] for i in bk.param_ids]))
+        self._hook_results.append((bk, out))
+        bk.launched = True
+        bk.grads.clear()
+        self._stats["buckets_launched"] += 1
+
+    def _finish_comm_hook(self):
+        for bk, out in self._hook_results:
+            if not torch.is_tensor(out):
+                res = out.wait() if hasattr(out, "wait") else out
+                if res is None or not torch.is_tensor(res):
+                    res = out.value() if hasattr(out, "value") else res
+                if isinstance(res, (list, tuple)):
+                    res = res[0]
+                out = res
+            if not torch.is_tensor(out) or out.numel() != bk.numel:
+                raise RuntimeError("communication hook must return a tensor with the bucket's %d elements" % bk.numel)
+            dst = self._backend.g_avg[bk.offset:bk.offset + bk.numel]
+            if out.data_ptr() != dst.data_ptr():
+                dst.copy_(out.reshape(-1))
+            for i in bk.param_ids:
+                self._params[i].grad = self._avg_views[i]
+        self._hook_results = []
 
     # ------------------------------------------------------------------ fused optimizer
     def _resolve_fused_optimizers(self):

@@ -176,3 +176,50 @@ def checkpoint_worker(rank, world, port, outdir):
     after = torch.cat([p.detach().reshape(-1) for p in model.parameters()])
     torch.save({"wrote": wrote, "roundtrip": torch.equal(before, after), "epoch": info.get("epoch")}, os.path.join(outdir, "r%d.pt" % rank))
     dist.destroy_process_group()
+
+
+class _Later:
+    """Minimal future: what a hook may return instead of a tensor."""
+
+    def __init__(self, fn):
+        self.fn = fn
+
+    def wait(self):
+        return self.fn()
+
+
+def comm_hook_worker(rank, world, port, outdir):
+    """DDP with a user communication hook (allreduce the un-divided bucket, scale by 1/W, hand back a future) must
+    produce the same gradients as the built-in reducer."""
+    _init(rank, world, port)
+    torch.manual_seed(0)
+    a = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 3))
+    b = torch.nn.Sequential(torch.nn.Linear(6, 5), torch.nn.Tanh(), torch.nn.Linear(5, 3))
+    b.load_state_dict(a.state_dict())
+    plain, hooked = pdl.DistributedDataParallel(a), pdl.DistributedDataParallel(b, bucket_cap_mb=1e-5, first_bucket_mb=1e-5)
+    seen = []
+
+    def hook(state, bucket):
+        seen.append((bucket.index(), bucket.is_last(), bucket.buffer().numel(), len(bucket.gradients())))
+        buf = bucket.buffer()
+
+        def finish():
+            dist.all_reduce(buf)
+            return buf.div_(state["world"])
+        return _Later(finish)
+
+    hooked.register_comm_hook({"world": world}, hook)
+    try:
+        hooked.register_comm_hook(None, hook)
+        twice = False
+    except RuntimeError:
+        twice = True
+    grads = []
+    for it in range(2):
+        x = torch.randn(4, 6, generator=torch.Generator().manual_seed(10 * it + rank))
+        for m in (plain, hooked):
+            m.zero_grad()
+            m(x).pow(2).sum().backward()
+        grads.append((torch.cat([p.grad.reshape(-1) for p in a.parameters()]), torch.cat([p.grad.reshape(-1) for p in b.parameters()])))
+    torch.save({"grads": grads, "seen": seen, "twice_rejected": twice}, os.path.join(outdir, "r%d.pt" % rank))
+    dist.destroy_process_group()

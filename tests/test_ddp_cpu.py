@@ -64,3 +64,16 @@ def test_ddp_argument_validation(port):
         assert ddp.get_step_stats()["iterations"] == 1
     finally:
         dist.destroy_process_group()
+
+
+def test_register_comm_hook(tmp_path):
+    pdl.multiprocessing.spawn(_workers.comm_hook_worker, args=(2, free_port(), str(tmp_path)), nprocs=2)
+    r0 = torch.load(tmp_path / "r0.pt", weights_only=False)
+    r1 = torch.load(tmp_path / "r1.pt", weights_only=False)
+    assert r0["twice_rejected"]
+    for (plain0, hooked0), (plain1, hooked1) in zip(r0["grads"], r1["grads"]):
+        torch.testing.assert_close(hooked0, plain0)
+        assert torch.equal(hooked0, hooked1)  # replicas agree
+    # tiny caps => several buckets per iteration; the hook saw each of them, the last one flagged
+    per_iter = len(r0["seen"]) // 2
+    assert per_iter >= 2 and r0["seen"][per_iter - 1][1] and not r0["seen"][0][1]
