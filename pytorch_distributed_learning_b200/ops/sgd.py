@@ -8,12 +8,14 @@ import torch
 from .. import _lib
 
 _tables = {}
+_captured = {}  # tables built while a CUDA graph was being captured: the graph replays their H2D copies, so they never expire
 
 
 def _table_for(params, grads, bufs):
     key = tuple((p.data_ptr(), g.data_ptr(), 0 if b is None else b.data_ptr(), p.numel()) for p, g, b in zip(params, grads, bufs))
-    t = _tables.get(key)
+    t = _tables.get(key) or _captured.get(key)
     if t is None:
+        capturing = torch.cuda.is_current_stream_capturing()
         if len(_tables) > 64:
             _tables.clear()
         chunk = _lib.cuda().pdl_sgd_chunk_elems()
@@ -23,9 +25,13 @@ def _table_for(params, grads, bufs):
             total += (n + chunk - 1) // chunk
             prefix.append(total)
         dev = params[0].device
-        t = (torch.tensor(rows, dtype=torch.int64, device=dev), torch.tensor(prefix, dtype=torch.int32, device=dev), total)
-        _tables[key] = t
-    return t
+        # pinned staging + async copy: legal under stream capture (the copy becomes a graph node that re-reads the
+        # pinned rows on every replay, which is why they are kept alive next to the device copies)
+        host_rows = torch.tensor(rows, dtype=torch.int64).pin_memory()
+        host_prefix = torch.tensor(prefix, dtype=torch.int32).pin_memory()
+        t = (host_rows.to(dev, non_blocking=True), host_prefix.to(dev, non_blocking=True), total, host_rows, host_prefix)
+        (_captured if capturing else _tables)[key] = t
+    return t[:3]
 
 
 def multi_tensor_sgd(params, grads, bufs, first_flags, lr, momentum, dampening, weight_decay, nesterov):

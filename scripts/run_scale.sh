@@ -8,3 +8,7 @@ timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --mas
 for impl in reference ours; do
   timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29577 bench.py --gpus $N --steps 300 --warmup 30 --impl $impl 2>&1 | tail -1 > gpurun_out/bench_${impl}_w$N.json; cut -c1-330 gpurun_out/bench_${impl}_w$N.json
 done
+for impl in reference ours; do
+  timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29599 bench.py --gpus $N --model resnet50 --steps 20 --warmup 5 --impl $impl 2>&1 | tail -1 > gpurun_out/bench_r50_${impl}_w$N.json; cut -c1-330 gpurun_out/bench_r50_${impl}_w$N.json
+done
+grep -o '"exposed_comm_ms_per_step": [0-9.e-]*\|"compute_only_ms_per_step": [0-9.e-]*' gpurun_out/bench_*_w$N.json

@@ -158,6 +158,26 @@ def test_generic_graph_engine_resnet18_matches_eager():
         dist.destroy_process_group()
 
 
+def test_generic_graph_engine_without_ddp():
+    """No DDP wrapper: gradients are fresh allocations and the stand-alone multi-tensor SGD builds its pointer table
+    while the graph is being captured (pinned staging); replays must keep following the eager trajectory."""
+    torch.manual_seed(0)
+    kw = dict(lr=0.05, momentum=0.9, weight_decay=1e-4, nesterov=True)
+    a = pdl.models.resnet18(num_classes=10).cuda()
+    b = copy.deepcopy(a)
+    oa, ob = pdl.optim.SGD(a.parameters(), **kw), pdl.optim.SGD(b.parameters(), **kw)
+    crit = pdl.nn.CrossEntropyLoss()
+    sa, sb = pdl.TrainStep(a, crit, oa), pdl.TrainStep(b, crit, ob, use_graph=False)
+    assert sa.graphed and not sb.graphed
+    g = torch.Generator().manual_seed(5)
+    for _ in range(4):
+        x, y = torch.randn(8, 3, 32, 32, generator=g).cuda(), torch.randint(0, 10, (8,), generator=g).cuda()
+        la, lb = sa(x, y).item(), sb(x, y).item()
+        assert abs(la - lb) <= 2e-3 * max(1.0, abs(lb)), (la, lb)
+    for (n, pa), (_, pb) in zip(a.named_parameters(), b.named_parameters()):
+        torch.testing.assert_close(pa, pb, rtol=2e-3, atol=2e-4, msg=lambda m, n=n: "%s: %s" % (n, m))
+
+
 def test_resnet18_modules_train_step_matches_torchvision():
     import torchvision
 
