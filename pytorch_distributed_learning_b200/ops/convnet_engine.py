@@ -12,6 +12,7 @@ flat buffer for a single un-wrapped GPU.
 from __future__ import annotations
 
 import ctypes
+import os
 
 import torch
 
@@ -127,6 +128,7 @@ class ConvNetEngine:
             p.grad = v
         self.graphs = {}
         self.kernel_count = 0
+        self._branch = torch.cuda.Stream(device=self.device)  # off-critical-path kernels (see _record_tc)
 
     # ------------------------------------------------------------------ buffers + capture
     def _build(self, N):
@@ -187,15 +189,26 @@ class ConvNetEngine:
         return k
 
     def _record_tc(self, b, N, stream_handle):
-        """Tensor-core path: 15 launches (tcgen05 conv2/conv3 fwd+dgrad+wgrad, fused CUDA-core kernels for the rest)."""
+        """Tensor-core path: 15 launches (tcgen05 conv2/conv3 fwd+dgrad+wgrad, fused CUDA-core kernels for the rest).
+
+        At batch 100 every kernel is a fraction of one wave and latency-bound, so the step time is the length of the
+        dependency chain.  The weight gradients (+ their split reductions) and the weight packing are not on that
+        chain: they are recorded on a branch stream (fork/join through events, which capture turns into graph edges)
+        and overlap the dgrad / pool-backward kernels of the main chain."""
         L, ok, st = self.L, NF._ok, ctypes.c_void_p(stream_handle)
         w1, b1, w2, b2, w3, b3, wf, bf = self.params
         gw1, gb1, gw2, gb2, gw3, gb3, gwf, gbf = self.g_views
         err = _p(b["err"])
         k = 0
-        ok(L.pdl_convnet_pack(_p(w2), _p(w3), _p(wf), _p(b["p2f"]), _p(b["p2b"]), _p(b["p3f"]), _p(b["p3b"]), _p(b["wfp"]), st), "weight pack"); k += 1
+        main = torch.cuda.ExternalStream(stream_handle, device=self.device)
+        fork = os.environ.get("PDL_CONVNET_FORK", "1") != "0"
+        branch = self._branch if fork else main
+        sb = ctypes.c_void_p(branch.cuda_stream)
+        branch.wait_stream(main)
+        ok(L.pdl_convnet_pack(_p(w2), _p(w3), _p(wf), _p(b["p2f"]), _p(b["p2b"]), _p(b["p3f"]), _p(b["p3b"]), _p(b["wfp"]), sb), "weight pack"); k += 1
         # forward: conv+bias+ReLU+pool fused per layer
         ok(L.pdl_conv1_fused_fwd(_p(b["x"]), _p(w1), _p(b1), _p(b["a1"]), _p(b["i1"]), N, st), "conv1"); k += 1
+        main.wait_stream(branch)
         ok(L.pdl_tc_conv2d_fwd(_p(b["a1"]), _p(b["p2f"]), _p(b2), _p(b["a2"]), _p(b["i2"]), N, 13, 13, 32, 64, 3, 3, 0, 1, 1, err, st), "conv2"); k += 1
         ok(L.pdl_tc_conv2d_fwd(_p(b["a2"]), _p(b["p3f"]), _p(b3), _p(b["a3"]), _p(b["i3"]), N, 10, 10, 64, 128, 3, 3, 0, 1, 2, err, st), "conv3"); k += 1
         ok(L.pdl_fc_ce_fused(_p(b["a3"]), _p(b["wfp"]), _p(bf), _p(b["y"]), _p(b["logits"]), _p(b["row_loss"]), _p(b["loss"]), _p(b["dlogits"]), N, st),
@@ -203,14 +216,17 @@ class ConvNetEngine:
         # backward
         ok(L.pdl_fc_bwd_pool3_fused(_p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
                                     _p(b["db3part"]), N, st), "fc1 backward + pool3 backward"); k += 1
+        branch.wait_stream(main)  # dz3 / db3part are ready
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a2"]), _p(b["dz3"]), _p(gw3), _p(gb3), _p(b["db3part"]), N, _p(b["wg_scratch"]), N, 10, 10, 64, 128, 3, 3, 0,
-                                 err, st), "conv3 wgrad"); k += 2
+                                 err, sb), "conv3 wgrad"); k += 2
         ok(L.pdl_tc_conv2d_dgrad(_p(b["dz3"]), _p(b["p3b"]), _p(b["da2"]), N, 10, 10, 64, 128, 3, 3, 0, err, st), "conv3 dgrad"); k += 1
         ok(L.pdl_pool2_bwd_dbias(_p(b["da2"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 11, 11, 64, 1, st), "pool2 backward"); k += 1
+        branch.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
-                                 3, 3, 0, err, st), "conv2 wgrad"); k += 2
+                                 3, 3, 0, err, sb), "conv2 wgrad"); k += 2
         ok(L.pdl_tc_conv2d_dgrad(_p(b["dz2"]), _p(b["p2b"]), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 dgrad"); k += 1
         ok(L.pdl_conv1_wgrad_fused(_p(b["x"]), _p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(gw1), _p(gb1), _p(b["c1part"]), N, st), "conv1 wgrad"); k += 1
+        main.wait_stream(branch)  # join: every gradient is in the bucket before the allreduce
         return k
 
     def _record_simt(self, b, N, stream_handle):
