@@ -26,6 +26,34 @@ extern long long g_pdl_launch_calls;
 
 static inline int pdl_ceil_div(long long a, long long b) { return static_cast<int>((a + b - 1) / b); }
 
+// ---- programmatic dependent launch ----
+// The training step is a chain of short kernels, each a fraction of one wave: what separates them is launch +
+// drain latency.  A kernel launched through launch_dependent() may start while its predecessor in the stream is
+// still draining and run its prologue (shared-memory carve-up, barrier init, TMEM allocation, descriptor prefetch);
+// it must call grid_dependency_wait() before it touches anything the predecessor wrote (the wait returns once the
+// predecessor grid has completed and its writes are visible; it is a no-op for ordinary launches).  Kernels call
+// launch_dependents() first thing so that the successor can be scheduled as soon as all of their CTAs are resident.
+// PDL_NO_PDL=1 turns the launch attribute off (plain stream order).
+__device__ __forceinline__ void grid_dependency_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
+bool pdl_dependent_launch_enabled();
+
+template <typename... KArgs, typename... Args>
+cudaError_t launch_dependent(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t stream, Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = pdl_dependent_launch_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...);
+}
+
 // Round-to-nearest TF32 (10-bit mantissa).  The tensor cores TRUNCATE fp32 operands to TF32; producers of
 // MMA operands round on store instead, which halves the error and removes the toward-zero bias.
 __device__ __forceinline__ float round_tf32(float x) {

@@ -22,6 +22,8 @@ __global__ void __launch_bounds__(kThreads) pool2_bwd_dbias_kernel(const float* 
   constexpr int G = kThreads / C;
   const int c = threadIdx.x % C, grp = threadIdx.x / C;
   float colsum = 0.f;
+  launch_dependents();     // successor may set up while this grid drains
+  grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
   const unsigned p_lo = blockIdx.x * pix_per_cta;  // 32-bit index math: 64-bit div/mod made this kernel ALU-bound
   const unsigned p_hi = min(total_pix, p_lo + pix_per_cta);
 #pragma unroll 4
@@ -78,6 +80,8 @@ __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const flo
   float acc[25], accb = 0.f;
 #pragma unroll
   for (int t = 0; t < 25; ++t) acc[t] = 0.f;
+  launch_dependents();     // successor may set up while this grid drains
+  grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
   const int n_lo = blockIdx.x * imgs_per_cta, n_hi = min(N, n_lo + imgs_per_cta);
   for (int n = n_lo; n < n_hi; ++n) {
     __syncthreads();
@@ -121,11 +125,24 @@ __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const flo
   __syncthreads();
   if (is_last) {
     __threadfence();
-    const unsigned nb = gridDim.x;
-    for (int i = threadIdx.x; i < 832; i += kC1Threads) {
-      float s = 0.f;
+    // 208 float4 columns x 2 halves of the row list = 416 threads, 16 independent loads in flight each; the two halves
+    // are then added in a fixed order (deterministic)
+    const unsigned nb = gridDim.x, half_rows = (nb + 1) / 2;
+    float4* red4 = reinterpret_cast<float4*>(red);
+    if (threadIdx.x < 416) {
+      const unsigned col4 = threadIdx.x % 208, half = threadIdx.x / 208;
+      const unsigned b_lo = half * half_rows, b_hi = min(nb, b_lo + half_rows);
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 16
-      for (unsigned b = 0; b < nb; ++b) s += __ldcg(partial + static_cast<size_t>(b) * 832 + i);
+      for (unsigned b = b_lo; b < b_hi; ++b) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(partial + static_cast<size_t>(b) * 832) + col4);
+        s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+      }
+      red4[half * 208 + col4] = s;
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < 832; i += kC1Threads) {
+      const float s = red[i] + red[832 + i];
       if (i < 800) gw1[i] = s; else gb1[i - 800] = s;
     }
     if (threadIdx.x == 0) g_c1w_done = 0;
@@ -162,7 +179,7 @@ PDL_API int pdl_pool2_bwd_dbias(const float* da, const uint8_t* idx, const float
   if (total * C >= (1ll << 31) || (stride != 1 && stride != 2)) { pdl_set_error("pool2_bwd_dbias: tensor too large or bad stride"); return -1; }
   const unsigned T = static_cast<unsigned>(total);
 #define PDL_POOL_CASE(CC, SS) \
-  if (C == CC && stride == SS) pool2_bwd_dbias_kernel<CC, SS><<<blocks, kThreads, 0, stream>>>(da, idx, pooled, dz, dbpart, T, H, W, ppc)
+  if (C == CC && stride == SS) PDL_CUDA_CHECK(launch_dependent(pool2_bwd_dbias_kernel<CC, SS>, dim3(blocks), dim3(kThreads), 0, stream, da, idx, pooled, dz, dbpart, T, H, W, ppc))
   PDL_POOL_CASE(32, 1); else PDL_POOL_CASE(64, 1); else PDL_POOL_CASE(128, 1); else PDL_POOL_CASE(32, 2); else PDL_POOL_CASE(64, 2);
   else PDL_POOL_CASE(128, 2); else { pdl_set_error("pool2_bwd_dbias: unsupported channel count %d", C); return -1; }
 #undef PDL_POOL_CASE
@@ -179,7 +196,8 @@ PDL_API int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_
     PDL_CUDA_CHECK(cudaFuncSetAttribute(conv1_wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  conv1_wgrad_fused_kernel<<<c1_blocks(N), kC1Threads, smem, stream>>>(x, da1, idx1, a1, gw1, gb1, partial, N, c1_imgs_per_cta(N));
+  PDL_CUDA_CHECK(launch_dependent(conv1_wgrad_fused_kernel, dim3(c1_blocks(N)), dim3(kC1Threads), smem, stream, x, da1, idx1, a1, gw1, gb1, partial, N,
+                                  c1_imgs_per_cta(N)));
   PDL_LAUNCH_CHECK();
   return 0;
 }

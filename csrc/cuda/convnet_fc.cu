@@ -23,6 +23,8 @@ __global__ void __launch_bounds__(kThreads) fc_ce_kernel(const float* __restrict
                                                          const long long* __restrict__ labels, float* __restrict__ logits,
                                                          float* __restrict__ row_loss, float* __restrict__ loss, float* __restrict__ dlogits, int N) {
   __shared__ float part_logit[kRowsPerCta][4][kClasses];
+  launch_dependents();     // successor may set up while this grid drains
+  grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
   const int row_in_cta = warp / 4, quarter = warp % 4;
   const int n = blockIdx.x * kRowsPerCta + row_in_cta;
@@ -105,9 +107,14 @@ __global__ void __launch_bounds__(kThreads) fc_ce_kernel(const float* __restrict
 __global__ void __launch_bounds__(kThreads) fc_bwd_pool3_kernel(const float* __restrict__ a3, const uint8_t* __restrict__ idx3,
                                                                 const float* __restrict__ dlogits, const float* __restrict__ wfp,
                                                                 float* __restrict__ gwf, float* __restrict__ gbf, float* __restrict__ wpart,
-                                                                float* __restrict__ dz3, float* __restrict__ db3part, int N, int splits) {
+                                                                float* __restrict__ dz3, float* __restrict__ db3part, int N, int splits,
+                                                                int mode) {
   __shared__ float dl[64 * kClasses];
-  const int roleA_blocks = 8 * splits;
+  launch_dependents();     // successor may set up while this grid drains
+  grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
+  // mode 0: both roles in one grid; 1: role A only (fc weight gradient -- off the critical path, the engine puts it
+  // on its branch stream); 2: role B only (dz3 / db3part, which the conv3 dgrad is waiting for)
+  const int roleA_blocks = mode == 2 ? 0 : 8 * splits;
   if (blockIdx.x < roleA_blocks) {
     const int colg = blockIdx.x % 8, split = blockIdx.x / 8;
     const int i = colg * kThreads + threadIdx.x;  // NHWC feature index
@@ -144,6 +151,7 @@ __global__ void __launch_bounds__(kThreads) fc_bwd_pool3_kernel(const float* __r
 #pragma unroll
       for (int j = 0; j < kClasses; ++j) {
         float s = 0.f;
+#pragma unroll 8
         for (int sp = 0; sp < splits; ++sp) s += __ldcg(wpart + (static_cast<long long>(sp) * kClasses + j) * kFeat + i);
         gwf[j * kFeat + c * 16 + hw] = s;
       }
@@ -158,7 +166,7 @@ __global__ void __launch_bounds__(kThreads) fc_bwd_pool3_kernel(const float* __r
   }
   // ---- role B ----
   const int n = blockIdx.x - roleA_blocks;
-  if (n >= N) return;
+  if (n >= N || mode == 1) return;
   if (threadIdx.x < kClasses) dl[threadIdx.x] = dlogits[n * kClasses + threadIdx.x];
   __syncthreads();
   const int c = threadIdx.x % 128, half = threadIdx.x / 128;  // 2 pooled pixels in flight per pass
@@ -190,7 +198,8 @@ __global__ void __launch_bounds__(kThreads) fc_bwd_pool3_kernel(const float* __r
 
 PDL_API int pdl_fc_ce_fused(const float* a3, const float* wfp, const float* bf, const long long* labels, float* logits, float* row_loss, float* loss,
                             float* dlogits, int N, cudaStream_t stream) {
-  fc_ce_kernel<<<pdl_ceil_div(N, kRowsPerCta), kThreads, 0, stream>>>(a3, wfp, bf, labels, logits, row_loss, loss, dlogits, N);
+  PDL_CUDA_CHECK(launch_dependent(fc_ce_kernel, dim3(pdl_ceil_div(N, kRowsPerCta)), dim3(kThreads), 0, stream, a3, wfp, bf, labels, logits, row_loss,
+                                  loss, dlogits, N));
   PDL_LAUNCH_CHECK();
   return 0;
 }
@@ -202,7 +211,21 @@ PDL_API long long pdl_fc_bwd_scratch_floats(int N) { long long s = pdl_fc_bwd_sp
 PDL_API int pdl_fc_bwd_pool3_fused(const float* a3, const uint8_t* idx3, const float* dlogits, const float* wfp, float* gwf, float* gbf,
                                    float* wpart, float* dz3, float* db3part, int N, cudaStream_t stream) {
   const int splits = pdl_fc_bwd_splits(N);
-  fc_bwd_pool3_kernel<<<8 * splits + N, kThreads, 0, stream>>>(a3, idx3, dlogits, wfp, gwf, gbf, wpart, dz3, db3part, N, splits);
+  PDL_CUDA_CHECK(launch_dependent(fc_bwd_pool3_kernel, dim3(8 * splits + N), dim3(kThreads), 0, stream, a3, idx3, dlogits, wfp, gwf, gbf, wpart, dz3,
+                                  db3part, N, splits, 0));
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// The two halves of pdl_fc_bwd_pool3_fused as separate launches: part 1 = fc1 weight/bias gradient (gwf, gbf),
+// part 2 = dz3 + conv3 bias-gradient partials.  Lets a caller overlap part 1 with the rest of the backward pass.
+PDL_API int pdl_fc_bwd_pool3_part(int part, const float* a3, const uint8_t* idx3, const float* dlogits, const float* wfp, float* gwf, float* gbf,
+                                  float* wpart, float* dz3, float* db3part, int N, cudaStream_t stream) {
+  if (part != 1 && part != 2) { pdl_set_error("fc_bwd_pool3_part: part must be 1 or 2"); return -1; }
+  const int splits = pdl_fc_bwd_splits(N);
+  const int blocks = part == 1 ? 8 * splits : N;
+  PDL_CUDA_CHECK(launch_dependent(fc_bwd_pool3_kernel, dim3(blocks), dim3(kThreads), 0, stream, a3, idx3, dlogits, wfp, gwf, gbf, wpart, dz3, db3part, N,
+                                  splits, part));
   PDL_LAUNCH_CHECK();
   return 0;
 }

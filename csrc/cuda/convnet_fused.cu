@@ -56,6 +56,7 @@ __global__ void __launch_bounds__(kThreads) convnet_pack_kernel(PackArgs a) {
 __global__ void __launch_bounds__(kThreads) conv1_fused_kernel(const float* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                                                                float* __restrict__ a1, uint8_t* __restrict__ idx1, int N) {
   __shared__ float img[30][32];  // 28 + 2 halo, row pitch 32
+  launch_dependents();  // conv2's CTAs may set up (barriers, TMEM) while this grid drains; they wait before reading a1
   const int n = blockIdx.x;
   if (n >= N) return;
   for (int i = threadIdx.x; i < 30 * 32; i += kThreads) {

@@ -35,6 +35,16 @@ long long g_pdl_launch_calls = 0;
 // Number of launcher calls (each enqueues at least one kernel of this library) made so far in this process.
 PDL_API long long pdl_launch_count() { return g_pdl_launch_calls; }
 
+// Programmatic dependent launch (common.cuh) is on unless PDL_NO_PDL=1.
+bool pdl_dependent_launch_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* s = getenv("PDL_NO_PDL");
+    v = (s && s[0] == '1') ? 0 : 1;
+  }
+  return v != 0;
+}
+
 // ---- driver entry points fetched at run time (the .so must load on a box without libcuda) ----
 namespace {
 

@@ -91,6 +91,10 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc(tmem_slot, kTmemCols);
+  // Everything above ran (possibly) while the previous kernel of the stream was still draining; from here on we read
+  // what it produced.  Our own successor may start its prologue as soon as all of our CTAs are resident.
+  launch_dependents();
+  grid_dependency_wait();
   // per-CTA constants of the epilogue, computed once: bias row, pooled pixel -> first staging row of its window
   const int ps = e.pool_stride > 0 ? e.pool_stride : 1;
   const int PH = (g.BH - 2) / ps + 1, PW = (g.BW - 2) / ps + 1;
@@ -367,7 +371,7 @@ int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& o, 
     configured = true;
   }
   int grid = g.num_tiles < 148 ? g.num_tiles : 148;
-  kernel<<<grid, kThreads, Smem<N_GEMM>::TOTAL, stream>>>(a, b, o, g, e);
+  PDL_CUDA_CHECK(launch_dependent(kernel, dim3(grid), dim3(kThreads), Smem<N_GEMM>::TOTAL, stream, a, b, o, g, e));
   PDL_LAUNCH_CHECK();
   return 0;
 }

@@ -83,6 +83,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
     tc::fence_barrier_init();
   }
   if (warp == 2) tc::tmem_alloc(tmem_slot, kCols);
+  launch_dependents();     // successor may set up while this grid drains
+  grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
@@ -171,6 +173,8 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
 // dw[co][ci][tap] = sum_split partial[split][tap][co][ci];  db[co] = sum_blk db_partial[blk][co]
 __global__ void wgrad_finish_kernel(const float* __restrict__ partial, int splits, int taps, int Cout, int Cin, float* __restrict__ dw,
                                     const float* __restrict__ db_partial, int db_blocks, float* __restrict__ db) {
+  launch_dependents();     // successor may set up while this grid drains
+  grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   const int per_split = taps * Cout * Cin;
   if (i < per_split) {
@@ -277,7 +281,7 @@ int launch_wg(const CUtensorMap& a, const CUtensorMap& b, const WgGeom& g, int K
     configured = true;
   }
   dim3 grid(KH, wg_splits(g), (g.Cout / M) * g.cin_tiles);
-  kernel<<<grid, kThreads, smem, stream>>>(a, b, g, partial, error);
+  PDL_CUDA_CHECK(launch_dependent(kernel, grid, dim3(kThreads), smem, stream, a, b, g, partial, error));
   PDL_LAUNCH_CHECK();
   return 0;
 }
@@ -331,7 +335,8 @@ PDL_API int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* 
   else if (mt == 64 && nt == 64) rc = launch_wg<64, 64>(ta, tb, g, KH, scratch, error_flag, stream);
   if (rc) return rc;
   const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
-  wgrad_finish_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(scratch, wg_splits(g), KH * KW, Cout, Cin, dw, db_partial, db_blocks, db);
+  PDL_CUDA_CHECK(launch_dependent(wgrad_finish_kernel, dim3(pdl_ceil_div(total, 256)), dim3(256), 0, stream, scratch, wg_splits(g), KH * KW, Cout, Cin, dw,
+                                  db_partial, db_blocks, db));
   PDL_LAUNCH_CHECK();
   return 0;
 }

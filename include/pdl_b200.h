@@ -130,6 +130,8 @@ long long pdl_fc_bwd_scratch_floats(int N);
 int pdl_fc_bwd_pool3_fused(const float* a3, const uint8_t* idx3, const float* dlogits, const float* wfp, float* gwf, float* gbf, float* wpart,
                            float* dz3, float* db3part, int N, cudaStream_t stream);
 int pdl_bwd_blocks(int N);
+int pdl_fc_bwd_pool3_part(int part, const float* a3, const uint8_t* idx3, const float* dlogits, const float* wfp, float* gwf, float* gbf,
+                          float* wpart, float* dz3, float* db3part, int N, cudaStream_t stream); /* 1: fc1 wgrad only, 2: dz3/db3part only */
 int pdl_pool2_bwd_blocks(int N, int H, int W, int C);
 int pdl_pool2_bwd_dbias(const float* da, const uint8_t* idx, const float* pooled, float* dz, float* dbpart, int N, int H, int W, int C,
                         int stride, cudaStream_t stream);

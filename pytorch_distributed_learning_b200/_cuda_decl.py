@@ -73,6 +73,7 @@ def declare(L):
     sig("pdl_fc_bwd_splits", [I])
     sig("pdl_fc_bwd_scratch_floats", [I], LL)
     sig("pdl_fc_bwd_pool3_fused", [P, P, P, P, P, P, P, P, P, I, P])
+    sig("pdl_fc_bwd_pool3_part", [I, P, P, P, P, P, P, P, P, P, I, P])
     sig("pdl_bwd_blocks", [I])
     sig("pdl_pool2_bwd_blocks", [I, I, I, I])
     sig("pdl_pool2_bwd_dbias", [P, P, P, P, P, I, I, I, I, I, P])

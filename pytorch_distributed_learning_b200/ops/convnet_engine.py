@@ -214,8 +214,15 @@ class ConvNetEngine:
         ok(L.pdl_fc_ce_fused(_p(b["a3"]), _p(b["wfp"]), _p(bf), _p(b["y"]), _p(b["logits"]), _p(b["row_loss"]), _p(b["loss"]), _p(b["dlogits"]), N, st),
            "fc1 + loss"); k += 1
         # backward
-        ok(L.pdl_fc_bwd_pool3_fused(_p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
-                                    _p(b["db3part"]), N, st), "fc1 backward + pool3 backward"); k += 1
+        if fork:  # fc1's weight gradient is only needed by the final allreduce: branch; dz3 feeds the dgrad chain: main
+            branch.wait_stream(main)
+            ok(L.pdl_fc_bwd_pool3_part(1, _p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
+                                       _p(b["db3part"]), N, sb), "fc1 weight gradient"); k += 1
+            ok(L.pdl_fc_bwd_pool3_part(2, _p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
+                                       _p(b["db3part"]), N, st), "fc1 dgrad + pool3 backward"); k += 1
+        else:
+            ok(L.pdl_fc_bwd_pool3_fused(_p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
+                                        _p(b["db3part"]), N, st), "fc1 backward + pool3 backward"); k += 1
         branch.wait_stream(main)  # dz3 / db3part are ready
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a2"]), _p(b["dz3"]), _p(gw3), _p(gb3), _p(b["db3part"]), N, _p(b["wg_scratch"]), N, 10, 10, 64, 128, 3, 3, 0,
                                  err, sb), "conv3 wgrad"); k += 2
