@@ -19,31 +19,72 @@ __device__ unsigned int g_fcw_done[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 // once: the kernel is L2-latency-bound at batch 100).  Then per-row loss and dlogits = (softmax - onehot) / N;
 // the last CTA reduces the per-row losses in index order into the mean loss.
 constexpr int kRowsPerCta = 2;
+// One sample of the fc1 backward fused with the backward of pool3 (2x2/2 over 8x8x128) and the ReLU before it:
+// da3 = dlogits * Wf on the fly, routed through argmax + ReLU mask into dz3[n][8][8][128]; the CTA's column sums are
+// the conv3 bias-gradient partials db3part[n][128].  All kThreads threads of the CTA take part; dl = the sample's
+// dlogits in shared memory, cs = kThreads floats of shared scratch.
+__device__ __forceinline__ void fc_dgrad_pool3_row(int n, const float* dl, const float* __restrict__ a3, const uint8_t* __restrict__ idx3,
+                                                   const float* __restrict__ wfp, float* __restrict__ dz3, float* __restrict__ db3part, float* cs) {
+  const int c = threadIdx.x % 128, half = threadIdx.x / 128;  // 2 pooled pixels in flight per pass
+  float colsum = 0.f;
+#pragma unroll
+  for (int pp = half; pp < 16; pp += 2) {
+    const int i = pp * 128 + c;
+    float g = 0.f;
+#pragma unroll
+    for (int j = 0; j < kClasses; ++j) g = fmaf(dl[j], wfp[j * kFeat + i], g);
+    const long long o = static_cast<long long>(n) * kFeat + i;
+    if (!(a3[o] > 0.f)) g = 0.f;  // ReLU mask: the pooled value is a ReLU output
+    const int arg = idx3[o], ph = pp / 4, pw = pp % 4;
+    colsum += g;
+    g = round_tf32(g);  // dz3 is an operand of the tcgen05 dgrad / wgrad
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int h = 2 * ph + q / 2, w = 2 * pw + q % 2;
+      dz3[((static_cast<long long>(n) * 8 + h) * 8 + w) * 128 + c] = (q == arg) ? g : 0.f;
+    }
+  }
+  cs[threadIdx.x] = colsum;
+  __syncthreads();
+  if (threadIdx.x < 128) db3part[n * 128 + threadIdx.x] = cs[threadIdx.x] + cs[threadIdx.x + 128];
+  __syncthreads();
+}
+
+// fc1 forward + cross-entropy (+ optionally, when dz3 != nullptr, the fc1 dgrad / pool3 backward of the same rows:
+// a row's dlogits only depend on that row, so the CTA that produced them can go straight on to dz3).
+// kRows samples per CTA (2: forward only, four warps x 512 features per sample; 1: fused form, eight warps x 256
+// features, so that the backward part has one CTA per sample like the stand-alone kernel).
+template <int kRows>
 __global__ void __launch_bounds__(kThreads) fc_ce_kernel(const float* __restrict__ a3, const float* __restrict__ wfp, const float* __restrict__ bf,
                                                          const long long* __restrict__ labels, float* __restrict__ logits,
-                                                         float* __restrict__ row_loss, float* __restrict__ loss, float* __restrict__ dlogits, int N) {
-  __shared__ float part_logit[kRowsPerCta][4][kClasses];
+                                                         float* __restrict__ row_loss, float* __restrict__ loss, float* __restrict__ dlogits, int N,
+                                                         const uint8_t* __restrict__ idx3, float* __restrict__ dz3, float* __restrict__ db3part) {
+  constexpr int kWpr = (kThreads / 32) / kRows;  // warps per sample
+  constexpr int kIters = 16 / kWpr;              // 128-feature float4 sweeps per warp
+  __shared__ float part_logit[kRows][kWpr][kClasses];
+  __shared__ float sdl[kRows][kClasses + 2];
+  __shared__ float cs[kThreads];
   launch_dependents();     // successor may set up while this grid drains
   grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
   const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
-  const int row_in_cta = warp / 4, quarter = warp % 4;
-  const int n = blockIdx.x * kRowsPerCta + row_in_cta;
+  const int row_in_cta = warp / kWpr, quarter = warp % kWpr;
+  const int n = blockIdx.x * kRows + row_in_cta;
   float acc[kClasses];
 #pragma unroll
   for (int j = 0; j < kClasses; ++j) acc[j] = 0.f;
   if (n < N) {
-    const float4* xr = reinterpret_cast<const float4*>(a3 + static_cast<long long>(n) * kFeat) + quarter * 128;
-    float4 xv[4];
+    const float4* xr = reinterpret_cast<const float4*>(a3 + static_cast<long long>(n) * kFeat) + quarter * (32 * kIters);
+    float4 xv[kIters];
 #pragma unroll
-    for (int it = 0; it < 4; ++it) xv[it] = xr[it * 32 + lane];
+    for (int it = 0; it < kIters; ++it) xv[it] = xr[it * 32 + lane];
 #pragma unroll
     for (int j = 0; j < kClasses; ++j) {
-      const float4* wr = reinterpret_cast<const float4*>(wfp + j * kFeat) + quarter * 128;
-      float4 wv[4];
+      const float4* wr = reinterpret_cast<const float4*>(wfp + j * kFeat) + quarter * (32 * kIters);
+      float4 wv[kIters];
 #pragma unroll
-      for (int it = 0; it < 4; ++it) wv[it] = wr[it * 32 + lane];
+      for (int it = 0; it < kIters; ++it) wv[it] = wr[it * 32 + lane];
 #pragma unroll
-      for (int it = 0; it < 4; ++it)
+      for (int it = 0; it < kIters; ++it)
         acc[j] = fmaf(xv[it].x, wv[it].x, fmaf(xv[it].y, wv[it].y, fmaf(xv[it].z, wv[it].z, fmaf(xv[it].w, wv[it].w, acc[j]))));
     }
   }
@@ -59,9 +100,12 @@ __global__ void __launch_bounds__(kThreads) fc_ce_kernel(const float* __restrict
   __syncthreads();
   if (quarter == 0 && n < N) {  // one warp finishes the row; lane j < 10 owns class j
     float mine = -FLT_MAX;
-    if (lane < kClasses)
-      mine = ((part_logit[row_in_cta][0][lane] + part_logit[row_in_cta][1][lane]) + part_logit[row_in_cta][2][lane]) +
-             part_logit[row_in_cta][3][lane] + bf[lane];
+    if (lane < kClasses) {
+      float s = part_logit[row_in_cta][0][lane];
+#pragma unroll
+      for (int q = 1; q < kWpr; ++q) s += part_logit[row_in_cta][q][lane];  // fixed order
+      mine = s + bf[lane];
+    }
     float mx = mine;
 #pragma unroll
     for (int o = 16; o; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
@@ -72,8 +116,18 @@ __global__ void __launch_bounds__(kThreads) fc_ce_kernel(const float* __restrict
     const int tgt = static_cast<int>(labels[n]);
     if (lane < kClasses) {
       logits[n * kClasses + lane] = mine;
-      dlogits[n * kClasses + lane] = (expf(mine - lse) - (lane == tgt ? 1.f : 0.f)) / N;
+      const float d = (expf(mine - lse) - (lane == tgt ? 1.f : 0.f)) / N;
+      dlogits[n * kClasses + lane] = d;
+      sdl[row_in_cta][lane] = d;
       if (lane == tgt) row_loss[n] = lse - mine;
+    }
+  }
+  if (dz3 != nullptr) {
+    __syncthreads();  // sdl is complete
+    for (int r = 0; r < kRows; ++r) {
+      const int nn = blockIdx.x * kRows + r;
+      if (nn >= N) break;  // uniform across the CTA
+      fc_dgrad_pool3_row(nn, sdl[r], a3, idx3, wfp, dz3, db3part, cs);
     }
   }
   __shared__ bool is_last;
@@ -169,37 +223,28 @@ __global__ void __launch_bounds__(kThreads) fc_bwd_pool3_kernel(const float* __r
   if (n >= N || mode == 1) return;
   if (threadIdx.x < kClasses) dl[threadIdx.x] = dlogits[n * kClasses + threadIdx.x];
   __syncthreads();
-  const int c = threadIdx.x % 128, half = threadIdx.x / 128;  // 2 pooled pixels in flight per pass
-  float colsum = 0.f;
-#pragma unroll
-  for (int pp = half; pp < 16; pp += 2) {
-    const int i = pp * 128 + c;
-    float g = 0.f;
-#pragma unroll
-    for (int j = 0; j < kClasses; ++j) g = fmaf(dl[j], wfp[j * kFeat + i], g);
-    const long long o = static_cast<long long>(n) * kFeat + i;
-    if (!(a3[o] > 0.f)) g = 0.f;  // ReLU mask: the pooled value is a ReLU output
-    const int arg = idx3[o], ph = pp / 4, pw = pp % 4;
-    colsum += g;
-    g = round_tf32(g);  // dz3 is an operand of the tcgen05 dgrad / wgrad
-#pragma unroll
-    for (int q = 0; q < 4; ++q) {
-      const int h = 2 * ph + q / 2, w = 2 * pw + q % 2;
-      dz3[((static_cast<long long>(n) * 8 + h) * 8 + w) * 128 + c] = (q == arg) ? g : 0.f;
-    }
-  }
   __shared__ float cs[kThreads];
-  cs[threadIdx.x] = colsum;
-  __syncthreads();
-  if (threadIdx.x < 128) db3part[n * 128 + threadIdx.x] = cs[threadIdx.x] + cs[threadIdx.x + 128];
+  fc_dgrad_pool3_row(n, dl, a3, idx3, wfp, dz3, db3part, cs);
 }
 
 }  // namespace
 
 PDL_API int pdl_fc_ce_fused(const float* a3, const float* wfp, const float* bf, const long long* labels, float* logits, float* row_loss, float* loss,
                             float* dlogits, int N, cudaStream_t stream) {
-  PDL_CUDA_CHECK(launch_dependent(fc_ce_kernel, dim3(pdl_ceil_div(N, kRowsPerCta)), dim3(kThreads), 0, stream, a3, wfp, bf, labels, logits, row_loss,
-                                  loss, dlogits, N));
+  PDL_CUDA_CHECK(launch_dependent(fc_ce_kernel<kRowsPerCta>, dim3(pdl_ceil_div(N, kRowsPerCta)), dim3(kThreads), 0, stream, a3, wfp, bf, labels, logits,
+                                  row_loss, loss, dlogits, N, static_cast<const uint8_t*>(nullptr), static_cast<float*>(nullptr),
+                                  static_cast<float*>(nullptr)));
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// fc1 forward + loss + dlogits AND, in the same kernel, part 2 of pdl_fc_bwd_pool3_fused (dz3, db3part): the
+// critical path of the step loses one kernel boundary.  The fc1 weight gradient (part 1) still needs every row's
+// dlogits and stays a separate launch.
+PDL_API int pdl_fc_ce_bwd_fused(const float* a3, const float* wfp, const float* bf, const long long* labels, float* logits, float* row_loss,
+                                float* loss, float* dlogits, const uint8_t* idx3, float* dz3, float* db3part, int N, cudaStream_t stream) {
+  PDL_CUDA_CHECK(launch_dependent(fc_ce_kernel<1>, dim3(N), dim3(kThreads), 0, stream, a3, wfp, bf, labels, logits, row_loss, loss, dlogits, N, idx3,
+                                  dz3, db3part));
   PDL_LAUNCH_CHECK();
   return 0;
 }

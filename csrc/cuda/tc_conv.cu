@@ -20,7 +20,7 @@ constexpr int kThreads = 384;   // 4 control warps (TMA, MMA, TMEM alloc, spare)
 constexpr int kEpiWarps = 8;
 constexpr int A_BYTES = 128 * 128;  // 128 rows x 32 tf32
 
-enum Epi : int { EPI_STORE = 0, EPI_RELU_POOL = 1 };
+enum Epi : int { EPI_STORE = 0, EPI_RELU_POOL = 1, EPI_POOL_BWD = 2 };
 
 struct TcGeom {
   int num_tiles;
@@ -45,6 +45,8 @@ struct EpiArgs {
   int tma_store;     // EPI_STORE: hand the tile to TMA through the swizzled staging buffer (dense outputs only)
   int* error;
   long long* trace;  // optional: clock64() of CTA 0 at pipeline milestones (profiling aid)
+  const float* pooled;  // EPI_POOL_BWD: the pooled activations (ReLU mask) ...
+  float* dbpart;        // ... and where the per-tile column sums go; `idx` is then the pool's arg-max, `out` is dz
 };
 
 template <int N_GEMM>
@@ -245,6 +247,61 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tc::tc_fence_before();
         __syncwarp();
         if (lane == 0) tc::mbar_arrive(&tempty[acc]);
+      } else if (EPI == EPI_POOL_BWD) {
+        // The tile is the gradient of a 2x2-max-pooled tensor (whole images).  Stage it, then route it back through the
+        // arg-max of each window with the ReLU mask folded in (windows whose pooled value is <= 0 pass nothing):
+        // dz[n][ZH][ZW][ldc], rounded to TF32 for the next tensor-core op, plus the tile's column sums (the bias-gradient
+        // partials of the layer below).  Saves a kernel on the critical path of the backward pass.
+#pragma unroll 1
+        for (int c = 0; c < HALF; c += CH) {
+          float v[CH];
+          tc::tmem_ld<CH>(t_row + c, v);
+#pragma unroll
+          for (int j = 0; j < CH; j += 4)
+            *reinterpret_cast<float4*>(staging + row * SM::STAGING_LD + half * HALF + c + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+        tc::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) tc::mbar_arrive(&tempty[acc]);
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        constexpr int C4 = N_GEMM / 4, LANES = 256 / C4;
+        const int c4 = et % C4, pl = et / C4;
+        const int ZH = (g.BH - 1) * ps + 2, ZW = (g.BW - 1) * ps + 2, zpix = ZH * ZW;
+        const int nimg = min(g.BN, g.Nimg - n0);
+        const int ch0 = nt * N_GEMM + c4 * 4;
+        float4 colsum = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 2
+        for (int px = pl; px < nimg * zpix; px += LANES) {
+          const int img = px / zpix, rem = px % zpix, h = rem / ZW, w = rem % ZW;
+          float4 a4 = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {  // the window whose element (k/2, k%2) is this pixel
+            const int ph_ = h - (k >> 1), pw_ = w - (k & 1);
+            const bool valid = ph_ >= 0 && pw_ >= 0 && (ph_ % ps) == 0 && (pw_ % ps) == 0 && (ph_ / ps) < g.BH && (pw_ / ps) < g.BW;
+            const int prow = valid ? (img * g.BH + ph_ / ps) * g.BW + pw_ / ps : 0;  // branch-free: the loads overlap
+            const float4 gv = *reinterpret_cast<const float4*>(staging + prow * SM::STAGING_LD + c4 * 4);
+            const long long o = (static_cast<long long>(n0) * g.BH * g.BW + prow) * g.ldc + ch0;
+            const float4 pv = __ldg(reinterpret_cast<const float4*>(e.pooled + o));
+            const uchar4 am = __ldg(reinterpret_cast<const uchar4*>(e.idx + o));
+            a4.x += (valid && am.x == k && pv.x > 0.f) ? gv.x : 0.f;
+            a4.y += (valid && am.y == k && pv.y > 0.f) ? gv.y : 0.f;
+            a4.z += (valid && am.z == k && pv.z > 0.f) ? gv.z : 0.f;
+            a4.w += (valid && am.w == k && pv.w > 0.f) ? gv.w : 0.f;
+          }
+          colsum.x += a4.x; colsum.y += a4.y; colsum.z += a4.z; colsum.w += a4.w;
+          *reinterpret_cast<float4*>(e.out + ((static_cast<long long>(n0 + img) * ZH + h) * ZW + w) * g.ldc + ch0) =
+              make_float4(round_tf32(a4.x), round_tf32(a4.y), round_tf32(a4.z), round_tf32(a4.w));
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");  // everyone is done reading the staged gradients
+        *reinterpret_cast<float4*>(staging + pl * SM::STAGING_LD + c4 * 4) = colsum;
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (et < N_GEMM) {
+          float s = 0.f;
+#pragma unroll
+          for (int i = 0; i < LANES; ++i) s += staging[i * SM::STAGING_LD + et];  // fixed order
+          e.dbpart[static_cast<long long>(mt) * g.ldc + nt * N_GEMM + et] = s;
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");  // staging may be overwritten by the next tile
       } else {
         // bias + ReLU into the staging tile, then 2x2 max-pool (stride 1 or 2) with first-max argmax
 #pragma unroll 1
@@ -519,6 +576,39 @@ PDL_API int pdl_tc_conv2d_dgrad_strided(const float* dy, const float* packed_w_b
       if (int rc = dispatch_n<EPI_STORE>(ng, ta, tb, to, g, e, stream)) return rc;
     }
   return 0;
+}
+
+// dgrad of a stride-1 convolution whose INPUT is a ReLU + 2x2 max-pool (stride pool_stride) of the layer below, with
+// that pool/ReLU backward fused into the epilogue: instead of the gradient of the pooled tensor [N][H][W][Cin] this
+// writes dz[N][ZH][ZW][Cin] (ZH = (H-1)*pool_stride + 2, TF32-rounded: it is the next dgrad/wgrad operand) and the
+// per-tile column sums dbpart[pdl_tc_dgrad_poolbwd_tiles()][Cin] (bias-gradient partials).  idx / pooled are the pool's
+// arg-max codes (0..3) and outputs, [N][H][W][Cin].  Needs whole images per tile (H*W <= 128).
+PDL_API int pdl_tc_dgrad_poolbwd_tiles(int N, int H, int W) {
+  TcGeom g{};
+  if (!choose_box(H, W, 1, &g)) return 0;
+  return g.BN > 1 ? (N + g.BN - 1) / g.BN : N;
+}
+PDL_API int pdl_tc_conv2d_dgrad_poolbwd(const float* dy, const float* packed_w_bwd, const uint8_t* idx, const float* pooled, float* dz,
+                                        float* dbpart, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad, int pool_stride,
+                                        int* error_flag, cudaStream_t stream) {
+  const int P = H + 2 * pad - KH + 1, Q = W + 2 * pad - KW + 1;
+  const int ng = n_gemm_for(Cin);
+  if (Cout % 32 || !ng || (pool_stride != 1 && pool_stride != 2)) { pdl_set_error("tc_conv dgrad+pool: unsupported channels/stride"); return -3; }
+  TcGeom g{};
+  if (!choose_box(H, W, 1, &g)) { pdl_set_error("tc_conv dgrad+pool: %dx%d images do not fit one tile", H, W); return -4; }
+  g.n_tiles = Cin / ng; g.ldc = Cin;
+  g.num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N) * g.n_tiles;
+  g.in_stride = 1;
+  g.R = KH; g.S = KW; g.kchunks = Cout / 32;
+  g.tap_r0 = g.tap_s0 = 0; g.tap_step = 1; g.S_full = KW;
+  g.a_h0 = pad; g.a_w0 = pad; g.tap_sign = -1;
+  g.out_stride = 1; g.out_oh = g.out_ow = 0; g.Hc = H;
+  g.Nimg = N; g.Hout = H; g.Wout = W;
+  CUtensorMap ta, tb;
+  if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, ng)) return rc;
+  if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
+  EpiArgs e{dz, const_cast<uint8_t*>(idx), nullptr, 0, pool_stride, 0, error_flag, g_trace, pooled, dbpart};
+  return dispatch_n<EPI_POOL_BWD>(ng, ta, tb, ta, g, e, stream);
 }
 
 // dgrad (stride 1): dx[N][H][W][Cin] from dy[N][P][Q][Cout] and packed_bwd[tap][Cin][Cout].

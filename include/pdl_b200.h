@@ -102,6 +102,12 @@ long long pdl_tc_wgrad_scratch_bytes_strided(int N, int H, int W, int Cin, int C
 int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch,
                                 int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int* error_flag,
                                 cudaStream_t stream); /* stride 1 or 2 */
+/* dgrad of a stride-1 conv whose input is ReLU + 2x2 max-pool (stride 1|2) of the layer below, pool/ReLU backward fused
+ * into the epilogue: writes dz[N][(H-1)*ps+2][(W-1)*ps+2][Cin] (TF32-rounded) and dbpart[tiles][Cin] column sums */
+int pdl_tc_dgrad_poolbwd_tiles(int N, int H, int W);
+int pdl_tc_conv2d_dgrad_poolbwd(const float* dy, const float* packed_w_bwd, const uint8_t* idx, const float* pooled, float* dz, float* dbpart,
+                                int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad, int pool_stride, int* error_flag,
+                                cudaStream_t stream);
 void pdl_tc_set_trace(long long* buf); /* profiling aid: clock64() milestones of CTA 0 */
 
 /* ---- small-Cin ("stem") convolutions on the tensor cores: Cin <= 4, KW <= 8, stride 1|2 (reference: the 7x7/2
@@ -130,6 +136,8 @@ long long pdl_fc_bwd_scratch_floats(int N);
 int pdl_fc_bwd_pool3_fused(const float* a3, const uint8_t* idx3, const float* dlogits, const float* wfp, float* gwf, float* gbf, float* wpart,
                            float* dz3, float* db3part, int N, cudaStream_t stream);
 int pdl_bwd_blocks(int N);
+int pdl_fc_ce_bwd_fused(const float* a3, const float* wfp, const float* bf, const long long* labels, float* logits, float* row_loss, float* loss,
+                        float* dlogits, const uint8_t* idx3, float* dz3, float* db3part, int N, cudaStream_t stream); /* fc1+loss+dz3 in one kernel */
 int pdl_fc_bwd_pool3_part(int part, const float* a3, const uint8_t* idx3, const float* dlogits, const float* wfp, float* gwf, float* gbf,
                           float* wpart, float* dz3, float* db3part, int N, cudaStream_t stream); /* 1: fc1 wgrad only, 2: dz3/db3part only */
 int pdl_pool2_bwd_blocks(int N, int H, int W, int C);

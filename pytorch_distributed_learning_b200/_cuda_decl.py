@@ -57,6 +57,8 @@ def declare(L):
     sig("pdl_tc_wgrad_scratch_bytes_strided", [I, I, I, I, I, I, I, I, I], LL)
     sig("pdl_tc_conv2d_wgrad_strided", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv2d_wgrad", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, P, P])
+    sig("pdl_tc_dgrad_poolbwd_tiles", [I, I, I])
+    sig("pdl_tc_conv2d_dgrad_poolbwd", [P, P, P, P, P, P, I, I, I, I, I, I, I, I, I, P, P])
     # small-Cin ("stem") convolutions on the tensor cores
     sig("pdl_tc_stem_supported", [I, I, I, I, I, I, I, I])
     sig("pdl_tc_stem_pad_floats", [I, I, I, I, I, I, I], LL)
@@ -74,6 +76,7 @@ def declare(L):
     sig("pdl_fc_bwd_scratch_floats", [I], LL)
     sig("pdl_fc_bwd_pool3_fused", [P, P, P, P, P, P, P, P, P, I, P])
     sig("pdl_fc_bwd_pool3_part", [I, P, P, P, P, P, P, P, P, P, I, P])
+    sig("pdl_fc_ce_bwd_fused", [P, P, P, P, P, P, P, P, P, P, P, I, P])
     sig("pdl_bwd_blocks", [I])
     sig("pdl_pool2_bwd_blocks", [I, I, I, I])
     sig("pdl_pool2_bwd_dbias", [P, P, P, P, P, I, I, I, I, I, P])

@@ -152,7 +152,10 @@ class ConvNetEngine:
         if self.use_tc:  # tensor-core path: packed weights, bias partials, split-K scratch
             L = self.L
             blocks = L.pdl_bwd_blocks(N)
-            pool2_blocks = L.pdl_pool2_bwd_blocks(N, 11, 11, 64)
+            # measured on B200 at batch 100: pool2-backward in conv3's dgrad epilogue is neutral (132.7 vs 132.6 us/step) and costs
+            # 5 % at batch 4096, so it is opt-in
+            self.fuse_pool2 = os.environ.get("PDL_CONVNET_FUSE_POOL2", "0") == "1" and L.pdl_tc_dgrad_poolbwd_tiles(N, 10, 10) > 0
+            pool2_blocks = L.pdl_tc_dgrad_poolbwd_tiles(N, 10, 10) if self.fuse_pool2 else L.pdl_pool2_bwd_blocks(N, 11, 11, 64)
             wg = max(L.pdl_tc_wgrad_scratch_bytes(N, 13, 13, 32, 64, 3, 3, 0), L.pdl_tc_wgrad_scratch_bytes(N, 10, 10, 64, 128, 3, 3, 0))
             b.update({
                 "p2f": e(9, 64, 32), "p2b": e(9, 32, 64), "p3f": e(9, 128, 64), "p3b": e(9, 64, 128), "wfp": e(10, 2048),
@@ -211,23 +214,39 @@ class ConvNetEngine:
         main.wait_stream(branch)
         ok(L.pdl_tc_conv2d_fwd(_p(b["a1"]), _p(b["p2f"]), _p(b2), _p(b["a2"]), _p(b["i2"]), N, 13, 13, 32, 64, 3, 3, 0, 1, 1, err, st), "conv2"); k += 1
         ok(L.pdl_tc_conv2d_fwd(_p(b["a2"]), _p(b["p3f"]), _p(b3), _p(b["a3"]), _p(b["i3"]), N, 10, 10, 64, 128, 3, 3, 0, 1, 2, err, st), "conv3"); k += 1
-        ok(L.pdl_fc_ce_fused(_p(b["a3"]), _p(b["wfp"]), _p(bf), _p(b["y"]), _p(b["logits"]), _p(b["row_loss"]), _p(b["loss"]), _p(b["dlogits"]), N, st),
-           "fc1 + loss"); k += 1
-        # backward
-        if fork:  # fc1's weight gradient is only needed by the final allreduce: branch; dz3 feeds the dgrad chain: main
+        if fork:
+            # fc1's weight gradient needs every row's dlogits and is only consumed by the final allreduce: branch.
+            # dz3 feeds the dgrad chain on main.  A row's dz3 only needs that row's dlogits, so the fc1+loss kernel can compute
+            # it too (PDL_CONVNET_FUSE_FC=1, one CTA per sample) -- measured SLOWER on B200 (132.7 vs 123.9 us/step at batch
+            # 100: the two latency chains serialise inside each CTA), hence off by default.
+            if os.environ.get("PDL_CONVNET_FUSE_FC", "0") == "1":
+                ok(L.pdl_fc_ce_bwd_fused(_p(b["a3"]), _p(b["wfp"]), _p(bf), _p(b["y"]), _p(b["logits"]), _p(b["row_loss"]), _p(b["loss"]),
+                                         _p(b["dlogits"]), _p(b["i3"]), _p(b["dz3"]), _p(b["db3part"]), N, st), "fc1 + loss + fc1 dgrad + pool3 backward"); k += 1
+                part2 = False
+            else:
+                ok(L.pdl_fc_ce_fused(_p(b["a3"]), _p(b["wfp"]), _p(bf), _p(b["y"]), _p(b["logits"]), _p(b["row_loss"]), _p(b["loss"]), _p(b["dlogits"]),
+                                     N, st), "fc1 + loss"); k += 1
+                part2 = True
             branch.wait_stream(main)
             ok(L.pdl_fc_bwd_pool3_part(1, _p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
                                        _p(b["db3part"]), N, sb), "fc1 weight gradient"); k += 1
-            ok(L.pdl_fc_bwd_pool3_part(2, _p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
-                                       _p(b["db3part"]), N, st), "fc1 dgrad + pool3 backward"); k += 1
+            if part2:
+                ok(L.pdl_fc_bwd_pool3_part(2, _p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]),
+                                           _p(b["dz3"]), _p(b["db3part"]), N, st), "fc1 dgrad + pool3 backward"); k += 1
         else:
+            ok(L.pdl_fc_ce_fused(_p(b["a3"]), _p(b["wfp"]), _p(bf), _p(b["y"]), _p(b["logits"]), _p(b["row_loss"]), _p(b["loss"]), _p(b["dlogits"]), N, st),
+               "fc1 + loss"); k += 1
             ok(L.pdl_fc_bwd_pool3_fused(_p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
                                         _p(b["db3part"]), N, st), "fc1 backward + pool3 backward"); k += 1
         branch.wait_stream(main)  # dz3 / db3part are ready
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a2"]), _p(b["dz3"]), _p(gw3), _p(gb3), _p(b["db3part"]), N, _p(b["wg_scratch"]), N, 10, 10, 64, 128, 3, 3, 0,
                                  err, sb), "conv3 wgrad"); k += 2
-        ok(L.pdl_tc_conv2d_dgrad(_p(b["dz3"]), _p(b["p3b"]), _p(b["da2"]), N, 10, 10, 64, 128, 3, 3, 0, err, st), "conv3 dgrad"); k += 1
-        ok(L.pdl_pool2_bwd_dbias(_p(b["da2"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 11, 11, 64, 1, st), "pool2 backward"); k += 1
+        if self.fuse_pool2:  # conv3 dgrad with pool2's backward + ReLU mask + bias partials in its epilogue
+            ok(L.pdl_tc_conv2d_dgrad_poolbwd(_p(b["dz3"]), _p(b["p3b"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 10, 10, 64, 128,
+                                             3, 3, 0, 1, err, st), "conv3 dgrad + pool2 backward"); k += 1
+        else:
+            ok(L.pdl_tc_conv2d_dgrad(_p(b["dz3"]), _p(b["p3b"]), _p(b["da2"]), N, 10, 10, 64, 128, 3, 3, 0, err, st), "conv3 dgrad"); k += 1
+            ok(L.pdl_pool2_bwd_dbias(_p(b["da2"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 11, 11, 64, 1, st), "pool2 backward"); k += 1
         branch.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
                                  3, 3, 0, err, sb), "conv2 wgrad"); k += 2

@@ -150,11 +150,19 @@ def test_tc_path_is_used_by_autograd_function():
     _tf32_close(w.grad, wr.grad)
 
 
+@pytest.mark.parametrize("variant", ["default", "single-stream", "fused-fc-pool2"])
 @pytest.mark.parametrize("batch", [100, 7])
 @pytest.mark.parametrize("opt_kw", [dict(lr=1e-2), dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)])
-def test_graphed_trainstep_tensor_core_path(batch, opt_kw):
-    """The flagship path: whole step in one CUDA graph with the tcgen05 conv kernels (TF32), against fp32 torch."""
+def test_graphed_trainstep_tensor_core_path(batch, opt_kw, variant, monkeypatch):
+    """The flagship path: whole step in one CUDA graph with the tcgen05 conv kernels (TF32), against fp32 torch.
+    Variants: the default forked graph, everything on one stream, and the opt-in fused kernels."""
     import copy
+
+    if variant == "single-stream":
+        monkeypatch.setenv("PDL_CONVNET_FORK", "0")
+    elif variant == "fused-fc-pool2":
+        monkeypatch.setenv("PDL_CONVNET_FUSE_FC", "1")
+        monkeypatch.setenv("PDL_CONVNET_FUSE_POOL2", "1")
 
     import pytorch_distributed_learning_b200 as pdl
     from test_gpu_engine import _reference_run
@@ -181,3 +189,47 @@ def test_graphed_trainstep_tensor_core_path(batch, opt_kw):
         err_ours, err_torch = (a - b).norm().item(), (c - b).norm().item()
         assert err_ours <= 2.5 * err_torch + 1e-2 * delta_ref + 1e-7, \
             "%s: |ours - fp32| = %.3e, |torch TF32 - fp32| = %.3e, update norm %.3e" % (n, err_ours, err_torch, delta_ref)
+
+
+# (N, Cin, H (pooled extent), Cout, k, pad, pool stride)
+POOLBWD_CASES = [(5, 64, 10, 128, 3, 0, 1), (100, 64, 10, 128, 3, 0, 1), (7, 32, 6, 64, 3, 1, 2), (9, 64, 5, 64, 3, 1, 1), (3, 128, 8, 128, 1, 0, 2)]
+
+
+@pytest.mark.parametrize("case", POOLBWD_CASES)
+def test_tc_dgrad_with_fused_pool_backward(case):
+    """conv dgrad whose epilogue also runs the 2x2 max-pool backward + ReLU mask + bias partials of the layer below,
+    against the same thing done by torch ops on strict-fp32 data."""
+    N, Cin, H, Cout, k, pad, ps = case
+    torch.manual_seed(11)
+    L = _lib.cuda()
+    ZH = (H - 1) * ps + 2
+    z = torch.randn(N, Cin, ZH, ZH, device=DEV)                     # pre-activation of the layer below
+    a = torch.relu(z)
+    pooled, flat_idx = F.max_pool2d(a, 2, ps, return_indices=True)    # [N, Cin, H, H]
+    # arg-max code 0..3 inside each window, NHWC like the kernels store it
+    ph = torch.arange(H, device=DEV).view(1, 1, H, 1) * ps
+    pw = torch.arange(H, device=DEV).view(1, 1, 1, H) * ps
+    code = ((flat_idx // ZH - ph) * 2 + (flat_idx % ZH - pw)).to(torch.uint8)
+    idx_nhwc = code.permute(0, 2, 3, 1).contiguous()
+    pooled_nhwc = pooled.contiguous(memory_format=CL)
+    P = H + 2 * pad - k + 1
+    dy = torch.randn(N, Cout, P, P, device=DEV).contiguous(memory_format=CL)
+    w = torch.randn(Cout, Cin, k, k, device=DEV) * 0.1
+    _, packed = tc_conv.pack_weights(w, False, True)
+    tiles = L.pdl_tc_dgrad_poolbwd_tiles(N, H, H)
+    assert tiles > 0
+    dz = torch.full((N, ZH, ZH, Cin), float("nan"), device=DEV)
+    dbpart = torch.full((tiles, Cin), float("nan"), device=DEV)
+    rc = L.pdl_tc_conv2d_dgrad_poolbwd(NF._p(dy), NF._p(packed), NF._p(idx_nhwc), NF._p(pooled_nhwc), NF._p(dz), NF._p(dbpart), N, H, H, Cin, Cout,
+                                       k, k, pad, ps, NF._p(tc_conv.error_flag(DEV)), NF._stream(dy))
+    assert rc == 0, L.pdl_last_error()
+    tc_conv.check_errors(DEV)
+    # oracle: strict-fp32 dgrad, then autograd through relu + max_pool
+    torch.backends.cudnn.allow_tf32 = False
+    da = torch.nn.grad.conv2d_input((N, Cin, H, H), w, dy, stride=1, padding=pad)
+    torch.backends.cudnn.allow_tf32 = True
+    zr = z.clone().requires_grad_(True)
+    F.max_pool2d(torch.relu(zr), 2, ps).backward(da)
+    ref = zr.grad.permute(0, 2, 3, 1)
+    _tf32_close(dz, ref, scale_ref=da)
+    torch.testing.assert_close(dbpart.sum(0), dz.sum((0, 1, 2)), rtol=2e-3, atol=2e-3 * dz.abs().sum((0, 1, 2)).max().item() / 10 + 1e-4)
