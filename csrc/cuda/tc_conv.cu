@@ -427,7 +427,10 @@ int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& o, 
     PDL_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<N_GEMM>::TOTAL));
     configured = true;
   }
-  int grid = g.num_tiles < 148 ? g.num_tiles : 148;
+  // balanced waves: 200 tiles run as 100 CTAs x 2 tiles, not 148 CTAs of which 52 take two -- same makespan, and the
+  // SMs left over go to whatever runs beside this kernel (the wgrad branch of the ConvNet graph)
+  const int waves = (g.num_tiles + 147) / 148;
+  int grid = (g.num_tiles + waves - 1) / waves;
   PDL_CUDA_CHECK(launch_dependent(kernel, dim3(grid), dim3(kThreads), Smem<N_GEMM>::TOTAL, stream, a, b, o, g, e));
   PDL_LAUNCH_CHECK();
   return 0;

@@ -259,6 +259,10 @@ bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KH, int KW, int pad
   int splits = (2 * 148 + KH * tiles - 1) / (KH * tiles);
   if (KH * tiles < 74) splits = 148 / (KH * tiles);  // few big tiles: one wave, each split costs a full dW of partial traffic
   if (splits > 148) splits = 148;
+  {
+    static const int cta_cap = env_int("PDL_WG_MAX_CTAS", 0);  // experiment knob: bound the grid (KH * splits * tiles)
+    if (cta_cap > 0 && KH * tiles * splits > cta_cap) splits = cta_cap / (KH * tiles) > 0 ? cta_cap / (KH * tiles) : 1;
+  }
   if (splits > g->units) splits = g->units;
   if (splits < 1) splits = 1;
   g->units_per_cta = (g->units + splits - 1) / splits;
