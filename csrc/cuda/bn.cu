@@ -358,6 +358,29 @@ PDL_API int pdl_bn_fwd_train(const float* x, const float* residual, const float*
   return 0;
 }
 
+namespace {
+// Statistics already reduced to `splits` (count, mean, M2) triples per channel by the producer of x (the tcgen05
+// convolution's epilogue): only the per-channel merge is left.
+__global__ void __launch_bounds__(kThreads) bn_finalize_only_kernel(const float* __restrict__ partial, int splits, int C, const FinalizeArgs fin) {
+  finalize_group(partial, splits, C, blockIdx.x, fin);
+}
+}  // namespace
+
+// Training forward when the producer of x already left per-channel partial statistics ([splits][C][3]: count, mean,
+// M2 -- pdl_tc_conv2d_fwd_bnstats): x is read once (normalise) instead of twice.  Same outputs as pdl_bn_fwd_train.
+PDL_API int pdl_bn_fwd_train_prestats(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean,
+                                      float* running_var, long long* num_batches_tracked, float momentum, float eps, float* y, float* saved,
+                                      uint8_t* relu_mask, const float* partial, int splits, long long M, int C, int relu, cudaStream_t stream) {
+  if (check_c(C)) return -1;
+  if (splits < 1) { pdl_set_error("batch norm: no partial statistics"); return -1; }
+  const int cgroups = (C + kCG - 1) / kCG;
+  const FinalizeArgs fin{gamma, beta, running_mean, running_var, momentum, eps, saved, num_batches_tracked};
+  bn_finalize_only_kernel<<<cgroups, kThreads, 0, stream>>>(partial, splits, C, fin);
+  apply(x, residual, y, saved + 2ll * C, saved + 3ll * C, M, C, relu, relu_mask, stream);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
 PDL_API int pdl_bn_fwd_eval(const float* x, const float* residual, const float* gamma, const float* beta, const float* running_mean,
                             const float* running_var, float eps, float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
   if (check_c(C)) return -1;

@@ -47,6 +47,7 @@ struct EpiArgs {
   long long* trace;  // optional: clock64() of CTA 0 at pipeline milestones (profiling aid)
   const float* pooled;  // EPI_POOL_BWD: the pooled activations (ReLU mask) ...
   float* dbpart;        // ... and where the per-tile column sums go; `idx` is then the pool's arg-max, `out` is dz
+  float* bn_partial;    // EPI_STORE + tma_store: per-CTA (count, mean, M2) of every output channel, [grid / n_tiles][ldc][3]
 };
 
 template <int N_GEMM>
@@ -183,6 +184,8 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     constexpr int CH = HALF < 32 ? HALF : 32;   // columns per TMEM load
     int acc = 0;
     uint32_t acc_phase = 0;
+    float bn_sum = 0.f, bn_sq = 0.f;  // fused BatchNorm statistics (see e.bn_partial)
+    int bn_count = 0;
     for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
       if (*failed || !tc::mbar_wait(&tfull[acc], acc_phase)) { *failed = 1; break; }
       tc::tc_fence_after();
@@ -222,6 +225,27 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int cc = 0; cc < N_GEMM / 32; ++cc)
             tc::tma_store_4d(&tmOut, reinterpret_cast<uint8_t*>(staging) + cc * A_BYTES, nt * N_GEMM + cc * 32, 0, h0, n0);
           tc::bulk_commit();
+        }
+        if (e.bn_partial) {
+          // BatchNorm statistics of this output, straight from the staged tile (saves the normalisation layer a full
+          // read of the tensor).  The grid is a multiple of n_tiles, so every tile of this CTA has the same column
+          // block and the sums live in two registers per thread: thread = (column, row slice).  Only the rows that exist
+          // in the output count: a ragged last strip / a last tile with fewer images still computes the rows past the
+          // tensor edge (from the halo of valid input), the TMA store merely clips them.  Rows are ordered image, row,
+          // column, so the valid ones are a prefix of the tile.
+          constexpr int PARTS = 256 / N_GEMM;
+          const int col = et % N_GEMM, part = et / N_GEMM;
+          const uint8_t* src = reinterpret_cast<const uint8_t*>(staging) + (col / 32) * A_BYTES + (col % 4) * 4;
+          const int piece = (col % 32) / 4;
+          const int vh = min(g.BH, g.Hc - h0), vn = min(g.BN, g.Nimg - n0);
+          const int valid_rows = g.BW * (vh > 0 ? vh : 0) * (vn > 0 ? vn : 0);
+#pragma unroll 4
+          for (int r = part; r < valid_rows; r += PARTS) {
+            const float v = *reinterpret_cast<const float*>(src + r * 128 + ((piece ^ (r & 7)) << 4));
+            bn_sum += v;
+            bn_sq = fmaf(v, v, bn_sq);
+          }
+          bn_count += valid_rows;
         }
       } else if (EPI == EPI_STORE) {
         const int bw = row % g.BW, t2 = row / g.BW, bh = t2 % g.BH, bn = t2 / g.BH;
@@ -356,6 +380,25 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
     if (EPI == EPI_STORE && e.tma_store && et == 0) tc::bulk_wait_read_all();  // smem must outlive the last store's reads
+    if (EPI == EPI_STORE && e.tma_store && e.bn_partial) {
+      // this CTA's (count, mean, M2) per column -> bn_partial[split][C][3], split = blockIdx.x / n_tiles
+      constexpr int PARTS = 256 / N_GEMM;
+      asm volatile("bar.sync 1, 256;" ::: "memory");  // all stores drained, staging is free
+      const int col = et % N_GEMM, part = et / N_GEMM;
+      staging[(part * 2 + 0) * N_GEMM + col] = bn_sum;
+      staging[(part * 2 + 1) * N_GEMM + col] = bn_sq;
+      asm volatile("bar.sync 1, 256;" ::: "memory");
+      if (et < N_GEMM) {
+        float s = 0.f, q = 0.f;
+#pragma unroll
+        for (int p = 0; p < PARTS; ++p) { s += staging[(p * 2) * N_GEMM + et]; q += staging[(p * 2 + 1) * N_GEMM + et]; }  // fixed order
+        const float n = static_cast<float>(bn_count);
+        const float mean = n > 0.f ? s / n : 0.f;
+        const int nt_mine = blockIdx.x % g.n_tiles;
+        float* o = e.bn_partial + (static_cast<long long>(blockIdx.x / g.n_tiles) * g.ldc + nt_mine * N_GEMM + et) * 3;
+        o[0] = n; o[1] = mean; o[2] = fmaxf(q - s * mean, 0.f);
+      }
+    }
   }
 
   tc::tc_fence_before();
@@ -419,6 +462,18 @@ inline bool use_tma_store() {
   return v != 0;
 }
 
+// CTAs of a launch over num_tiles (= m_tiles * n_tiles) tiles: balanced waves; with fused BatchNorm statistics also a
+// multiple of n_tiles, so that all tiles of a CTA share one column block (grid / n_tiles = rows of the partial buffer).
+int tc_grid(int num_tiles, int n_tiles, bool bn_stats) {
+  const int waves = (num_tiles + 147) / 148;
+  int grid = (num_tiles + waves - 1) / waves;
+  if (bn_stats) {
+    grid = grid / n_tiles * n_tiles;
+    if (grid < n_tiles) grid = n_tiles;
+  }
+  return grid;
+}
+
 template <int N_GEMM, int EPI>
 int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& o, const TcGeom& g, const EpiArgs& e, cudaStream_t stream) {
   static bool configured = false;
@@ -429,8 +484,7 @@ int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& o, 
   }
   // balanced waves: 200 tiles run as 100 CTAs x 2 tiles, not 148 CTAs of which 52 take two -- same makespan, and the
   // SMs left over go to whatever runs beside this kernel (the wgrad branch of the ConvNet graph)
-  const int waves = (g.num_tiles + 147) / 148;
-  int grid = (g.num_tiles + waves - 1) / waves;
+  const int grid = tc_grid(g.num_tiles, g.n_tiles, e.bn_partial != nullptr);
   PDL_CUDA_CHECK(launch_dependent(kernel, dim3(grid), dim3(kThreads), Smem<N_GEMM>::TOTAL, stream, a, b, o, g, e));
   PDL_LAUNCH_CHECK();
   return 0;
@@ -502,7 +556,8 @@ PDL_API int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed
 // Forward: y = conv(x, w) + bias, optional ReLU; with pool_stride in {1,2} the 2x2 max-pool is fused and
 // `y`/`idx` receive the POOLED output [N][PH][PW][Cout] and its argmax (0..3).  x is NHWC.
 static int tc_fwd_impl(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin, int Cout,
-                       int KH, int KW, int stride, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream) {
+                       int KH, int KW, int stride, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream,
+                       float* bn_partial = nullptr) {
   TcGeom g{};
   const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
   g.in_stride = stride;
@@ -519,8 +574,29 @@ static int tc_fwd_impl(const float* x, const float* packed_w, const float* bias,
   const int tma_store = pool_stride == 0 && use_tma_store();
   CUtensorMap to = ta;
   if (tma_store) { if (int rc = make_out_map(&to, y, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc; }
-  EpiArgs e{y, idx, bias, relu, pool_stride, tma_store, error_flag, g_trace};
+  if (bn_partial && (!tma_store || bias || relu)) { pdl_set_error("tc_conv fwd: fused BatchNorm statistics need the plain TMA-store epilogue"); return -3; }
+  EpiArgs e{y, idx, bias, relu, pool_stride, tma_store, error_flag, g_trace, nullptr, nullptr, bn_partial};
   return pool_stride > 0 ? dispatch_n<EPI_RELU_POOL>(ng, ta, tb, to, g, e, stream) : dispatch_n<EPI_STORE>(ng, ta, tb, to, g, e, stream);
+}
+
+// Rows of the statistics buffer pdl_tc_conv2d_fwd_bnstats fills ([splits][Cout][3] floats: count, mean, M2 per CTA group),
+// or 0 when the shape is not covered by the tensor-core forward.
+PDL_API int pdl_tc_conv_bn_splits(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
+  if (!pdl_tc_conv_supported(H, W, Cin, Cout, KH, KW, stride, pad, 0) || !use_tma_store()) return 0;
+  TcGeom g{};
+  const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
+  if (!choose_box(P, Q, 0, &g)) return 0;
+  const int n_tiles = Cout / n_gemm_for(Cout);
+  const int num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * n_tiles;
+  return tc_grid(num_tiles, n_tiles, true) / n_tiles;
+}
+
+// Bias-free forward (stride 1|2) that also leaves the per-channel BatchNorm statistics of its output in bn_partial, in
+// the partial format of pdl_bn_fwd_train_prestats -- the normalisation layer then skips its own pass over y.
+PDL_API int pdl_tc_conv2d_fwd_bnstats(const float* x, const float* packed_w, float* y, float* bn_partial, int N, int H, int W, int Cin, int Cout,
+                                      int KH, int KW, int stride, int pad, int* error_flag, cudaStream_t stream) {
+  if (stride != 1 && stride != 2) { pdl_set_error("tc_conv fwd: stride %d is not supported", stride); return -3; }
+  return tc_fwd_impl(x, packed_w, nullptr, y, nullptr, N, H, W, Cin, Cout, KH, KW, stride, pad, 0, 0, error_flag, stream, bn_partial);
 }
 
 PDL_API int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin,
@@ -690,8 +766,8 @@ PDL_API int pdl_tc_stem_pack_weights(const float* w, float* packed, int Cout, in
 }
 
 // y[N][P][Q][Cout] = conv(x, w) (+ bias, ReLU) from the padded copy and the packed weights.
-PDL_API int pdl_tc_stem_fwd(const float* xp, const float* packed_w, const float* bias, float* y, int N, int H, int W, int Cout, int KH, int KW,
-                            int stride, int pad, int relu, int* error_flag, cudaStream_t stream) {
+static int stem_fwd_impl(const float* xp, const float* packed_w, const float* bias, float* y, int N, int H, int W, int Cout, int KH, int KW,
+                         int stride, int pad, int relu, int* error_flag, cudaStream_t stream, float* bn_partial) {
   const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
   TcGeom g{};
   if (!choose_box(d.P, d.Q, 0, &g)) { pdl_set_error("stem conv: no tile for %dx%d output", d.P, d.Q); return -4; }
@@ -719,6 +795,25 @@ PDL_API int pdl_tc_stem_fwd(const float* xp, const float* packed_w, const float*
   const int tma_store = use_tma_store();
   CUtensorMap to = ta;
   if (tma_store) { if (int rc = make_out_map(&to, y, N, d.P, d.Q, Cout, g.BW, g.BH, g.BN)) return rc; }
-  EpiArgs e{y, nullptr, bias, relu, 0, tma_store, error_flag, g_trace};
+  if (bn_partial && (!tma_store || bias || relu)) { pdl_set_error("stem conv: fused BatchNorm statistics need the plain TMA-store epilogue"); return -3; }
+  EpiArgs e{y, nullptr, bias, relu, 0, tma_store, error_flag, g_trace, nullptr, nullptr, bn_partial};
   return dispatch_n<EPI_STORE>(ng, ta, tb, to, g, e, stream);
+}
+PDL_API int pdl_tc_stem_fwd(const float* xp, const float* packed_w, const float* bias, float* y, int N, int H, int W, int Cout, int KH, int KW,
+                            int stride, int pad, int relu, int* error_flag, cudaStream_t stream) {
+  return stem_fwd_impl(xp, packed_w, bias, y, N, H, W, Cout, KH, KW, stride, pad, relu, error_flag, stream, nullptr);
+}
+// Stem forward that also produces the BatchNorm statistics of its output (see pdl_tc_conv2d_fwd_bnstats).
+PDL_API int pdl_tc_stem_bn_splits(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
+  if (!pdl_tc_stem_supported(H, W, Cin, Cout, KH, KW, stride, pad) || !use_tma_store()) return 0;
+  const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
+  TcGeom g{};
+  if (!choose_box(d.P, d.Q, 0, &g)) return 0;
+  const int n_tiles = Cout / n_gemm_for(Cout);
+  const int num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * n_tiles;
+  return tc_grid(num_tiles, n_tiles, true) / n_tiles;
+}
+PDL_API int pdl_tc_stem_fwd_bnstats(const float* xp, const float* packed_w, float* y, float* bn_partial, int N, int H, int W, int Cout, int KH,
+                                    int KW, int stride, int pad, int* error_flag, cudaStream_t stream) {
+  return stem_fwd_impl(xp, packed_w, nullptr, y, N, H, W, Cout, KH, KW, stride, pad, 0, error_flag, stream, bn_partial);
 }

@@ -102,6 +102,12 @@ long long pdl_tc_wgrad_scratch_bytes_strided(int N, int H, int W, int Cin, int C
 int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch,
                                 int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int* error_flag,
                                 cudaStream_t stream); /* stride 1 or 2 */
+/* Bias-free forward that also leaves the BatchNorm statistics of its output in bn_partial ([splits][Cout][3] floats:
+ * count, mean, M2 per CTA group; splits = pdl_tc_conv_bn_splits(...), 0 = shape not covered): the epilogue reduces
+ * the staged output tile, so the following BatchNorm (pdl_bn_fwd_train_prestats) does not re-read the tensor. */
+int pdl_tc_conv_bn_splits(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+int pdl_tc_conv2d_fwd_bnstats(const float* x, const float* packed_w, float* y, float* bn_partial, int N, int H, int W, int Cin, int Cout, int KH,
+                              int KW, int stride, int pad, int* error_flag, cudaStream_t stream);
 /* dgrad of a stride-1 conv whose input is ReLU + 2x2 max-pool (stride 1|2) of the layer below, pool/ReLU backward fused
  * into the epilogue: writes dz[N][(H-1)*ps+2][(W-1)*ps+2][Cin] (TF32-rounded) and dbpart[tiles][Cin] column sums */
 int pdl_tc_dgrad_poolbwd_tiles(int N, int H, int W);
@@ -120,6 +126,9 @@ int pdl_tc_stem_prepare(const float* x, long long sn, long long sc, long long sh
 int pdl_tc_stem_pack_weights(const float* w, float* packed, int Cout, int Cin, int KH, int KW, cudaStream_t stream);
 int pdl_tc_stem_fwd(const float* xp, const float* packed_w, const float* bias, float* y, int N, int H, int W, int Cout, int KH, int KW, int stride,
                     int pad, int relu, int* error_flag, cudaStream_t stream);
+int pdl_tc_stem_bn_splits(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+int pdl_tc_stem_fwd_bnstats(const float* xp, const float* packed_w, float* y, float* bn_partial, int N, int H, int W, int Cout, int KH, int KW,
+                            int stride, int pad, int* error_flag, cudaStream_t stream); /* stem forward + BatchNorm statistics of y */
 int pdl_tc_stem_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
 long long pdl_tc_stem_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
 int pdl_tc_stem_wgrad(const float* xp, const float* dy, float* dw, float* scratch, int N, int H, int W, int Cin, int Cout, int KH, int KW,
@@ -153,6 +162,9 @@ long long pdl_bn_scratch_floats(long long M, int C);
 int pdl_bn_fwd_train(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean, float* running_var,
                      long long* num_batches_tracked, float momentum, float eps, float* y, float* saved, uint8_t* relu_mask, float* scratch,
                      long long M, int C, int relu, cudaStream_t stream); /* relu_mask: M*C/4 bytes, written for the residual+ReLU form */
+int pdl_bn_fwd_train_prestats(const float* x, const float* residual, const float* gamma, const float* beta, float* running_mean,
+                              float* running_var, long long* num_batches_tracked, float momentum, float eps, float* y, float* saved,
+                              uint8_t* relu_mask, const float* partial, int splits, long long M, int C, int relu, cudaStream_t stream);
 int pdl_bn_fwd_eval(const float* x, const float* residual, const float* gamma, const float* beta, const float* running_mean,
                     const float* running_var, float eps, float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream);
 int pdl_bn_bwd(const float* x, const float* dy, const uint8_t* relu_mask, const float* gamma, const float* saved, float* dx, float* dres,

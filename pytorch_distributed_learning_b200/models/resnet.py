@@ -21,6 +21,20 @@ def _conv1x1(cin, cout, stride=1):
     return nn.Conv2d(cin, cout, kernel_size=1, stride=stride, bias=False)
 
 
+def _conv_bn(conv, bn, x, relu=False, residual=None):
+    """conv -> batch norm (-> + residual) (-> ReLU) as the fused kernels see it: the convolution's epilogue reduces the
+    normalisation statistics (``bn_stats=True`` is a hint, ignored where it does not apply), and the normalisation,
+    skip connection and activation are one pass over the tensor."""
+    return bn(conv(x, bn_stats=True), relu=relu, residual=residual)
+
+
+def _downsample(ds, x):
+    """The ``downsample`` branch is ``Sequential(conv1x1, BatchNorm2d)`` (torchvision's layout, kept for the state_dict keys)."""
+    if isinstance(ds, nn.Sequential) and len(ds) == 2 and isinstance(ds[0], nn.Conv2d) and isinstance(ds[1], nn.BatchNorm2d):
+        return _conv_bn(ds[0], ds[1], x)
+    return ds(x)
+
+
 class BasicBlock(nn.Module):
     expansion = 1
 
@@ -35,9 +49,9 @@ class BasicBlock(nn.Module):
         self.stride = stride
 
     def forward(self, x):
-        identity = x if self.downsample is None else self.downsample(x)
-        out = self.bn1(self.conv1(x), relu=True)  # bn + relu, and below bn + add + relu, are single fused passes
-        return self.bn2(self.conv2(out), relu=True, residual=identity)
+        identity = x if self.downsample is None else _downsample(self.downsample, x)
+        out = _conv_bn(self.conv1, self.bn1, x, relu=True)
+        return _conv_bn(self.conv2, self.bn2, out, relu=True, residual=identity)
 
 
 class Bottleneck(nn.Module):
@@ -56,10 +70,10 @@ class Bottleneck(nn.Module):
         self.stride = stride
 
     def forward(self, x):
-        identity = x if self.downsample is None else self.downsample(x)
-        out = self.bn1(self.conv1(x), relu=True)
-        out = self.bn2(self.conv2(out), relu=True)
-        return self.bn3(self.conv3(out), relu=True, residual=identity)
+        identity = x if self.downsample is None else _downsample(self.downsample, x)
+        out = _conv_bn(self.conv1, self.bn1, x, relu=True)
+        out = _conv_bn(self.conv2, self.bn2, out, relu=True)
+        return _conv_bn(self.conv3, self.bn3, out, relu=True, residual=identity)
 
 
 class ResNet(nn.Module):
@@ -94,7 +108,7 @@ class ResNet(nn.Module):
         return nn.Sequential(*layers)
 
     def forward(self, x):
-        x = self.maxpool(self.bn1(self.conv1(x), relu=True))
+        x = self.maxpool(_conv_bn(self.conv1, self.bn1, x, relu=True))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = self.avgpool(x)
         x = x.flatten(1)

@@ -22,12 +22,21 @@ def _pair(v):
 
 
 class Conv2d(tnn.Conv2d):
-    def forward(self, x):
+    """``conv(x)``.  ``conv(x, bn_stats=True)`` tells the tensor-core kernel that a training-mode ``BatchNorm2d`` consumes
+    the result: its epilogue then also reduces the per-channel statistics of the output tile and the result carries them
+    (``_pdl_bn_partial``), so the normalisation layer does not have to re-read the tensor.  A hint, never a requirement."""
+
+    def forward(self, x, bn_stats=False):
         if (_native(x) and self.groups == 1 and _pair(self.dilation) == (1, 1) and self.padding_mode == "zeros"
                 and not isinstance(self.padding, str) and self.stride[0] == self.stride[1] and self.padding[0] == self.padding[1]
                 and self.kernel_size[0] == self.kernel_size[1]):
             from ..ops import functional as NF
 
+            if bn_stats and self.bias is None and torch.is_grad_enabled():
+                y, partial = NF.conv2d(x, self.weight, None, self.stride[0], self.padding[0], bn_stats=True)
+                if partial is not None:
+                    y._pdl_bn_partial = partial
+                return y
             return NF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0])
         return super().forward(x)
 
@@ -80,7 +89,8 @@ class BatchNorm2d(tnn.BatchNorm2d):
             from ..ops import functional as NF
 
             return NF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum, self.eps,
-                                 relu, residual, self.num_batches_tracked)  # the step counter is bumped by the finalize kernel
+                                 relu, residual, self.num_batches_tracked,  # the step counter is bumped by the finalize kernel
+                                 partial=getattr(x, "_pdl_bn_partial", None) if self.training else None)
         y = super().forward(x)
         if residual is not None:
             y = y + residual

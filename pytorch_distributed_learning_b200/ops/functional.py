@@ -52,7 +52,9 @@ def conv_out(h, k, s, p):
 
 class _Conv2d(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, b, stride, pad):
+    def forward(ctx, x, w, b, stride, pad, bn_stats=False):
+        """``bn_stats``: also return the per-channel statistics partials of y ([splits][Cout][3], or None when the
+        tensor-core kernel does not cover the shape) for the BatchNorm that follows."""
         L = _lib.cuda()
         w = w.contiguous()
         N, Cin, H, W = x.shape
@@ -64,19 +66,25 @@ class _Conv2d(torch.autograd.Function):
         ctx.geom = (stride, pad, b is not None)
         ctx.x_shape = tuple(x.shape)
         ctx.stem = tc_conv.stem_supported(x, w, stride, pad)
+        partial = None
         if ctx.stem:  # first layer: the padded NHWC4 copy replaces x for the backward pass (wgrad only needs that)
-            xp = tc_conv.stem_fwd(x, w, b, y, stride, pad)
+            xp, partial = tc_conv.stem_fwd(x, w, b, y, stride, pad, bn_stats=bn_stats)
             ctx.save_for_backward(xp, w, None)
+        else:
+            x = _nhwc(x)
+            handled, packed_bwd, partial = tc_conv.conv2d_fwd(x, w, b, y, stride, pad, relu=False, want_bwd_pack=ctx.needs_input_grad[0],
+                                                              bn_stats=bn_stats)
+            if not handled:
+                _ok(L.pdl_conv2d_fwd_simt(_p(x), _p(w), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, 0, _stream(x)), "conv2d forward")
+            ctx.save_for_backward(x, w, packed_bwd)
+        if not bn_stats:
             return y
-        x = _nhwc(x)
-        handled, packed_bwd = tc_conv.conv2d_fwd(x, w, b, y, stride, pad, relu=False, want_bwd_pack=ctx.needs_input_grad[0])
-        if not handled:
-            _ok(L.pdl_conv2d_fwd_simt(_p(x), _p(w), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, 0, _stream(x)), "conv2d forward")
-        ctx.save_for_backward(x, w, packed_bwd)
-        return y
+        if partial is not None:
+            ctx.mark_non_differentiable(partial)
+        return y, partial
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, *_unused):
         L = _lib.cuda()
         x, w, packed_bwd = ctx.saved_tensors
         stride, pad, has_bias = ctx.geom
@@ -101,10 +109,13 @@ class _Conv2d(torch.autograd.Function):
                 nbytes = L.pdl_conv2d_wgrad_scratch_bytes(N, H, W, Cin, Cout, KH, KW, stride, pad)
                 sc = scratch(nbytes, x.device, "wgrad")
                 _ok(L.pdl_conv2d_wgrad_simt(_p(x), _p(dy), _p(dw), _p(db), _p(sc), N, H, W, Cin, Cout, KH, KW, stride, pad, _stream(x)), "conv2d wgrad")
-        return dx, dw, db, None, None
+        return dx, dw, db, None, None, None
 
 
-def conv2d(x, w, b=None, stride=1, padding=0):
+def conv2d(x, w, b=None, stride=1, padding=0, bn_stats=False):
+    """``bn_stats=True`` returns ``(y, partial)``; see ``_Conv2d.forward``."""
+    if bn_stats:
+        return _Conv2d.apply(x, w, b, int(stride), int(padding), True)
     return _Conv2d.apply(x, w, b, int(stride), int(padding))
 
 
@@ -214,11 +225,13 @@ def cross_entropy(logits, target):
     return _CrossEntropy.apply(logits, target)
 
 
-def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None, num_batches_tracked=None):
-    """``act(bn(x) [+ residual])`` in one pass (the tail of every ResNet block)."""
+def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None, num_batches_tracked=None,
+               partial=None):
+    """``act(bn(x) [+ residual])`` in one pass (the tail of every ResNet block).  ``partial``: statistics partials of x
+    left by the convolution that produced it (``conv2d(..., bn_stats=True)``); x is then read once instead of twice."""
     from . import bn
 
-    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual, num_batches_tracked)
+    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual, num_batches_tracked, partial)
 
 
 class _GlobalAvgPool(torch.autograd.Function):

@@ -63,20 +63,32 @@ def dgrad_supported(Cin, Cout, W, stride):
     return stride in (1, 2) and Cout % 32 == 0 and (Cin in (32, 64) or Cin % 128 == 0) and W <= 128 * stride
 
 
-def conv2d_fwd(x, w, b, y, stride, pad, relu=False, want_bwd_pack=False):
-    """Returns (handled, packed_bwd): with ``want_bwd_pack`` the dgrad operand copy of the weights is produced by
-    the same packing launch and handed back for the backward pass (None when dgrad will not use the tensor cores)."""
+def conv2d_fwd(x, w, b, y, stride, pad, relu=False, want_bwd_pack=False, bn_stats=False):
+    """Returns (handled, packed_bwd, bn_partial).  With ``want_bwd_pack`` the dgrad operand copy of the weights is produced
+    by the same packing launch and handed back for the backward pass (None when dgrad will not use the tensor cores).  With
+    ``bn_stats`` (bias-free, no ReLU) the kernel's epilogue also reduces the BatchNorm statistics of y: bn_partial is
+    [splits][Cout][3] (count, mean, M2), or None when that is not possible."""
     if not enabled():
-        return False, None
+        return False, None, None
     N, Cin, H, W = x.shape
     Cout, _, KH, KW = w.shape
     L = _lib.cuda()
     if not L.pdl_tc_conv_supported(H, W, Cin, Cout, KH, KW, stride, pad, 0):
-        return False, None
+        return False, None, None
     packed, packed_bwd = pack_weights(w, True, want_bwd_pack and dgrad_supported(Cin, Cout, W, stride))
+    splits = L.pdl_tc_conv_bn_splits(N, H, W, Cin, Cout, KH, KW, stride, pad) if (bn_stats and b is None and not relu and fused_bn_stats()) else 0
+    if splits > 0:
+        partial = torch.empty((splits, Cout, 3), dtype=torch.float32, device=x.device)
+        _ok(L.pdl_tc_conv2d_fwd_bnstats(_p(x), _p(packed), _p(y), _p(partial), N, H, W, Cin, Cout, KH, KW, stride, pad,
+                                        _p(error_flag(x.device)), _stream(x)), "tensor-core conv forward + BatchNorm statistics")
+        return True, packed_bwd, partial
     _ok(L.pdl_tc_conv2d_fwd_strided(_p(x), _p(packed), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, int(relu),
                                     _p(error_flag(x.device)), _stream(x)), "tensor-core conv forward")
-    return True, packed_bwd
+    return True, packed_bwd, None
+
+
+def fused_bn_stats():
+    return os.environ.get("PDL_FUSE_BN_STATS", "1") != "0"
 
 
 def stem_supported(x, w, stride, pad):
@@ -90,8 +102,9 @@ def stem_supported(x, w, stride, pad):
                 and L.pdl_tc_stem_wgrad_supported(N, H, W, Cin, Cout, KH, KW, stride, pad))
 
 
-def stem_fwd(x, w, b, y, stride, pad):
-    """x in ANY layout (strides are passed down) -> y (NHWC); returns the padded NHWC4 copy the wgrad reuses."""
+def stem_fwd(x, w, b, y, stride, pad, bn_stats=False):
+    """x in ANY layout (strides are passed down) -> y (NHWC); returns (the padded NHWC4 copy the wgrad reuses, BatchNorm
+    statistics partials of y or None)."""
     N, Cin, H, W = x.shape
     Cout, _, KH, KW = w.shape
     L = _lib.cuda()
@@ -100,9 +113,15 @@ def stem_fwd(x, w, b, y, stride, pad):
     _ok(L.pdl_tc_stem_prepare(_p(x), sn, sc, sh, sw, _p(xp), N, Cin, H, W, KH, KW, stride, pad, _stream(x)), "stem input padding")
     packed = torch.empty((KH, Cout, 32), dtype=w.dtype, device=w.device)
     _ok(L.pdl_tc_stem_pack_weights(_p(w), _p(packed), Cout, Cin, KH, KW, _stream(x)), "stem weight packing")
+    splits = L.pdl_tc_stem_bn_splits(N, H, W, Cin, Cout, KH, KW, stride, pad) if (bn_stats and b is None and fused_bn_stats()) else 0
+    if splits > 0:
+        partial = torch.empty((splits, Cout, 3), dtype=torch.float32, device=x.device)
+        _ok(L.pdl_tc_stem_fwd_bnstats(_p(xp), _p(packed), _p(y), _p(partial), N, H, W, Cout, KH, KW, stride, pad, _p(error_flag(x.device)),
+                                      _stream(x)), "tensor-core stem conv forward + BatchNorm statistics")
+        return xp, partial
     _ok(L.pdl_tc_stem_fwd(_p(xp), _p(packed), _p(b), _p(y), N, H, W, Cout, KH, KW, stride, pad, 0, _p(error_flag(x.device)), _stream(x)),
         "tensor-core stem conv forward")
-    return xp
+    return xp, None
 
 
 def stem_wgrad(xp, dy, dw, x_shape, stride, pad):

@@ -301,3 +301,46 @@ def test_add_relu():
     yr.backward(dy)
     torch.testing.assert_close(a.grad, ar.grad)
     torch.testing.assert_close(b.grad, br.grad)
+
+
+# (N, Cin, H, Cout, k, stride, pad): whole-image tiles, row-strip tiles with a ragged last strip, several images per
+# tile, several column tiles, stride 2, and the small-Cin stem
+BN_STATS_CASES = [(4, 64, 56, 64, 3, 1, 1), (3, 64, 14, 256, 1, 1, 0), (5, 128, 7, 128, 3, 1, 1), (2, 256, 28, 512, 1, 2, 0),
+                  (3, 128, 30, 128, 3, 1, 1), (6, 3, 64, 64, 7, 2, 3)]
+
+
+@pytest.mark.parametrize("case", BN_STATS_CASES)
+def test_conv_epilogue_batchnorm_statistics(case):
+    """conv(x, bn_stats=True) -> bn: the statistics come from the convolution's epilogue; same result as bn's own pass."""
+    import copy
+
+    old = torch.backends.cudnn.allow_tf32
+    torch.backends.cudnn.allow_tf32 = True  # the tensor-core path is what carries the fused statistics
+    try:
+        N, Cin, H, Cout, k, stride, pad = case
+        torch.manual_seed(12)
+        conv = pdl.nn.Conv2d(Cin, Cout, k, stride, pad, bias=False).to(_dev())
+        bn_a = pdl.nn.BatchNorm2d(Cout).to(_dev())
+        with torch.no_grad():
+            bn_a.weight.uniform_(0.5, 1.5)
+            bn_a.bias.uniform_(-0.5, 0.5)
+        bn_b = copy.deepcopy(bn_a)
+        x = (torch.randn(N, Cin, H, H, device=_dev()) + 0.3).requires_grad_(Cin > 4)
+        ya = conv(x, bn_stats=True)
+        partial = getattr(ya, "_pdl_bn_partial", None)
+        assert partial is not None and partial.shape[1:] == (Cout, 3)
+        P = (H + 2 * pad - k) // stride + 1
+        assert torch.equal(partial[:, :, 0].sum(0), torch.full((Cout,), float(N * P * P), device=_dev()))
+        out_a = bn_a(ya, relu=True)
+        yb = conv(x)
+        assert not hasattr(yb, "_pdl_bn_partial")
+        torch.testing.assert_close(ya, yb, rtol=0, atol=0)  # same kernel, same tile order
+        out_b = bn_b(yb, relu=True)
+        torch.testing.assert_close(out_a, out_b, rtol=1e-4, atol=1e-4)
+        torch.testing.assert_close(bn_a.running_mean, bn_b.running_mean, rtol=1e-4, atol=1e-6)
+        torch.testing.assert_close(bn_a.running_var, bn_b.running_var, rtol=1e-4, atol=1e-6)
+        assert int(bn_a.num_batches_tracked) == 1
+        out_a.square().sum().backward()
+        assert conv.weight.grad is not None and torch.isfinite(conv.weight.grad).all()
+    finally:
+        torch.backends.cudnn.allow_tf32 = old
