@@ -545,6 +545,53 @@ PDL_API int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int K
   return choose_box(P, Q, pool, &g) ? 1 : 0;
 }
 
+namespace {
+// All convolution weights of a model in ONE launch (a per-layer pack is a ~5 us latency-bound kernel, 52 of them in a
+// ResNet-50 step, and its element-wise transposing writes touch one 32-byte sector per float).  A CTA owns a tile of
+// 32 output x 32 input channels x taps (<= 9): the tile is read with contiguous runs of 32*taps floats per output
+// channel, staged in shared memory (TF32-rounded), and written out as 128-byte rows in both operand layouts,
+// fwd[tap][co][ci] and bwd[tap][ci][co].  table[t] = {w, packed_fwd, packed_bwd, Cout, Cin, taps} as int64;
+// prefix[t] = first tile of tensor t.
+constexpr int kPackMaxTaps = 9;
+__global__ void __launch_bounds__(256) pack_weights_multi_kernel(const long long* __restrict__ table, const int* __restrict__ prefix, int num) {
+  __shared__ float tile[32][32 * kPackMaxTaps + 1];  // [co][ci * taps + tap]
+  int lo = 0, hi = num - 1;  // binary search: prefix[lo] <= blockIdx.x < prefix[lo + 1]
+  while (lo < hi) {
+    const int mid = (lo + hi + 1) / 2;
+    if (prefix[mid] <= static_cast<int>(blockIdx.x)) lo = mid; else hi = mid - 1;
+  }
+  const long long* row = table + lo * 6;
+  const float* w = reinterpret_cast<const float*>(row[0]);
+  float* fwd = reinterpret_cast<float*>(row[1]);
+  float* bwd = reinterpret_cast<float*>(row[2]);
+  const int Cout = static_cast<int>(row[3]), Cin = static_cast<int>(row[4]), taps = static_cast<int>(row[5]);
+  const int t = blockIdx.x - prefix[lo], ci_tiles = Cin / 32;
+  const int co0 = (t / ci_tiles) * 32, ci0 = (t % ci_tiles) * 32;
+  const int run = 32 * taps;  // contiguous floats per output channel in w: [ci0 .. ci0+32) x taps
+  for (int k = threadIdx.x; k < 32 * run; k += 256) {
+    const int co = k / run, e = k % run;
+    tile[co][e] = round_tf32(w[(static_cast<long long>(co0 + co) * Cin + ci0) * taps + e]);
+  }
+  __syncthreads();
+  const int lane = threadIdx.x % 32, wp = threadIdx.x / 32;
+  for (int r = wp; r < 32 * taps; r += 8) {  // one 128-byte row per warp iteration, for each layout
+    const int tap = r / 32, j = r % 32;
+    if (fwd) fwd[(static_cast<long long>(tap) * Cout + co0 + j) * Cin + ci0 + lane] = tile[j][lane * taps + tap];   // row = (tap, co), lanes = ci
+    if (bwd) bwd[(static_cast<long long>(tap) * Cin + ci0 + j) * Cout + co0 + lane] = tile[lane][j * taps + tap];   // row = (tap, ci), lanes = co
+  }
+}
+}  // namespace
+
+PDL_API int pdl_tc_pack_max_taps() { return kPackMaxTaps; }
+// table: [num][6] int64 device rows {w, packed_fwd, packed_bwd, Cout, Cin, taps} with Cout % 32 == Cin % 32 == 0 and
+// taps <= pdl_tc_pack_max_taps(); prefix: [num + 1] int32 offsets in tiles of 32 x 32 channels ((Cout/32)*(Cin/32) per tensor).
+PDL_API int pdl_tc_pack_weights_multi(const void* table, const int* prefix, int num, int total_tiles, cudaStream_t stream) {
+  if (num <= 0 || total_tiles <= 0) return 0;
+  pack_weights_multi_kernel<<<total_tiles, 256, 0, stream>>>(static_cast<const long long*>(table), prefix, num);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
 // w[Cout][Cin][KH][KW] -> packed_fwd[tap][Cout][Cin], packed_bwd[tap][Cin][Cout] (either may be null).
 PDL_API int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed_bwd, int Cout, int Cin, int taps, cudaStream_t stream) {
   int total = Cout * Cin * taps;

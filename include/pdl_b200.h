@@ -85,6 +85,11 @@ int pdl_conv2d_wgrad_simt_noalloc(const float* x, const float* dy, float* dw, fl
 /* ---- convolution, tcgen05 tensor cores (TF32 in, fp32 accumulate in TMEM), TMA-fed (same reference lines) ---- */
 int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool);
 int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed_bwd, int Cout, int Cin, int taps, cudaStream_t stream);
+/* every convolution weight of a model in one launch (shared-memory tile transpose, both operand layouts): table
+ * [num][6] int64 {w, fwd, bwd, Cout, Cin, taps} (device; channels % 32 == 0, taps <= pdl_tc_pack_max_taps()),
+ * prefix [num+1] int32 first 32x32-channel tile of each tensor */
+int pdl_tc_pack_max_taps(void);
+int pdl_tc_pack_weights_multi(const void* table, const int* prefix, int num, int total_tiles, cudaStream_t stream);
 /* pool_stride 0: y = conv+bias(+relu); 1|2: fused ReLU + 2x2 max-pool, y/idx are the pooled output and argmax */
 int pdl_tc_conv2d_fwd(const float* x, const float* packed_w, const float* bias, float* y, uint8_t* idx, int N, int H, int W, int Cin, int Cout,
                       int KH, int KW, int pad, int relu, int pool_stride, int* error_flag, cudaStream_t stream);

@@ -48,6 +48,8 @@ def declare(L):
     # convolution (tcgen05 / TMA tensor-core path)
     sig("pdl_tc_conv_supported", [I, I, I, I, I, I, I, I, I])
     sig("pdl_tc_pack_weights", [P, P, P, I, I, I, P])
+    sig("pdl_tc_pack_max_taps", [])
+    sig("pdl_tc_pack_weights_multi", [P, P, I, I, P])
     sig("pdl_tc_conv2d_fwd", [P, P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv2d_fwd_strided", [P, P, P, P, I, I, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv2d_dgrad", [P, P, P, I, I, I, I, I, I, I, I, P, P])

@@ -79,12 +79,15 @@ class _Conv2d(torch.autograd.Function):
             ctx.save_for_backward(x, w, packed_bwd)
         if not bn_stats:
             return y
+        ctx.set_materialize_grads(False)  # no zero-filled "gradient" tensor for the statistics output
         if partial is not None:
             ctx.mark_non_differentiable(partial)
         return y, partial
 
     @staticmethod
     def backward(ctx, dy, *_unused):
+        if dy is None:
+            return None, None, None, None, None, None
         L = _lib.cuda()
         x, w, packed_bwd = ctx.saved_tensors
         stride, pad, has_bias = ctx.geom

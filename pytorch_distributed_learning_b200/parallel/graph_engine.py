@@ -27,10 +27,13 @@ class GenericGraphEngine:
         return tuple(tuple(g.get(k) for k in keys) for g in self.optimizer.param_groups)
 
     def _eager_step(self, x, y):
-        out = self.model(x)
-        loss = self.criterion(out, y)
-        self.optimizer.zero_grad(set_to_none=True)
-        loss.backward()
+        from ..ops import tc_conv
+
+        with tc_conv.prepacked(self.model):  # one launch packs every conv weight for the tensor cores (fwd + dgrad copies)
+            out = self.model(x)
+            loss = self.criterion(out, y)
+            self.optimizer.zero_grad(set_to_none=True)
+            loss.backward()
         self.optimizer.step()
         return loss.detach()
 
