@@ -12,6 +12,7 @@ scripts call ``torch.cuda.set_device`` only AFTER ``init_process_group`` (mpspaw
 from __future__ import annotations
 
 import ctypes
+import weakref
 import os
 import uuid
 
@@ -148,7 +149,11 @@ class B200ProcessGroup(dist.ProcessGroup):
         return seg
 
     def new_comm_state(self):
-        return torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device="cuda:%d" % self._ensure_cuda())
+        st = torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device="cuda:%d" % self._ensure_cuda())
+        if not hasattr(self, "_comm_states"):
+            self._comm_states = []
+        self._comm_states.append(weakref.ref(st))  # every communicator state of this group: checked by check_device_errors()
+        return st
 
     def _stage(self):
         if self._staging is None:
@@ -267,6 +272,7 @@ class B200ProcessGroup(dist.ProcessGroup):
     def barrier(self):
         if self.device_index is not None and self._staging is not None:
             torch.cuda.synchronize(self.device_index)
+            self.check_device_errors()  # a host-side synchronisation point: the cheapest place to notice a dead peer
         self._ctl.barrier()
 
     def device_barrier(self):
@@ -288,12 +294,20 @@ class B200ProcessGroup(dist.ProcessGroup):
             return tensor
         return self._ctl.recv(tensor, src)
 
-    def check_device_errors(self):
-        """Raise if a kernel gave up waiting for a peer (dead or hung rank)."""
-        bad = False
-        if self._staging is not None:
-            state = self._staging["state"]
-            bad = int(state.view(torch.int32)[-1].item()) != 0
+    def check_device_errors(self, raise_on_error=True):
+        """Failure detection for the device-side collectives: every peer wait inside a kernel is bounded
+        (``PDL_KERNEL_TIMEOUT_S``, default 60 s) and a kernel that gives up sets the error word of its communicator state
+        instead of spinning forever (a dead or hung rank must not wedge the GPU).  This reads those words (one small D2H
+        copy per communicator, so it is called at host synchronisation points: ``barrier()``, checkpoints, group
+        destruction, or explicitly) and raises.  The data produced by a timed-out kernel is garbage."""
+        bad = 0
+        for ref in getattr(self, "_comm_states", []):
+            st = ref()
+            if st is not None and int(st.view(torch.int32)[-1].item()) != 0:
+                bad += 1
+        if bad and raise_on_error:
+            raise RuntimeError("[rank %d] %d device communicator(s) of group %r timed out waiting for a peer GPU (PDL_KERNEL_TIMEOUT_S=%gs): "
+                               "a rank died or hung; gradients/parameters of this step are not valid" % (self.rank(), bad, self.name, self.timeout_s))
         return bad
 
     # control plane

@@ -408,6 +408,15 @@ class DistributedDataParallel(nn.Module):
         finally:
             self.require_backward_grad_sync = old
 
+    def check_health(self):
+        """Raise if a bucket kernel of this group gave up waiting for a peer GPU (dead / hung rank); see
+        ``B200ProcessGroup.check_device_errors``.  Costs a device synchronisation: call it where you already synchronise
+        (when you print the loss, before a checkpoint).  No-op on the CPU backend, whose collectives raise by themselves."""
+        check = getattr(self.process_group, "check_device_errors", None)
+        if check is not None and self.device.type == "cuda":
+            torch.cuda.synchronize(self.device)
+            check()
+
     def get_step_stats(self):
         stats = dict(self._stats)
         stats["bucket_bytes"] = self.bucket_sizes_bytes()
