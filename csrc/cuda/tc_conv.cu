@@ -48,6 +48,7 @@ struct EpiArgs {
   const float* pooled;  // EPI_POOL_BWD: the pooled activations (ReLU mask) ...
   float* dbpart;        // ... and where the per-tile column sums go; `idx` is then the pool's arg-max, `out` is dz
   float* bn_partial;    // EPI_STORE + tma_store: per-CTA (count, mean, M2) of every output channel, [grid / n_tiles][ldc][3]
+  const float* add_src; // EPI_STORE + tma_store: tensor of the output's shape added to the result (skip-connection gradient)
 };
 
 template <int N_GEMM>
@@ -200,6 +201,15 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (et == 0) tc::bulk_wait_read_all();  // the previous tile's stores have drained the staging buffer
         asm volatile("bar.sync 1, 256;" ::: "memory");
         const float* bias_t = e.bias ? e.bias + nt * N_GEMM + half * HALF : nullptr;
+        // optional second addend with the output's layout (the skip connection's gradient, when this is the dgrad of the
+        // first convolution of a residual block): out = acc + add_src.  Rows past the tensor edge are clipped by the store
+        // and must not be read here.
+        const float* add_row = nullptr;
+        if (e.add_src) {
+          const int bw_ = row % g.BW, t2_ = row / g.BW, bh_ = t2_ % g.BH, bn_ = t2_ / g.BH;
+          if (row < rows && (n0 + bn_) < g.Nimg && (h0 + bh_) < g.Hc)
+            add_row = e.add_src + ((static_cast<long long>(n0 + bn_) * g.Hout + h0 + bh_) * g.Wout + bw_) * g.ldc + nt * N_GEMM + half * HALF;
+        }
 #pragma unroll 1
         for (int c = 0; c < HALF; c += CH) {
           float v[CH];
@@ -211,6 +221,10 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int j = 0; j < CH; j += 4) {
             const float4 bb = bias_t ? *reinterpret_cast<const float4*>(bias_t + c + j) : make_float4(0.f, 0.f, 0.f, 0.f);
             float4 o = make_float4(v[j] + bb.x, v[j + 1] + bb.y, v[j + 2] + bb.z, v[j + 3] + bb.w);
+            if (add_row) {
+              const float4 aa = __ldg(reinterpret_cast<const float4*>(add_row + c + j));
+              o.x += aa.x; o.y += aa.y; o.z += aa.z; o.w += aa.w;
+            }
             if (e.relu) { o.x = fmaxf(o.x, 0.f); o.y = fmaxf(o.y, 0.f); o.z = fmaxf(o.z, 0.f); o.w = fmaxf(o.w, 0.f); }
             *reinterpret_cast<float4*>(dst_row + (((j0 + j / 4) ^ (row & 7)) << 4)) = o;
           }
@@ -662,8 +676,21 @@ PDL_API int pdl_tc_conv2d_fwd_strided(const float* x, const float* packed_w, con
 // dgrad for convolution stride 1 or 2.  Stride 2 is solved as four stride-1 problems, one per parity class
 // (h % 2, w % 2) of dx: only the taps with matching parity reach a class, the class is a dense sub-grid of dx,
 // and its outputs are written with a stride of 2.  Classes no tap reaches (1x1 filters) stay zero.
+static int dgrad_impl(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride,
+                      int pad, int* error_flag, cudaStream_t stream, const float* add_src);
 PDL_API int pdl_tc_conv2d_dgrad_strided(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH,
                                         int KW, int stride, int pad, int* error_flag, cudaStream_t stream) {
+  return dgrad_impl(dy, packed_w_bwd, dx, N, H, W, Cin, Cout, KH, KW, stride, pad, error_flag, stream, nullptr);
+}
+// dx = dgrad(dy, w) + add_src (stride 1): the skip connection's gradient joins in the epilogue instead of a separate
+// element-wise pass over two full tensors.  Returns -5 if the TMA-store epilogue is disabled (caller adds separately).
+PDL_API int pdl_tc_conv2d_dgrad_add(const float* dy, const float* packed_w_bwd, const float* add_src, float* dx, int N, int H, int W, int Cin,
+                                    int Cout, int KH, int KW, int pad, int* error_flag, cudaStream_t stream) {
+  if (!use_tma_store()) { pdl_set_error("tc_conv dgrad+add needs the TMA-store epilogue"); return -5; }
+  return dgrad_impl(dy, packed_w_bwd, dx, N, H, W, Cin, Cout, KH, KW, 1, pad, error_flag, stream, add_src);
+}
+static int dgrad_impl(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride,
+                      int pad, int* error_flag, cudaStream_t stream, const float* add_src) {
   if (stride != 1 && stride != 2) { pdl_set_error("tc_conv dgrad: stride %d is not supported", stride); return -3; }
   const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
   const int ng = n_gemm_for(Cin);
@@ -698,7 +725,7 @@ PDL_API int pdl_tc_conv2d_dgrad_strided(const float* dy, const float* packed_w_b
       const int tma_store = stride == 1 && use_tma_store();  // parity classes scatter with a stride: direct stores
       CUtensorMap to = ta;
       if (tma_store) { if (int rc = make_out_map(&to, dx, N, H, W, Cin, g.BW, g.BH, g.BN)) return rc; }
-      EpiArgs e{dx, nullptr, nullptr, 0, 0, tma_store, error_flag, g_trace};
+      EpiArgs e{dx, nullptr, nullptr, 0, 0, tma_store, error_flag, g_trace, nullptr, nullptr, nullptr, tma_store ? add_src : nullptr};
       if (int rc = dispatch_n<EPI_STORE>(ng, ta, tb, to, g, e, stream)) return rc;
     }
   return 0;

@@ -107,6 +107,10 @@ long long pdl_tc_wgrad_scratch_bytes_strided(int N, int H, int W, int Cin, int C
 int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch,
                                 int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int* error_flag,
                                 cudaStream_t stream); /* stride 1 or 2 */
+/* dx = dgrad(dy, w) + add_src, stride 1: the skip connection's gradient of a residual block is added in the epilogue of
+ * the block's first convolution (returns -5 when the TMA-store epilogue is switched off) */
+int pdl_tc_conv2d_dgrad_add(const float* dy, const float* packed_w_bwd, const float* add_src, float* dx, int N, int H, int W, int Cin, int Cout,
+                            int KH, int KW, int pad, int* error_flag, cudaStream_t stream);
 /* Bias-free forward that also leaves the BatchNorm statistics of its output in bn_partial ([splits][Cout][3] floats:
  * count, mean, M2 per CTA group; splits = pdl_tc_conv_bn_splits(...), 0 = shape not covered): the epilogue reduces
  * the staged output tile, so the following BatchNorm (pdl_bn_fwd_train_prestats) does not re-read the tensor. */

@@ -59,6 +59,7 @@ def declare(L):
     sig("pdl_tc_wgrad_scratch_bytes_strided", [I, I, I, I, I, I, I, I, I], LL)
     sig("pdl_tc_conv2d_wgrad_strided", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv2d_wgrad", [P, P, P, P, P, I, P, I, I, I, I, I, I, I, I, P, P])
+    sig("pdl_tc_conv2d_dgrad_add", [P, P, P, P, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv_bn_splits", [I, I, I, I, I, I, I, I, I])
     sig("pdl_tc_conv2d_fwd_bnstats", [P, P, P, P, I, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_stem_bn_splits", [I, I, I, I, I, I, I, I, I])

@@ -10,6 +10,8 @@ ones/zeros for batch-norm).
 """
 from __future__ import annotations
 
+import os
+
 from .. import nn
 
 
@@ -26,6 +28,18 @@ def _conv_bn(conv, bn, x, relu=False, residual=None):
     normalisation statistics (``bn_stats=True`` is a hint, ignored where it does not apply), and the normalisation,
     skip connection and activation are one pass over the tensor."""
     return bn(conv(x, bn_stats=True), relu=relu, residual=residual)
+
+
+def _open_block(conv, bn, x):
+    """First conv+bn+relu of an identity block, and the skip connection.  With PDL_SKIP_VIA_CONV=1 the skip is routed
+    through the convolution's autograd node, so that in backward its gradient is added in that convolution's dgrad
+    epilogue instead of by autograd's separate pass over two full tensors.  Measured on B200 (ResNet-50, batch 64):
+    13.32 ms/step with the fused addend vs 13.08 ms with autograd's add -- the per-lane reads of the addend lengthen the
+    epilogue of exactly the kernels that are epilogue-bound -- so it stays opt-in."""
+    if os.environ.get("PDL_SKIP_VIA_CONV", "0") == "1":
+        y, skip = conv(x, bn_stats=True, skip=True)
+        return bn(y, relu=True), skip
+    return bn(conv(x, bn_stats=True), relu=True), x
 
 
 def _downsample(ds, x):
@@ -49,8 +63,11 @@ class BasicBlock(nn.Module):
         self.stride = stride
 
     def forward(self, x):
-        identity = x if self.downsample is None else _downsample(self.downsample, x)
-        out = _conv_bn(self.conv1, self.bn1, x, relu=True)
+        if self.downsample is None:
+            out, identity = _open_block(self.conv1, self.bn1, x)
+        else:
+            identity = _downsample(self.downsample, x)
+            out = _conv_bn(self.conv1, self.bn1, x, relu=True)
         return _conv_bn(self.conv2, self.bn2, out, relu=True, residual=identity)
 
 
@@ -70,8 +87,11 @@ class Bottleneck(nn.Module):
         self.stride = stride
 
     def forward(self, x):
-        identity = x if self.downsample is None else _downsample(self.downsample, x)
-        out = _conv_bn(self.conv1, self.bn1, x, relu=True)
+        if self.downsample is None:
+            out, identity = _open_block(self.conv1, self.bn1, x)
+        else:
+            identity = _downsample(self.downsample, x)
+            out = _conv_bn(self.conv1, self.bn1, x, relu=True)
         out = _conv_bn(self.conv2, self.bn2, out, relu=True)
         return _conv_bn(self.conv3, self.bn3, out, relu=True, residual=identity)
 

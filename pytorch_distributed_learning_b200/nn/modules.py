@@ -24,21 +24,31 @@ def _pair(v):
 class Conv2d(tnn.Conv2d):
     """``conv(x)``.  ``conv(x, bn_stats=True)`` tells the tensor-core kernel that a training-mode ``BatchNorm2d`` consumes
     the result: its epilogue then also reduces the per-channel statistics of the output tile and the result carries them
-    (``_pdl_bn_partial``), so the normalisation layer does not have to re-read the tensor.  A hint, never a requirement."""
+    (``_pdl_bn_partial``), so the normalisation layer does not have to re-read the tensor.  A hint, never a requirement.
+    ``conv(x, skip=True)`` returns ``(y, x_skip)``: ``x_skip`` is x, routed through this layer's autograd node, for use as
+    the residual of the block this convolution opens -- its gradient is then added inside the dgrad kernel."""
 
-    def forward(self, x, bn_stats=False):
+    def forward(self, x, bn_stats=False, skip=False):
         if (_native(x) and self.groups == 1 and _pair(self.dilation) == (1, 1) and self.padding_mode == "zeros"
                 and not isinstance(self.padding, str) and self.stride[0] == self.stride[1] and self.padding[0] == self.padding[1]
                 and self.kernel_size[0] == self.kernel_size[1]):
             from ..ops import functional as NF
 
-            if bn_stats and self.bias is None and torch.is_grad_enabled():
+            want_stats = bn_stats and self.bias is None and torch.is_grad_enabled()
+            if skip and torch.is_grad_enabled() and x.requires_grad:
+                y, partial, x_skip = NF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0], bn_stats=want_stats, with_skip=True)
+                if partial is not None:
+                    y._pdl_bn_partial = partial
+                return y, x_skip
+            if want_stats:
                 y, partial = NF.conv2d(x, self.weight, None, self.stride[0], self.padding[0], bn_stats=True)
                 if partial is not None:
                     y._pdl_bn_partial = partial
-                return y
-            return NF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0])
-        return super().forward(x)
+                return (y, x) if skip else y
+            y = NF.conv2d(x, self.weight, self.bias, self.stride[0], self.padding[0])
+            return (y, x) if skip else y
+        y = super().forward(x)
+        return (y, x) if skip else y
 
 
 class ReLU(tnn.ReLU):

@@ -52,10 +52,14 @@ def conv_out(h, k, s, p):
 
 class _Conv2d(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, w, b, stride, pad, bn_stats=False):
+    def forward(ctx, x, w, b, stride, pad, bn_stats=False, with_skip=False):
         """``bn_stats``: also return the per-channel statistics partials of y ([splits][Cout][3], or None when the
-        tensor-core kernel does not cover the shape) for the BatchNorm that follows."""
+        tensor-core kernel does not cover the shape) for the BatchNorm that follows.  ``with_skip``: also return the
+        input itself as a third output -- the residual block's skip connection.  Routing the skip through this node
+        means its gradient arrives here together with dy, and the dgrad kernel adds it in its epilogue instead of
+        autograd summing two full tensors afterwards."""
         L = _lib.cuda()
+        x_in = x
         w = w.contiguous()
         N, Cin, H, W = x.shape
         Cout, _, KH, KW = w.shape
@@ -77,17 +81,19 @@ class _Conv2d(torch.autograd.Function):
             if not handled:
                 _ok(L.pdl_conv2d_fwd_simt(_p(x), _p(w), _p(b), _p(y), N, H, W, Cin, Cout, KH, KW, stride, pad, 0, _stream(x)), "conv2d forward")
             ctx.save_for_backward(x, w, packed_bwd)
-        if not bn_stats:
+        if not bn_stats and not with_skip:
             return y
-        ctx.set_materialize_grads(False)  # no zero-filled "gradient" tensor for the statistics output
+        ctx.set_materialize_grads(False)  # no zero-filled "gradient" tensors for outputs nobody differentiates
         if partial is not None:
             ctx.mark_non_differentiable(partial)
+        if with_skip:
+            return y, partial, x_in.view_as(x_in)
         return y, partial
 
     @staticmethod
-    def backward(ctx, dy, *_unused):
+    def backward(ctx, dy, _dpartial=None, dskip=None):
         if dy is None:
-            return None, None, None, None, None, None
+            return dskip, None, None, None, None, None, None
         L = _lib.cuda()
         x, w, packed_bwd = ctx.saved_tensors
         stride, pad, has_bias = ctx.geom
@@ -99,8 +105,13 @@ class _Conv2d(torch.autograd.Function):
 
         if ctx.needs_input_grad[0]:
             dx = torch.empty(ctx.x_shape, dtype=dy.dtype, device=dy.device, memory_format=_CL)
-            if not tc_conv.conv2d_dgrad(dy, w, dx, stride, pad, packed_bwd):
+            done = tc_conv.conv2d_dgrad(dy, w, dx, stride, pad, packed_bwd, add=dskip)
+            if not done:
                 _ok(L.pdl_conv2d_dgrad_simt(_p(dy), _p(w), _p(dx), N, H, W, Cin, Cout, KH, KW, stride, pad, _stream(dy)), "conv2d dgrad")
+            if dskip is not None and done is not True:
+                dx += dskip  # the kernel that ran has no fused addend
+        elif dskip is not None:
+            dx = dskip
         if ctx.stem and (ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2])):
             dw = torch.empty_like(w)
             tc_conv.stem_wgrad(x, dy, dw, ctx.x_shape, stride, pad)  # x is the padded NHWC4 copy here
@@ -112,11 +123,13 @@ class _Conv2d(torch.autograd.Function):
                 nbytes = L.pdl_conv2d_wgrad_scratch_bytes(N, H, W, Cin, Cout, KH, KW, stride, pad)
                 sc = scratch(nbytes, x.device, "wgrad")
                 _ok(L.pdl_conv2d_wgrad_simt(_p(x), _p(dy), _p(dw), _p(db), _p(sc), N, H, W, Cin, Cout, KH, KW, stride, pad, _stream(x)), "conv2d wgrad")
-        return dx, dw, db, None, None, None
+        return dx, dw, db, None, None, None, None
 
 
-def conv2d(x, w, b=None, stride=1, padding=0, bn_stats=False):
-    """``bn_stats=True`` returns ``(y, partial)``; see ``_Conv2d.forward``."""
+def conv2d(x, w, b=None, stride=1, padding=0, bn_stats=False, with_skip=False):
+    """``bn_stats=True`` returns ``(y, partial)``, ``with_skip=True`` returns ``(y, partial, skip)``; see ``_Conv2d.forward``."""
+    if with_skip:
+        return _Conv2d.apply(x, w, b, int(stride), int(padding), bool(bn_stats), True)
     if bn_stats:
         return _Conv2d.apply(x, w, b, int(stride), int(padding), True)
     return _Conv2d.apply(x, w, b, int(stride), int(padding))

@@ -218,16 +218,26 @@ def conv2d_fwd_relu_pool(x, w, b, pool_stride):
     return y, idx
 
 
-def conv2d_dgrad(dy, w, dx, stride, pad, packed=None):
+def conv2d_dgrad(dy, w, dx, stride, pad, packed=None, add=None):
+    """dx = dgrad(dy, w) [+ add].  Returns False when the tensor cores do not cover the shape, True when dx is complete,
+    and "no-add" when dx was written WITHOUT the addend (the caller adds it)."""
     N, Cin, H, W = dx.shape
     Cout, _, KH, KW = w.shape
     if not enabled() or not dgrad_supported(Cin, Cout, W, stride):
         return False
     if packed is None:
         _, packed = pack_weights(w, False, True)
+    if add is not None and stride == 1 and add.shape == dx.shape and add.is_contiguous(memory_format=torch.channels_last) \
+            and os.environ.get("PDL_FUSE_SKIP_ADD", "1") != "0":
+        rc = _lib.cuda().pdl_tc_conv2d_dgrad_add(_p(dy), _p(packed), _p(add), _p(dx), N, H, W, Cin, Cout, KH, KW, pad,
+                                                 _p(error_flag(dx.device)), _stream(dx))
+        if rc == 0:
+            return True
+        if rc != -5:
+            _ok(rc, "tensor-core conv dgrad + skip gradient")
     _ok(_lib.cuda().pdl_tc_conv2d_dgrad_strided(_p(dy), _p(packed), _p(dx), N, H, W, Cin, Cout, KH, KW, stride, pad,
                                                 _p(error_flag(dx.device)), _stream(dx)), "tensor-core conv dgrad")
-    return True
+    return True if add is None else "no-add"
 
 
 def conv2d_wgrad(x, dy, dw, db, stride, pad):
