@@ -548,6 +548,8 @@ PDL_API void pdl_tc_set_trace(long long* buf) { g_trace = buf; }
 // 1 if the tensor-core forward path covers this shape (stride 1, Cin % 32 == 0, Cout in {32,64,128}).
 static int n_gemm_for(int channels) {  // widest supported column tile dividing `channels`, 0 if none
   if (channels == 32 || channels == 64) return channels;
+  static const int forced = getenv("PDL_TC_NGEMM") ? atoi(getenv("PDL_TC_NGEMM")) : 0;  // experiment knob (64 | 128)
+  if (forced == 64 && channels % 64 == 0) return 64;
   return channels % 128 == 0 ? 128 : 0;
 }
 
