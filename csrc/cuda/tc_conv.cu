@@ -55,8 +55,11 @@ template <int N_GEMM>
 struct Smem {
   static constexpr int B_BYTES = N_GEMM * 128;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = N_GEMM == 128 ? 4 : (N_GEMM == 64 ? 6 : 8);  // what fits next to the staging tile
-  static constexpr int STAGING_LD = N_GEMM + 4;
+  // what fits next to the staging tile.  N = 256 (48 KB stages) exists because these kernels are bound by aggregate L2
+  // traffic: one A tile then serves twice the columns (24 KB per 128x128x32 of MACs instead of 32 KB).
+  static constexpr int STAGES = N_GEMM == 256 ? 3 : N_GEMM == 128 ? 4 : (N_GEMM == 64 ? 6 : 8);
+  static constexpr int PASS_N = N_GEMM > 128 ? 128 : N_GEMM;  // columns the epilogue stages (and stores) at a time
+  static constexpr int STAGING_LD = PASS_N + 4;
   static constexpr int STAGING_BYTES = 128 * STAGING_LD * 4;
   static constexpr int BAR_OFFSET = STAGES * STAGE_BYTES + STAGING_BYTES;
   static constexpr int TOTAL = BAR_OFFSET + 256 + 512 + 512 + 1024;  // + barriers + bias row + pool table + alignment slack
@@ -104,7 +107,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int PH = (g.BH - 2) / ps + 1, PW = (g.BW - 2) / ps + 1;
   if (threadIdx.x >= 128) {
     const int t = threadIdx.x - 128;
-    if (t < N_GEMM) sbias[t] = e.bias ? e.bias[t] : 0.f;
+    if (EPI == EPI_RELU_POOL && t < N_GEMM) sbias[t] = e.bias ? e.bias[t] : 0.f;
     if (EPI == EPI_RELU_POOL && t < g.BN * PH * PW) {
       const int img = t / (PH * PW), pp = t % (PH * PW);
       pool_row[t] = (img * g.BH + (pp / PW) * ps) * g.BW + (pp % PW) * ps;
@@ -181,11 +184,14 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     const int et = threadIdx.x - 128;           // 0..255
     const int ew = warp - 4, quarter = ew & 3, half = ew >> 2;
     const int row = quarter * 32 + lane;        // accumulator row = output pixel of the tile
-    constexpr int HALF = N_GEMM / 2;            // columns per warp
+    constexpr int PN = SM::PASS_N, NPASS = N_GEMM / PN;  // the epilogue handles PN columns at a time (two passes for N = 256)
+    constexpr int HALF = PN / 2;                // columns per warp (per pass)
     constexpr int CH = HALF < 32 ? HALF : 32;   // columns per TMEM load
     int acc = 0;
     uint32_t acc_phase = 0;
-    float bn_sum = 0.f, bn_sq = 0.f;  // fused BatchNorm statistics (see e.bn_partial)
+    float bn_sum[NPASS], bn_sq[NPASS];  // fused BatchNorm statistics (see e.bn_partial)
+#pragma unroll
+    for (int p = 0; p < NPASS; ++p) { bn_sum[p] = 0.f; bn_sq[p] = 0.f; }
     int bn_count = 0;
     for (int tile = blockIdx.x; tile < g.num_tiles; tile += gridDim.x) {
       if (*failed || !tc::mbar_wait(&tfull[acc], acc_phase)) { *failed = 1; break; }
@@ -196,11 +202,15 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const int h0 = g.BN > 1 ? 0 : (mt % g.tiles_per_img) * g.BH;
       const uint32_t t_row = tmem_base + acc * N_GEMM + half * HALF + (static_cast<uint32_t>(quarter * 32) << 16);
       if (EPI == EPI_STORE && e.tma_store) {
-        // registers -> swizzled staging tile (one [128 rows][128 B] block per 32 channels) -> one TMA store per block.
-        // The store clips rows / images past the tensor edge, so no per-row predicate is needed.
-        if (et == 0) tc::bulk_wait_read_all();  // the previous tile's stores have drained the staging buffer
+       // registers -> swizzled staging tile (one [128 rows][128 B] block per 32 channels) -> one TMA store per block.
+       // The store clips rows / images past the tensor edge, so no per-row predicate is needed.
+#pragma unroll
+       for (int pass = 0; pass < NPASS; ++pass) {
+        const int pc0 = nt * N_GEMM + pass * PN;  // first output channel of this pass
+        const uint32_t t_row = tmem_base + acc * N_GEMM + pass * PN + half * HALF + (static_cast<uint32_t>(quarter * 32) << 16);
+        if (et == 0) tc::bulk_wait_read_all();  // the previous stores have drained the staging buffer
         asm volatile("bar.sync 1, 256;" ::: "memory");
-        const float* bias_t = e.bias ? e.bias + nt * N_GEMM + half * HALF : nullptr;
+        const float* bias_t = e.bias ? e.bias + pc0 + half * HALF : nullptr;
         // optional second addend with the output's layout (the skip connection's gradient, when this is the dgrad of the
         // first convolution of a residual block): out = acc + add_src.  Rows past the tensor edge are clipped by the store
         // and must not be read here.
@@ -208,7 +218,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (e.add_src) {
           const int bw_ = row % g.BW, t2_ = row / g.BW, bh_ = t2_ % g.BH, bn_ = t2_ / g.BH;
           if (row < rows && (n0 + bn_) < g.Nimg && (h0 + bh_) < g.Hc)
-            add_row = e.add_src + ((static_cast<long long>(n0 + bn_) * g.Hout + h0 + bh_) * g.Wout + bw_) * g.ldc + nt * N_GEMM + half * HALF;
+            add_row = e.add_src + ((static_cast<long long>(n0 + bn_) * g.Hout + h0 + bh_) * g.Wout + bw_) * g.ldc + pc0 + half * HALF;
         }
 #pragma unroll 1
         for (int c = 0; c < HALF; c += CH) {
@@ -229,15 +239,17 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             *reinterpret_cast<float4*>(dst_row + (((j0 + j / 4) ^ (row & 7)) << 4)) = o;
           }
         }
-        tc::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) tc::mbar_arrive(&tempty[acc]);  // accumulator drained: the next tile's MMAs may start
+        if (pass == NPASS - 1) {
+          tc::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(&tempty[acc]);  // accumulator drained: the next tile's MMAs may start
+        }
         tc::fence_proxy_async_smem();
         asm volatile("bar.sync 1, 256;" ::: "memory");
         if (et == 0) {
 #pragma unroll
-          for (int cc = 0; cc < N_GEMM / 32; ++cc)
-            tc::tma_store_4d(&tmOut, reinterpret_cast<uint8_t*>(staging) + cc * A_BYTES, nt * N_GEMM + cc * 32, 0, h0, n0);
+          for (int cc = 0; cc < PN / 32; ++cc)
+            tc::tma_store_4d(&tmOut, reinterpret_cast<uint8_t*>(staging) + cc * A_BYTES, pc0 + cc * 32, 0, h0, n0);
           tc::bulk_commit();
         }
         if (e.bn_partial) {
@@ -247,20 +259,24 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           // in the output count: a ragged last strip / a last tile with fewer images still computes the rows past the
           // tensor edge (from the halo of valid input), the TMA store merely clips them.  Rows are ordered image, row,
           // column, so the valid ones are a prefix of the tile.
-          constexpr int PARTS = 256 / N_GEMM;
-          const int col = et % N_GEMM, part = et / N_GEMM;
+          constexpr int PARTS = 256 / PN;
+          const int col = et % PN, part = et / PN;
           const uint8_t* src = reinterpret_cast<const uint8_t*>(staging) + (col / 32) * A_BYTES + (col % 4) * 4;
           const int piece = (col % 32) / 4;
           const int vh = min(g.BH, g.Hc - h0), vn = min(g.BN, g.Nimg - n0);
           const int valid_rows = g.BW * (vh > 0 ? vh : 0) * (vn > 0 ? vn : 0);
+          float s_ = 0.f, q_ = 0.f;
 #pragma unroll 4
           for (int r = part; r < valid_rows; r += PARTS) {
             const float v = *reinterpret_cast<const float*>(src + r * 128 + ((piece ^ (r & 7)) << 4));
-            bn_sum += v;
-            bn_sq = fmaf(v, v, bn_sq);
+            s_ += v;
+            q_ = fmaf(v, v, q_);
           }
-          bn_count += valid_rows;
+          bn_sum[pass] += s_;
+          bn_sq[pass] += q_;
+          if (pass == 0) bn_count += valid_rows;
         }
+       }  // pass
       } else if (EPI == EPI_STORE) {
         const int bw = row % g.BW, t2 = row / g.BW, bh = t2 % g.BH, bn = t2 / g.BH;
         // output pixel of this row: the tile grid (Hc x BW) is the full image, or one parity class of it (strided dgrad)
@@ -396,21 +412,24 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (EPI == EPI_STORE && e.tma_store && et == 0) tc::bulk_wait_read_all();  // smem must outlive the last store's reads
     if (EPI == EPI_STORE && e.tma_store && e.bn_partial) {
       // this CTA's (count, mean, M2) per column -> bn_partial[split][C][3], split = blockIdx.x / n_tiles
-      constexpr int PARTS = 256 / N_GEMM;
-      asm volatile("bar.sync 1, 256;" ::: "memory");  // all stores drained, staging is free
-      const int col = et % N_GEMM, part = et / N_GEMM;
-      staging[(part * 2 + 0) * N_GEMM + col] = bn_sum;
-      staging[(part * 2 + 1) * N_GEMM + col] = bn_sq;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      if (et < N_GEMM) {
-        float s = 0.f, q = 0.f;
+      constexpr int PARTS = 256 / PN;
+      const int col = et % PN, part = et / PN;
 #pragma unroll
-        for (int p = 0; p < PARTS; ++p) { s += staging[(p * 2) * N_GEMM + et]; q += staging[(p * 2 + 1) * N_GEMM + et]; }  // fixed order
-        const float n = static_cast<float>(bn_count);
-        const float mean = n > 0.f ? s / n : 0.f;
-        const int nt_mine = blockIdx.x % g.n_tiles;
-        float* o = e.bn_partial + (static_cast<long long>(blockIdx.x / g.n_tiles) * g.ldc + nt_mine * N_GEMM + et) * 3;
-        o[0] = n; o[1] = mean; o[2] = fmaxf(q - s * mean, 0.f);
+      for (int pass = 0; pass < NPASS; ++pass) {
+        asm volatile("bar.sync 1, 256;" ::: "memory");  // all stores drained (or the previous pass read): staging is free
+        staging[(part * 2 + 0) * PN + col] = bn_sum[pass];
+        staging[(part * 2 + 1) * PN + col] = bn_sq[pass];
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (et < PN) {
+          float s = 0.f, q = 0.f;
+#pragma unroll
+          for (int p = 0; p < PARTS; ++p) { s += staging[(p * 2) * PN + et]; q += staging[(p * 2 + 1) * PN + et]; }  // fixed order
+          const float n = static_cast<float>(bn_count);
+          const float mean = n > 0.f ? s / n : 0.f;
+          const int nt_mine = blockIdx.x % g.n_tiles;
+          float* o = e.bn_partial + (static_cast<long long>(blockIdx.x / g.n_tiles) * g.ldc + nt_mine * N_GEMM + pass * PN + et) * 3;
+          o[0] = n; o[1] = mean; o[2] = fmaxf(q - s * mean, 0.f);
+        }
       }
     }
   }
@@ -511,6 +530,12 @@ int dispatch_n(int n_gemm, const CUtensorMap& a, const CUtensorMap& b, const CUt
     case 32: return launch_tc<32, EPI>(a, b, o, g, e, stream);
     case 64: return launch_tc<64, EPI>(a, b, o, g, e, stream);
     case 128: return launch_tc<128, EPI>(a, b, o, g, e, stream);
+    case 256:
+      if constexpr (EPI == EPI_STORE) {
+        if (e.tma_store) return launch_tc<256, EPI_STORE>(a, b, o, g, e, stream);
+      }
+      pdl_set_error("tc_conv: 256-column tiles need the TMA-store epilogue");
+      return -3;
     default: pdl_set_error("tc_conv: unsupported GEMM N %d", n_gemm); return -3;
   }
 }
@@ -546,12 +571,18 @@ static long long* g_trace = nullptr;
 PDL_API void pdl_tc_set_trace(long long* buf) { g_trace = buf; }
 
 // 1 if the tensor-core forward path covers this shape (stride 1, Cin % 32 == 0, Cout in {32,64,128}).
-static int n_gemm_for(int channels) {  // widest supported column tile dividing `channels`, 0 if none
+// `wide`: the launch uses the TMA-store epilogue, which is the only one that handles 256-column tiles (in two passes).
+static int n_gemm_for(int channels, bool wide = false, int m_tiles = 0) {  // column tile for `channels` outputs, 0 if none
   if (channels == 32 || channels == 64) return channels;
-  static const int forced = getenv("PDL_TC_NGEMM") ? atoi(getenv("PDL_TC_NGEMM")) : 0;  // experiment knob (64 | 128)
+  static const int forced = getenv("PDL_TC_NGEMM") ? atoi(getenv("PDL_TC_NGEMM")) : 0;  // experiment knob (64 | 128 | 256)
   if (forced == 64 && channels % 64 == 0) return 64;
+  // 256 columns cut the L2 traffic per MAC by a quarter but halve the number of tiles: measured on ResNet-50's layers
+  // (batch 64) they win from ~96 tiles up (14x14 and larger maps: 0.049 -> 0.040 ms) and lose below (7x7 maps: 0.056 -> 0.069)
+  if (wide && forced != 128 && channels % 256 == 0 && (forced == 256 || static_cast<long long>(m_tiles) * (channels / 256) >= 96)) return 256;
   return channels % 128 == 0 ? 128 : 0;
 }
+// M tiles of a launch whose box was chosen by choose_box
+static int m_tiles_of(const TcGeom& g, int N) { return g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img; }
 
 PDL_API int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool) {
   if ((stride != 1 && stride != 2) || (stride == 2 && pool) || Cin % 32 || !n_gemm_for(Cout) || (pool && Cout > 128)) return 0;
@@ -626,7 +657,7 @@ static int tc_fwd_impl(const float* x, const float* packed_w, const float* bias,
   g.in_stride = stride;
   g.tap_r0 = g.tap_s0 = 0; g.tap_step = 1; g.S_full = KW; g.out_stride = 1; g.out_oh = g.out_ow = 0; g.Hc = P;
   if (!choose_box(P, Q, pool_stride > 0, &g)) { pdl_set_error("tc_conv fwd: no tile for %dx%d output", P, Q); return -4; }
-  const int ng = n_gemm_for(Cout);
+  const int ng = n_gemm_for(Cout, pool_stride == 0 && use_tma_store(), m_tiles_of(g, N));
   if (!ng || Cin % 32 || (pool_stride > 0 && Cout > 128)) { pdl_set_error("tc_conv fwd: unsupported channels %d -> %d", Cin, Cout); return -3; }
   g.n_tiles = Cout / ng; g.ldc = Cout;
   g.num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * g.n_tiles;
@@ -649,8 +680,8 @@ PDL_API int pdl_tc_conv_bn_splits(int N, int H, int W, int Cin, int Cout, int KH
   TcGeom g{};
   const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
   if (!choose_box(P, Q, 0, &g)) return 0;
-  const int n_tiles = Cout / n_gemm_for(Cout);
-  const int num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * n_tiles;
+  const int n_tiles = Cout / n_gemm_for(Cout, true, m_tiles_of(g, N));
+  const int num_tiles = m_tiles_of(g, N) * n_tiles;
   return tc_grid(num_tiles, n_tiles, true) / n_tiles;
 }
 
@@ -695,7 +726,12 @@ static int dgrad_impl(const float* dy, const float* packed_w_bwd, float* dx, int
                       int pad, int* error_flag, cudaStream_t stream, const float* add_src) {
   if (stride != 1 && stride != 2) { pdl_set_error("tc_conv dgrad: stride %d is not supported", stride); return -3; }
   const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
-  const int ng = n_gemm_for(Cin);
+  int m_tiles = 0;
+  {
+    TcGeom g0{};
+    if (stride == 1 && choose_box(H, W, 0, &g0)) m_tiles = m_tiles_of(g0, N);
+  }
+  const int ng = n_gemm_for(Cin, stride == 1 && use_tma_store(), m_tiles);  // parity-class launches (stride 2) store directly
   if (Cout % 32 || !ng) { pdl_set_error("tc_conv dgrad: unsupported channels %d -> %d", Cout, Cin); return -3; }
   CUtensorMap tb;
   if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, ng)) return rc;
