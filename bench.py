@@ -39,6 +39,7 @@ def parse_args():
     p.add_argument("--model", choices=["convnet", "resnet18", "resnet50"], default="convnet")
     p.add_argument("--batch", type=int, default=None, help="per-rank batch (default: 100 ConvNet, 128 ResNet-18, 64 ResNet-50)")
     p.add_argument("--eager", action="store_true", help="ours: run the reference-style eager loop instead of the graphed TrainStep")
+    p.add_argument("--e2e-sync", action="store_true", help="end-to-end loop: block on loss.item() after every step (default: read it one step late)")
     p.add_argument("--algorithm", default=None, help="ours: force an allreduce variant (oneshot|twoshot|ring|nvls)")
     p.add_argument("--local-rank", "--local_rank", type=int, default=None)
     return p.parse_args()
@@ -270,15 +271,32 @@ def main():
     wall_ms = gather_max(wall_ms)
 
     # ---------------- end to end: pinned host batch -> H2D -> step -> loss D2H, every step ----------------
+    # Both arms read every step's loss on the host ONE STEP LATE (step i's value is fetched after step i+1 has been
+    # issued), so neither arm drains the GPU per step; the last value is fetched before the closing event.  Reference:
+    # loss.item() on the previous step's tensor.  Ours: TrainStep.step_async -> PendingLoss (pinned-host ring) with the
+    # batch's H2D copy on a copy stream.  --e2e-sync restores a blocking .item() after every step in both arms.
+    if args.impl == "ours" and not args.e2e_sync:
+        e2e_step = train_step.step_async
+    else:
+        e2e_step = step_fn
     for i in range(3):
-        float(step_fn(host_x[i % pool], host_y[i % pool]).item())
+        float(e2e_step(host_x[i % pool], host_y[i % pool]).item())
     barrier()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     loss_sum = 0.0
+    prev = None
     for i in range(args.steps):
-        loss_sum += float(step_fn(host_x[i % pool], host_y[i % pool]).item())
+        cur = e2e_step(host_x[i % pool], host_y[i % pool])
+        if args.e2e_sync:
+            loss_sum += float(cur.item())
+            continue
+        if prev is not None:
+            loss_sum += float(prev.item())
+        prev = cur
+    if prev is not None:
+        loss_sum += float(prev.item())
     e1.record()
     torch.cuda.synchronize()
     barrier()
@@ -329,7 +347,9 @@ def main():
                        "weights": "random init", "timing": "CUDA events, max over ranks; wall %.3f ms/step" % (wall_ms / args.steps)},
             "clocks": clocks,
             "e2e": {"value": global_batch * args.steps / (e2e_ms / 1e3), "unit": "images/s", "ms_per_step": e2e_ms / args.steps,
-                    "h2d_bytes_per_step": per_batch + batch * 8, "d2h_bytes_per_step": 4, "mean_loss": loss_sum / args.steps},
+                    "h2d_bytes_per_step": per_batch + batch * 8, "d2h_bytes_per_step": 4, "mean_loss": loss_sum / args.steps,
+                    "loss_read": "blocking .item() after every step" if args.e2e_sync else
+                    "every step's loss is read on the host one step late (both arms); all reads inside the timed region"},
             "gpu_launches": int(kernels_per_step * args.steps) if args.impl == "ours" else None,
         }
         if local_ms is not None:

@@ -28,6 +28,7 @@ from . import nn  # noqa: F401
 from . import utils  # noqa: F401
 from . import models  # noqa: F401
 from .parallel.train_step import TrainStep  # noqa: F401
+from .parallel.pipeline import PendingLoss  # noqa: F401
 
 init_process_group = distributed.init_process_group
 destroy_process_group = distributed.destroy_process_group

@@ -129,6 +129,7 @@ class ConvNetEngine:
         self.graphs = {}
         self.kernel_count = 0
         self._branch = torch.cuda.Stream(device=self.device)  # off-critical-path kernels (see _record_tc)
+        self._ring = self._d2h = None  # pinned loss ring + its copy stream, created by the first step(pending=True)
 
     # ------------------------------------------------------------------ buffers + capture
     def _build(self, N):
@@ -178,6 +179,19 @@ class ConvNetEngine:
         with torch.cuda.graph(g):
             entry["kernels"] = self._record(b, N, torch.cuda.current_stream(dev).cuda_stream, reduce=True)
         entry["graph"] = g
+        # Slot 1: the same iteration captured over a second set of input/loss buffers (everything else is shared --
+        # replays are ordered on one stream).  Host batches alternate between the two, so the H2D copy of batch i+1
+        # lands while step i still reads batch i, and the loss of step i can leave for the host while step i+1 runs.
+        b1 = dict(b)
+        b1["x"], b1["y"], b1["loss"] = torch.zeros_like(b["x"]), torch.zeros_like(b["y"]), torch.zeros_like(b["loss"])
+        torch.cuda.synchronize(dev)
+        g1 = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g1):
+            self._record(b1, N, torch.cuda.current_stream(dev).cuda_stream, reduce=True)
+        from ..parallel.pipeline import InputStager
+
+        entry["slots"] = [{"buf": b, "graph": g, "read": None}, {"buf": b1, "graph": g1, "read": None}]
+        entry["stager"] = InputStager(dev, zones=[(b["x"], b["y"]), (b1["x"], b1["y"])])
         return entry
 
     def _record(self, b, N, stream_handle, reduce):
@@ -292,7 +306,9 @@ class ConvNetEngine:
         else:
             self.arena.refresh_hyper(self.group)
 
-    def step(self, images, labels):
+    def step(self, images, labels, pending=False):
+        """One iteration.  Returns the loss as a device scalar, or (``pending=True``) as a ``PendingLoss`` whose value is
+        copied to pinned host memory behind the step.  Host batches are staged through two alternating input slots."""
         N = images.shape[0]
         from . import tc_conv
 
@@ -303,16 +319,36 @@ class ConvNetEngine:
                 raise ValueError("ConvNet expects N x 1 x 28 x 28 inputs, got %s" % (tuple(images.shape),))
             self._refresh_hyper()
             entry = self.graphs[key] = self._build(N)
-        b = entry["buf"]
         self._refresh_hyper()
-        b["x"].view(N, 1, 28, 28).copy_(images, non_blocking=True)
-        b["y"].copy_(labels, non_blocking=True)
-        entry["graph"].replay()
+        main = torch.cuda.current_stream(self.device)
+        stager = entry["stager"]
+        if not images.is_cuda and not labels.is_cuda:
+            _, _, ready, slot = stager.stage(images, labels)  # H2D on the copy stream, overlapping the step in flight
+            main.wait_event(ready)
+        else:
+            slot = 0
+            b0 = entry["buf"]
+            main.wait_event(stager.ready[0])  # a staged copy into this slot, if any, is ordered before this one
+            b0["x"].view(N, 1, 28, 28).copy_(images, non_blocking=True)
+            b0["y"].copy_(labels, non_blocking=True)
+        s = entry["slots"][slot]
+        if s["read"] is not None:  # this slot's previous loss must have left for the host before it is overwritten
+            main.wait_event(s["read"])
+            s["read"] = None
+        s["graph"].replay()
+        stager.consumed(slot, main)
         self.kernel_count = entry["kernels"]
         self.last_key = key
         if self.ddp is not None:
             self.ddp._iteration += 1
-        return b["loss"]
+        if pending:
+            if self._ring is None:
+                from ..parallel.pipeline import LossRing
+
+                self._ring, self._d2h = LossRing(self.device), torch.cuda.Stream(device=self.device)
+            handle, s["read"] = self._ring.publish(s["buf"]["loss"], self._d2h, after=stager.free[slot])
+            return handle
+        return s["buf"]["loss"]
 
     def kernels_per_step(self):
         return self.kernel_count

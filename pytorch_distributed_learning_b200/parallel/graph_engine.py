@@ -20,6 +20,7 @@ class GenericGraphEngine:
         self.device = next(model.parameters()).device
         self.graphs = {}
         self._kernel_count = 0
+        self._ring = None  # pinned loss ring, created by the first step(pending=True)
 
     # -- helpers ---------------------------------------------------------------------------
     def _hyper_signature(self):
@@ -93,7 +94,10 @@ class GenericGraphEngine:
         self._kernel_count = int(L.pdl_launch_count() - before)  # launcher calls of this library inside one iteration
         return {"graph": g, "x": x, "y": y, "loss": loss, "hyper": self._hyper_signature()}
 
-    def step(self, images, labels):
+    def step(self, images, labels, pending=False):
+        """One iteration.  A host batch crosses PCIe on a copy stream into one of two staging buffers while the previous
+        step computes; the graph's input is then refreshed by a device-to-device copy (38 MB for 64 ImageNet-sized images:
+        ~25 us at HBM speed instead of ~0.7 ms of PCIe on the critical path).  ``pending=True`` returns a ``PendingLoss``."""
         key = (tuple(images.shape), images.dtype, tuple(labels.shape), labels.dtype)
         entry = self.graphs.get(key)
         if entry is not None and entry["hyper"] != self._hyper_signature() and not self._all_fused():
@@ -101,11 +105,30 @@ class GenericGraphEngine:
         if entry is None:
             entry = self.graphs[key] = self._build(images, labels)
         self._refresh_fused_hyper()
-        entry["x"].copy_(images, non_blocking=True)
-        entry["y"].copy_(labels, non_blocking=True)
+        if not images.is_cuda and not labels.is_cuda:
+            from .pipeline import InputStager
+
+            stager = entry.get("stager")
+            if stager is None:
+                stager = entry["stager"] = InputStager(self.device)
+            main = torch.cuda.current_stream(self.device)
+            sx, sy, ready, slot = stager.stage(images, labels)
+            main.wait_event(ready)
+            entry["x"].copy_(sx, non_blocking=True)
+            entry["y"].copy_(sy, non_blocking=True)
+            stager.consumed(slot, main)
+        else:
+            entry["x"].copy_(images, non_blocking=True)
+            entry["y"].copy_(labels, non_blocking=True)
         entry["graph"].replay()
         if hasattr(self.model, "_iteration"):
             self.model._iteration += 1
+        if pending:
+            if self._ring is None:
+                from .pipeline import LossRing
+
+                self._ring = LossRing(self.device)
+            return self._ring.publish(entry["loss"], torch.cuda.current_stream(self.device))[0]
         return entry["loss"]
 
     def _all_fused(self):

@@ -23,6 +23,7 @@ class TrainStep:
     def __init__(self, model, criterion, optimizer, use_graph=True):
         self.model, self.criterion, self.optimizer = model, criterion, optimizer
         self.engine = None
+        self._ring = None
         if use_graph:
             self.engine = self._try_native_engine()
 
@@ -51,6 +52,30 @@ class TrainStep:
         if self.engine is not None:
             return self.engine.step(images, labels)
         return self._eager(images, labels)
+
+    def step_async(self, images, labels):
+        """Like ``step(images, labels)`` but returns a ``PendingLoss``: the scalar is copied to pinned host memory right
+        behind the step, and ``.item()`` / ``float()`` waits for that copy only.  Read it one step late --
+
+            pending = None
+            for images, labels in loader:            # pinned host batches
+                cur = step.step_async(images, labels)
+                if pending is not None: log(pending.item())
+                pending = cur
+
+        -- and neither the next batch's H2D copy nor the loss read-back ever leaves the GPU idle (the reference's loop
+        reads ``loss.item()`` every 100th step for the same reason, launch_dist.py:93-99).  A handle stays valid for
+        ``LossRing.DEPTH`` further steps."""
+        if self.engine is not None:
+            return self.engine.step(images, labels, pending=True)
+        loss = self._eager(images, labels)
+        if not loss.is_cuda:
+            return loss  # CPU training: the value is already on the host; .item() works the same way
+        if self._ring is None:
+            from .pipeline import LossRing
+
+            self._ring = LossRing(loss.device)
+        return self._ring.publish(loss, torch.cuda.current_stream(loss.device))[0]
 
     def _eager(self, images, labels):
         dev = next(self.model.parameters()).device

@@ -1,0 +1,72 @@
+"""TrainStep.step_async: host batches staged on a copy stream through two alternating input slots and the loss read
+back through a pinned ring must train exactly like the blocking path (same kernels, same order -> same numbers)."""
+import copy
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import pytorch_distributed_learning_b200 as pdl  # noqa: E402
+
+
+def _batches(n, shape, classes, batch):
+    g = torch.Generator().manual_seed(7)
+    xs = [torch.randn((batch,) + shape, generator=g).pin_memory() for _ in range(n)]
+    ys = [torch.randint(0, classes, (batch,), generator=g).pin_memory() for _ in range(n)]
+    return xs, ys
+
+
+def _twin_steps(make_model, opt_kw):
+    dev = torch.device("cuda", 0)
+    torch.manual_seed(11)
+    a = make_model().to(dev)
+    b = copy.deepcopy(a)
+    crit = pdl.nn.CrossEntropyLoss()
+    sa = pdl.TrainStep(a, crit, pdl.optim.SGD(a.parameters(), **opt_kw))
+    sb = pdl.TrainStep(b, crit, pdl.optim.SGD(b.parameters(), **opt_kw))
+    return a, b, sa, sb
+
+
+@pytest.mark.parametrize("which", ["convnet", "generic"])
+def test_step_async_matches_blocking_steps(which):
+    dev = torch.device("cuda", 0)
+    if which == "convnet":
+        make, shape, batch, kw, tol = pdl.models.ConvNet, (1, 28, 28), 24, dict(lr=0.05), 1e-6
+    else:
+        make, shape, batch, kw, tol = (lambda: pdl.models.resnet18(num_classes=10)), (3, 32, 32), 8, dict(lr=0.05, momentum=0.9), 1e-4
+    a, b, sa, sb = _twin_steps(make, kw)
+    xs, ys = _batches(7, shape, 10, batch)
+    want = [float(sb(x.to(dev), y.to(dev)).item()) for x, y in zip(xs, ys)]  # blocking, device-resident inputs
+    got, prev = [], None
+    for x, y in zip(xs, ys):  # read one step late, as a training loop would
+        cur = sa.step_async(x, y)
+        assert isinstance(cur, pdl.PendingLoss)
+        if prev is not None:
+            got.append(prev.item())
+        prev = cur
+    got.append(float(prev))
+    assert prev.ready()
+    assert got == pytest.approx(want, rel=tol, abs=tol), (got, want)
+    for (n, p), (_, q) in zip(a.named_parameters(), b.named_parameters()):
+        assert torch.allclose(p, q, rtol=tol, atol=tol), n
+    # the two entry points can be mixed: a blocking step on a host batch, then a device batch, land on the same numbers
+    la = float(sa(xs[0], ys[0]).item())
+    lb = float(sb(xs[0].to(dev), ys[0].to(dev)).item())
+    assert la == pytest.approx(lb, rel=tol)
+    la = float(sa(xs[1].to(dev), ys[1].to(dev)).item())
+    lb = float(sb(xs[1], ys[1]).item())
+    assert la == pytest.approx(lb, rel=tol)
+
+
+def test_pending_loss_expires_instead_of_returning_a_later_step():
+    dev = torch.device("cuda", 0)
+    model = pdl.models.ConvNet().to(dev)
+    step = pdl.TrainStep(model, pdl.nn.CrossEntropyLoss(), pdl.optim.SGD(model.parameters(), lr=0.01))
+    xs, ys = _batches(2, (1, 28, 28), 10, 16)
+    first = step.step_async(xs[0], ys[0])
+    depth = first._ring.DEPTH
+    kept = [step.step_async(xs[i % 2], ys[i % 2]) for i in range(depth)]
+    with pytest.raises(RuntimeError, match="expired"):
+        first.item()
+    assert all(torch.isfinite(torch.tensor(h.item())) for h in kept[1:])
