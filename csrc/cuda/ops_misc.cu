@@ -406,3 +406,59 @@ PDL_API int pdl_cross_entropy(const float* logits, const long long* target, int 
   PDL_LAUNCH_CHECK();
   return 0;
 }
+
+// Running training metrics kept on the device (reference example_launch.py:91-93 does argmax / eq / sum / .item() and
+// loss.item() -- two host syncs -- every step; here the step only accumulates and the host reads when it prints).
+// acc[0] += *loss (if loss), acc[1] += #rows whose arg-max (first maximum) equals the label, acc[2] += N.
+// One warp per row; counts are integers carried in doubles, so the atomic adds commute exactly.
+// (v, c) replaces (best, arg)?  Larger value wins, a NaN counts as the maximum (as in torch), ties go to the lower index;
+// index 0x7fffffff marks "nothing seen yet".
+__device__ __forceinline__ bool argmax_beats(float v, int c, float best, int arg) {
+  if (c == 0x7fffffff) return false;
+  if (arg == 0x7fffffff) return true;
+  bool nan_v = v != v, nan_b = best != best;
+  if (nan_v != nan_b) return nan_v;
+  if (nan_v || v == best) return c < arg;
+  return v > best;
+}
+
+__global__ void __launch_bounds__(kThreads) step_metrics_kernel(const float* __restrict__ logits, const long long* __restrict__ target,
+                                                                const float* __restrict__ loss, int N, int C, double* __restrict__ acc) {
+  __shared__ int hits[kThreads / 32];
+  int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  int row = blockIdx.x * (kThreads / 32) + warp;
+  int hit = 0;
+  if (row < N) {
+    const float* r = logits + (size_t)row * C;
+    float best = -INFINITY;
+    int arg = 0x7fffffff;
+    for (int c = lane; c < C; c += 32) {
+      float v = r[c];
+      if (argmax_beats(v, c, best, arg)) { best = v; arg = c; }
+    }
+    for (int o = 16; o; o >>= 1) {
+      float ob = __shfl_xor_sync(0xffffffffu, best, o);
+      int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (argmax_beats(ob, oa, best, arg)) { best = ob; arg = oa; }
+    }
+    hit = (long long)arg == target[row];
+  }
+  if (lane == 0) hits[warp] = hit;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int h = 0;
+    for (int w = 0; w < kThreads / 32; ++w) h += hits[w];
+    if (h) atomicAdd(&acc[1], (double)h);
+    if (blockIdx.x == 0) {
+      if (loss) atomicAdd(&acc[0], (double)*loss);
+      atomicAdd(&acc[2], (double)N);
+    }
+  }
+}
+
+PDL_API int pdl_step_metrics(const float* logits, const long long* target, const float* loss, int N, int C, double* acc, cudaStream_t stream) {
+  if (N <= 0 || C <= 0) return 0;
+  step_metrics_kernel<<<pdl_ceil_div(N, kThreads / 32), kThreads, 0, stream>>>(logits, target, loss, N, C, acc);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}

@@ -95,8 +95,9 @@ def train_resnet(net, criterion, optimizer, loader, device, epochs, is_printer, 
         print("            =======  Training  ======= \n")
     net.train()
     seen = 0
+    metrics = pdl.utils.stats.RunningMetrics(device)  # running loss / accuracy stay on the GPU; read when a line is printed
     for ep in range(1, epochs + 1):
-        train_loss = correct = total = 0
+        metrics.reset()
         loader.sampler.set_epoch(ep)
         for idx, (inputs, targets) in enumerate(loader):
             inputs, targets = inputs.to(device), targets.to(device)
@@ -105,12 +106,11 @@ def train_resnet(net, criterion, optimizer, loader, device, epochs, is_printer, 
             optimizer.zero_grad()
             loss.backward()
             optimizer.step()
-            train_loss += loss.item()
-            total += targets.size(0)
-            correct += torch.eq(outputs.argmax(dim=1), targets).sum().item()
+            metrics.update(outputs, targets, loss)
             if is_printer and ((idx + 1) % 25 == 0 or (idx + 1) == len(loader)):
+                mean_loss, acc, _ = metrics.read()
                 print("   == step: [{:3}/{}] [{}/{}] | loss: {:.3f} | acc: {:6.3f}%".format(
-                    idx + 1, len(loader), ep, epochs, train_loss / (idx + 1), 100.0 * correct / total))
+                    idx + 1, len(loader), ep, epochs, mean_loss, 100.0 * acc))
             seen += 1
             if max_steps and seen >= max_steps:
                 break

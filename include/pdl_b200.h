@@ -195,6 +195,9 @@ int pdl_linear_dgrad(const float* dy, const float* w, float* dx, int M, int N, i
 int pdl_linear_wgrad(const float* x, const float* dy, float* dw, float* db, int M, int N, int K, cudaStream_t stream);
 int pdl_cross_entropy(const float* logits, const long long* target, int N, int C, float* row_loss, float* loss, float* dlogits,
                       const float* grad_scale, cudaStream_t stream);
+/* Running metrics on the device (reference example_launch.py:91-93: argmax/eq/sum/.item() + loss.item() every step):
+ * acc[0] += *loss (skipped if NULL), acc[1] += rows whose arg-max equals the label, acc[2] += N.  No host sync. */
+int pdl_step_metrics(const float* logits, const long long* target, const float* loss, int N, int C, double* acc, cudaStream_t stream);
 
 #ifdef __cplusplus
 }

@@ -353,6 +353,10 @@ class ConvNetEngine:
     def kernels_per_step(self):
         return self.kernel_count
 
+    def outputs(self):
+        """Logits of the most recent step (static buffer: the next step overwrites it)."""
+        return self.graphs[self.last_key]["buf"]["logits"]
+
     def logits(self, N):
         """Logits of the most recent step with batch size N (static buffer)."""
         return self.graphs[(N, self.last_key[1])]["buf"]["logits"]

@@ -20,6 +20,7 @@ class GenericGraphEngine:
         self.device = next(model.parameters()).device
         self.graphs = {}
         self._kernel_count = 0
+        self._out = self._last = None
         self._ring = None  # pinned loss ring, created by the first step(pending=True)
 
     # -- helpers ---------------------------------------------------------------------------
@@ -32,6 +33,7 @@ class GenericGraphEngine:
 
         with tc_conv.prepacked(self.model):  # one launch packs every conv weight for the tensor cores (fwd + dgrad copies)
             out = self.model(x)
+            self._out = out.detach()
             loss = self.criterion(out, y)
             self.optimizer.zero_grad(set_to_none=True)
             loss.backward()
@@ -92,7 +94,7 @@ class GenericGraphEngine:
         with torch.cuda.graph(g):
             loss = self._eager_step(x, y)
         self._kernel_count = int(L.pdl_launch_count() - before)  # launcher calls of this library inside one iteration
-        return {"graph": g, "x": x, "y": y, "loss": loss, "hyper": self._hyper_signature()}
+        return {"graph": g, "x": x, "y": y, "loss": loss, "out": self._out, "hyper": self._hyper_signature()}
 
     def step(self, images, labels, pending=False):
         """One iteration.  A host batch crosses PCIe on a copy stream into one of two staging buffers while the previous
@@ -121,6 +123,7 @@ class GenericGraphEngine:
             entry["x"].copy_(images, non_blocking=True)
             entry["y"].copy_(labels, non_blocking=True)
         entry["graph"].replay()
+        self._last = entry
         if hasattr(self.model, "_iteration"):
             self.model._iteration += 1
         if pending:
@@ -130,6 +133,10 @@ class GenericGraphEngine:
                 self._ring = LossRing(self.device)
             return self._ring.publish(entry["loss"], torch.cuda.current_stream(self.device))[0]
         return entry["loss"]
+
+    def outputs(self):
+        """Model outputs of the most recent step (the graph's static buffer: the next step overwrites it)."""
+        return self._last["out"]
 
     def _all_fused(self):
         buckets = getattr(self.model, "_buckets", None)

@@ -23,7 +23,7 @@ class TrainStep:
     def __init__(self, model, criterion, optimizer, use_graph=True):
         self.model, self.criterion, self.optimizer = model, criterion, optimizer
         self.engine = None
-        self._ring = None
+        self._ring = self._out = None
         if use_graph:
             self.engine = self._try_native_engine()
 
@@ -83,11 +83,19 @@ class TrainStep:
             images = images.to(dev, non_blocking=True)
             labels = labels.to(dev, non_blocking=True)
         out = self.model(images)
+        self._out = out.detach()
         loss = self.criterion(out, labels)
         self.optimizer.zero_grad()
         loss.backward()
         self.optimizer.step()
         return loss.detach()
+
+    def outputs(self):
+        """Model outputs (logits) of the most recent step, for metrics such as ``utils.stats.RunningMetrics``.  Under a
+        graph this is a static buffer that the next step overwrites; consume it (on the same stream) before stepping again."""
+        if self.engine is not None:
+            return self.engine.outputs()
+        return self._out
 
     def kernels_per_step(self):
         return self.engine.kernels_per_step() if self.engine is not None else None
