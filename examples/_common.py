@@ -89,11 +89,12 @@ def train_convnet(model, criterion, optimizer, loader, device, epochs, is_printe
         print("Training complete in: " + str(datetime.now() - start))
 
 
-def train_resnet(net, criterion, optimizer, loader, device, epochs, is_printer, max_steps=None):
+def train_resnet(net, criterion, optimizer, loader, device, epochs, is_printer, max_steps=None, graphed=False):
     """Loop body of the reference's ResNet scripts: running loss / accuracy every 25 steps on global rank 0."""
     if is_printer:
         print("            =======  Training  ======= \n")
     net.train()
+    step_fn = pdl.TrainStep(net, criterion, optimizer) if graphed else None
     seen = 0
     metrics = pdl.utils.stats.RunningMetrics(device)  # running loss / accuracy stay on the GPU; read when a line is printed
     for ep in range(1, epochs + 1):
@@ -101,11 +102,15 @@ def train_resnet(net, criterion, optimizer, loader, device, epochs, is_printer, 
         loader.sampler.set_epoch(ep)
         for idx, (inputs, targets) in enumerate(loader):
             inputs, targets = inputs.to(device), targets.to(device)
-            outputs = net(inputs)
-            loss = criterion(outputs, targets)
-            optimizer.zero_grad()
-            loss.backward()
-            optimizer.step()
+            if step_fn is not None:  # the same iteration replayed as one CUDA graph (captured once per batch shape)
+                loss = step_fn(inputs, targets)
+                outputs = step_fn.outputs()
+            else:
+                outputs = net(inputs)
+                loss = criterion(outputs, targets)
+                optimizer.zero_grad()
+                loss.backward()
+                optimizer.step()
             metrics.update(outputs, targets, loss)
             if is_printer and ((idx + 1) % 25 == 0 or (idx + 1) == len(loader)):
                 mean_loss, acc, _ = metrics.read()

@@ -17,6 +17,7 @@ if __name__ == "__main__":
     ap.add_argument("--local-rank", "--local_rank", type=int, default=None)
     ap.add_argument("--data-root", default=None)
     ap.add_argument("--max-steps", type=int, default=None)
+    ap.add_argument("--graphed", action="store_true", help="run each iteration as one CUDA graph (pdl.TrainStep)")
     args = ap.parse_args()
     rank, local_rank = int(os.environ["RANK"]), int(os.environ["LOCAL_RANK"])
     device = pick_device(rank)
@@ -30,5 +31,5 @@ if __name__ == "__main__":
                                          pin_memory=device.type == "cuda", sampler=sampler)
     criterion = nn.CrossEntropyLoss()
     optimizer = pdl.optim.SGD(net.parameters(), lr=0.01 * 2, momentum=0.9, weight_decay=0.0001, nesterov=True)
-    train_resnet(net, criterion, optimizer, loader, device, EPOCHS, is_printer=(rank == 0), max_steps=args.max_steps)
+    train_resnet(net, criterion, optimizer, loader, device, EPOCHS, is_printer=(rank == 0), max_steps=args.max_steps, graphed=args.graphed)
     dist.destroy_process_group()

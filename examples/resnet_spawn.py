@@ -18,6 +18,7 @@ parser.add_argument("--dist-url", default="tcp://127.0.0.1:12345", type=str, hel
 parser.add_argument("--node_rank", default=0, type=int, help="node rank for distributed training")
 parser.add_argument("--data-root", default=None)
 parser.add_argument("--max-steps", type=int, default=None)
+parser.add_argument("--graphed", action="store_true", help="run each iteration as one CUDA graph (pdl.TrainStep)")
 
 
 def train_worker(local_rank, ngpus_per_node, args):
@@ -34,7 +35,8 @@ def train_worker(local_rank, ngpus_per_node, args):
                                          pin_memory=device.type == "cuda", sampler=sampler)
     criterion = nn.CrossEntropyLoss().to(device)
     optimizer = pdl.optim.SGD(net.parameters(), lr=0.01 * 2, momentum=0.9, weight_decay=0.0001, nesterov=True)
-    train_resnet(net, criterion, optimizer, loader, device, EPOCHS, is_printer=(args.global_rank == 0), max_steps=args.max_steps)
+    train_resnet(net, criterion, optimizer, loader, device, EPOCHS, is_printer=(args.global_rank == 0), max_steps=args.max_steps,
+                 graphed=args.graphed)
     dist.destroy_process_group()
 
 
