@@ -33,6 +33,7 @@ import torch.nn as nn
 from torch.autograd import Variable
 
 from .. import _lib
+from ..utils import tracing as _tracing
 from . import distributed as dist
 
 _MiB = 1024 * 1024
@@ -215,6 +216,12 @@ class DistributedDataParallel(nn.Module):
 
     # ------------------------------------------------------------------ forward
     def forward(self, *inputs, **kwargs):
+        if _tracing.enabled():
+            with _tracing.trace_range("pdl.DistributedDataParallel.forward", iteration=self._iteration):
+                return self._forward(*inputs, **kwargs)
+        return self._forward(*inputs, **kwargs)
+
+    def _forward(self, *inputs, **kwargs):
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             self._maybe_rebuild_buckets()
             self._prepare_for_backward()
@@ -291,6 +298,12 @@ class DistributedDataParallel(nn.Module):
             self._next_bucket += 1
 
     def _launch_bucket(self, bk):
+        if _tracing.enabled():
+            with _tracing.trace_range("pdl.bucket", index=self._buckets.index(bk), params=len(bk.param_ids), fused=bk.fused_group is not None):
+                return self._launch_bucket_impl(bk)
+        return self._launch_bucket_impl(bk)
+
+    def _launch_bucket_impl(self, bk):
         srcs, dsts = [], []
         for i in bk.param_ids:
             g = bk.grads.get(i)

@@ -18,6 +18,8 @@ from __future__ import annotations
 
 import torch
 
+from ..utils import tracing as _tracing
+
 
 class TrainStep:
     def __init__(self, model, criterion, optimizer, use_graph=True):
@@ -49,6 +51,12 @@ class TrainStep:
         return self.engine is not None
 
     def __call__(self, images, labels):
+        if _tracing.enabled():
+            with _tracing.trace_range("pdl.TrainStep", graphed=self.graphed, batch=int(images.shape[0])):
+                return self._step(images, labels)
+        return self._step(images, labels)
+
+    def _step(self, images, labels):
         if self.engine is not None:
             return self.engine.step(images, labels)
         return self._eager(images, labels)

@@ -1,1 +1,1 @@
-from . import checkpoint, data, logging, stats  # noqa: F401
+from . import checkpoint, data, logging, stats, tracing  # noqa: F401

@@ -223,3 +223,19 @@ def comm_hook_worker(rank, world, port, outdir):
         grads.append((torch.cat([p.grad.reshape(-1) for p in a.parameters()]), torch.cat([p.grad.reshape(-1) for p in b.parameters()])))
     torch.save({"grads": grads, "seen": seen, "twice_rejected": twice}, os.path.join(outdir, "r%d.pt" % rank))
     dist.destroy_process_group()
+
+
+def tracing_worker(rank, world, port, outdir):
+    os.environ["PDL_TRACE"] = os.path.join(outdir, "trace")
+    os.environ["RANK"] = str(rank)
+    from pytorch_distributed_learning_b200.utils import tracing
+
+    tracing.reset()
+    _init(rank, world, port)
+    torch.manual_seed(0)
+    ddp = pdl.DistributedDataParallel(ConvNet())
+    step = pdl.TrainStep(ddp, pdl.nn.CrossEntropyLoss(), pdl.optim.SGD(ddp.parameters(), lr=0.01))
+    for _ in range(2):
+        step(torch.randn(4, 1, 28, 28), torch.randint(0, 10, (4,)))
+    tracing.flush()
+    dist.destroy_process_group()
