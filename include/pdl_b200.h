@@ -197,6 +197,8 @@ int pdl_cross_entropy(const float* logits, const long long* target, int N, int C
                       const float* grad_scale, cudaStream_t stream);
 /* Running metrics on the device (reference example_launch.py:91-93: argmax/eq/sum/.item() + loss.item() every step):
  * acc[0] += *loss (skipped if NULL), acc[1] += rows whose arg-max equals the label, acc[2] += N.  No host sync. */
+/* Two device-to-device copies in one launch (a graphed step's images + labels; reference launch_dist.py:82-83). */
+int pdl_copy_pair(void* d0, const void* s0, long long n0, void* d1, const void* s1, long long n1, cudaStream_t stream);
 int pdl_step_metrics(const float* logits, const long long* target, const float* loss, int N, int C, double* acc, cudaStream_t stream);
 
 #ifdef __cplusplus

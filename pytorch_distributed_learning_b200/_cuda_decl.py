@@ -108,6 +108,7 @@ def declare(L):
     sig("pdl_linear_wgrad", [P, P, P, P, I, I, I, P])
     sig("pdl_cross_entropy", [P, P, I, I, P, P, P, P, P])
     sig("pdl_step_metrics", [P, P, P, I, I, P, P])
+    sig("pdl_copy_pair", [P, P, LL, P, P, LL, P])
     for name, args, res in _OPTIONAL:
         if hasattr(L, name):
             sig(name, args, res)

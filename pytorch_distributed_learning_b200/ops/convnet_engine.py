@@ -329,8 +329,9 @@ class ConvNetEngine:
             slot = 0
             b0 = entry["buf"]
             main.wait_event(stager.ready[0])  # a staged copy into this slot, if any, is ordered before this one
-            b0["x"].view(N, 1, 28, 28).copy_(images, non_blocking=True)
-            b0["y"].copy_(labels, non_blocking=True)
+            from ..parallel.pipeline import refresh_inputs
+
+            refresh_inputs(b0["x"], b0["y"], images, labels)
         s = entry["slots"][slot]
         if s["read"] is not None:  # this slot's previous loss must have left for the host before it is overwritten
             main.wait_event(s["read"])

@@ -107,21 +107,19 @@ class GenericGraphEngine:
         if entry is None:
             entry = self.graphs[key] = self._build(images, labels)
         self._refresh_fused_hyper()
-        if not images.is_cuda and not labels.is_cuda:
-            from .pipeline import InputStager
+        from .pipeline import InputStager, refresh_inputs
 
+        if not images.is_cuda and not labels.is_cuda:
             stager = entry.get("stager")
             if stager is None:
                 stager = entry["stager"] = InputStager(self.device)
             main = torch.cuda.current_stream(self.device)
             sx, sy, ready, slot = stager.stage(images, labels)
             main.wait_event(ready)
-            entry["x"].copy_(sx, non_blocking=True)
-            entry["y"].copy_(sy, non_blocking=True)
+            refresh_inputs(entry["x"], entry["y"], sx, sy)
             stager.consumed(slot, main)
         else:
-            entry["x"].copy_(images, non_blocking=True)
-            entry["y"].copy_(labels, non_blocking=True)
+            refresh_inputs(entry["x"], entry["y"], images, labels)
         entry["graph"].replay()
         self._last = entry
         if hasattr(self.model, "_iteration"):

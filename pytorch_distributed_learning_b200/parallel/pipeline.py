@@ -15,6 +15,27 @@ from __future__ import annotations
 import torch
 
 
+def refresh_inputs(x_dst, y_dst, images, labels):
+    """Copy a device-resident batch into a graph's static inputs on the current stream: one kernel for both tensors when
+    they are plain contiguous CUDA tensors of the destination's dtype (two ``copy_`` calls otherwise)."""
+    if (images.is_cuda and labels.is_cuda and images.dtype == x_dst.dtype and labels.dtype == y_dst.dtype
+            and images.is_contiguous() and labels.is_contiguous() and images.numel() == x_dst.numel() and labels.numel() == y_dst.numel()
+            and images.device == x_dst.device and labels.device == y_dst.device):
+        import ctypes
+
+        from .. import _lib
+
+        L = _lib.cuda()
+        stream = ctypes.c_void_p(torch.cuda.current_stream(x_dst.device).cuda_stream)
+        rc = L.pdl_copy_pair(ctypes.c_void_p(x_dst.data_ptr()), ctypes.c_void_p(images.data_ptr()), images.numel() * images.element_size(),
+                             ctypes.c_void_p(y_dst.data_ptr()), ctypes.c_void_p(labels.data_ptr()), labels.numel() * labels.element_size(), stream)
+        if rc != 0:
+            raise RuntimeError("input refresh kernel failed: %s" % L.pdl_last_error().decode())
+        return
+    x_dst.view(images.shape).copy_(images, non_blocking=True)
+    y_dst.copy_(labels, non_blocking=True)
+
+
 class PendingLoss:
     """Loss of one training step on its way to (or already in) pinned host memory."""
 

@@ -70,3 +70,23 @@ def test_pending_loss_expires_instead_of_returning_a_later_step():
     with pytest.raises(RuntimeError, match="expired"):
         first.item()
     assert all(torch.isfinite(torch.tensor(h.item())) for h in kept[1:])
+
+
+@pytest.mark.parametrize("n0,n1,off", [(313600, 800, 0), (1000, 7, 0), (4099, 33, 4), (16, 16, 1), (0, 24, 0)])
+def test_copy_pair_kernel(n0, n1, off):
+    import ctypes
+
+    from pytorch_distributed_learning_b200 import _lib
+
+    dev = torch.device("cuda", 0)
+    g = torch.Generator().manual_seed(n0 + n1)
+    s0 = torch.randint(0, 255, (n0 + off,), dtype=torch.uint8, generator=g).to(dev)
+    s1 = torch.randint(0, 255, (n1 + off,), dtype=torch.uint8, generator=g).to(dev)
+    d0 = torch.zeros(n0 + off + 16, dtype=torch.uint8, device=dev)
+    d1 = torch.zeros(n1 + off + 16, dtype=torch.uint8, device=dev)
+    P = ctypes.c_void_p
+    rc = _lib.cuda().pdl_copy_pair(P(d0.data_ptr() + off), P(s0.data_ptr() + off), n0, P(d1.data_ptr() + off), P(s1.data_ptr() + off), n1,
+                                   P(torch.cuda.current_stream().cuda_stream))
+    assert rc == 0
+    assert torch.equal(d0[off:off + n0], s0[off:off + n0]) and torch.equal(d1[off:off + n1], s1[off:off + n1])
+    assert d0[:off].sum() == 0 and d0[off + n0:].sum() == 0 and d1[:off].sum() == 0 and d1[off + n1:].sum() == 0  # nothing outside the ranges
