@@ -66,14 +66,17 @@ __device__ unsigned int g_c1w_done = 0;
 // are summed in shared memory in warp order, the CTA's row goes to `partial`, the last CTA adds the rows in
 // CTA order (deterministic).
 constexpr int kC1Threads = 512, kC1Warps = kC1Threads / 32;
-constexpr int kC1StageFloats = 30 * 32 + 169 * 32 + 169 * 32 / 4;  // img + g + argmax bytes
+// Image rows are 34 floats apart: the four arg-max offsets {0, 1, 34, 35} a warp's lanes can ask for then sit in four
+// different banks (with a stride of 32, rows r and r+1 collide and every tap load is a 2-way conflict).
+constexpr int kC1ImgLd = 34;
+constexpr int kC1StageFloats = 30 * kC1ImgLd + 169 * 32 + 169 * 32 / 4;  // img + g + argmax bytes
 __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const float* __restrict__ x, const float* __restrict__ da1,
                                                                        const uint8_t* __restrict__ idx1, const float* __restrict__ a1,
                                                                        float* __restrict__ gw1, float* __restrict__ gb1,
                                                                        float* __restrict__ partial, int N, int imgs_per_cta) {
   extern __shared__ float c1_smem[];
-  float* img = c1_smem;          // [30][32]
-  float* sg = img + 30 * 32;     // [169][32]
+  float* img = c1_smem;               // [30][kC1ImgLd]
+  float* sg = img + 30 * kC1ImgLd;    // [169][32]
   uint8_t* sarg = reinterpret_cast<uint8_t*>(sg + 169 * 32);
   float* red = c1_smem + kC1StageFloats;  // [16][832]
   const int c = threadIdx.x % 32, wp = threadIdx.x / 32;
@@ -87,7 +90,7 @@ __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const flo
     __syncthreads();
     for (int i = threadIdx.x; i < 30 * 32; i += kC1Threads) {
       const int r = i / 32, cc = i % 32, h = r - 1, w = cc - 1;
-      img[i] = (h >= 0 && h < 28 && w >= 0 && w < 28) ? x[(static_cast<long long>(n) * 28 + h) * 28 + w] : 0.f;
+      img[r * kC1ImgLd + cc] = (h >= 0 && h < 28 && w >= 0 && w < 28) ? x[(static_cast<long long>(n) * 28 + h) * 28 + w] : 0.f;
     }
     const long long base = static_cast<long long>(n) * 169 * 32;
 #pragma unroll 11
@@ -100,10 +103,10 @@ __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const flo
     for (int pp = wp; pp < 169; pp += kC1Warps) {
       const float g = sg[pp * 32 + c];
       const int arg = sarg[pp * 32 + c];
-      const float* patch = img + (2 * (pp / 13) + (arg >> 1)) * 32 + 2 * (pp % 13) + (arg & 1);
+      const float* patch = img + (2 * (pp / 13) + (arg >> 1)) * kC1ImgLd + 2 * (pp % 13) + (arg & 1);
       accb += g;
 #pragma unroll
-      for (int t = 0; t < 25; ++t) acc[t] = fmaf(g, patch[(t / 5) * 32 + t % 5], acc[t]);
+      for (int t = 0; t < 25; ++t) acc[t] = fmaf(g, patch[(t / 5) * kC1ImgLd + t % 5], acc[t]);
     }
   }
 #pragma unroll
