@@ -49,7 +49,7 @@ class PendingLoss:
 
     def item(self):
         ring = self._ring
-        if ring.serial - self._serial >= ring.DEPTH:
+        if ring.serial - self._serial > ring.DEPTH:  # the publish numbered serial + DEPTH has taken this slot
             raise RuntimeError("PendingLoss expired: its host slot was reused (%d steps were issued since; the ring keeps %d)"
                                % (ring.serial - self._serial, ring.DEPTH))
         ring.events[self._slot].synchronize()

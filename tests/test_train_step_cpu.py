@@ -20,3 +20,40 @@ def test_cpu_train_step_and_step_async_agree():
         assert float(la.item()) == float(lb.item())
     for p, q in zip(a.parameters(), b.parameters()):
         assert torch.equal(p, q)
+
+
+def test_pending_loss_bookkeeping_without_a_gpu():
+    """PendingLoss reads its own ring slot after its own event and refuses to read a slot that has been reused."""
+    from pytorch_distributed_learning_b200.parallel.pipeline import PendingLoss
+
+    class _Event:
+        def __init__(self):
+            self.waited = 0
+
+        def synchronize(self):
+            self.waited += 1
+
+        def query(self):
+            return True
+
+    class _Ring:
+        DEPTH = 4
+
+        def __init__(self):
+            self.host, self.events, self.serial = torch.arange(4, dtype=torch.float32) * 1.5, [_Event() for _ in range(4)], 0
+
+    ring = _Ring()
+    handles = []
+    for _ in range(4):
+        handles.append(PendingLoss(ring, ring.serial % ring.DEPTH, ring.serial))
+        ring.serial += 1
+    assert [h.item() for h in handles] == [0.0, 1.5, 3.0, 4.5] and float(handles[2]) == 3.0
+    assert ring.events[2].waited == 2 and handles[0].ready()
+    ring.serial += 1  # a fifth step reuses slot 0
+    try:
+        handles[0].item()
+    except RuntimeError as e:
+        assert "expired" in str(e)
+    else:
+        raise AssertionError("expired handle was read")
+    assert handles[1].item() == 1.5
