@@ -100,8 +100,8 @@ def train_resnet(net, criterion, optimizer, loader, device, epochs, is_printer, 
     for ep in range(1, epochs + 1):
         metrics.reset()
         loader.sampler.set_epoch(ep)
-        for idx, (inputs, targets) in enumerate(loader):
-            inputs, targets = inputs.to(device), targets.to(device)
+        # batches arrive on the device one step ahead (the reference does a blocking .to(device) here, example_launch.py:83)
+        for idx, (inputs, targets) in enumerate(pdl.utils.data.CudaPrefetcher(loader, device)):
             if step_fn is not None:  # the same iteration replayed as one CUDA graph (captured once per batch shape)
                 loss = step_fn(inputs, targets)
                 outputs = step_fn.outputs()

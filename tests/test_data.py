@@ -89,3 +89,17 @@ def test_transforms_match_their_definitions():
         T.RandomCrop(64)(img)
     assert "RandomCrop" in repr(T.cifar10_train_transform())
     assert pdl.utils.data.transforms is T
+
+
+def test_cuda_prefetcher_is_a_passthrough_on_cpu():
+    import torch
+
+    import pytorch_distributed_learning_b200 as pdl
+
+    ds = pdl.utils.data.SyntheticMNIST(20)
+    loader = torch.utils.data.DataLoader(ds, batch_size=6, shuffle=False)
+    pre = pdl.utils.data.CudaPrefetcher(loader, "cpu")
+    assert len(pre) == len(loader) == 4 and pre.sampler is loader.sampler
+    for (a, b), (c, d) in zip(pre, loader):
+        assert torch.equal(a, c) and torch.equal(b, d)
+    assert sum(1 for _ in pre) == 4  # re-iterable

@@ -90,3 +90,20 @@ def test_copy_pair_kernel(n0, n1, off):
     assert rc == 0
     assert torch.equal(d0[off:off + n0], s0[off:off + n0]) and torch.equal(d1[off:off + n1], s1[off:off + n1])
     assert d0[:off].sum() == 0 and d0[off + n0:].sum() == 0 and d1[:off].sum() == 0 and d1[off + n1:].sum() == 0  # nothing outside the ranges
+
+
+def test_cuda_prefetcher_delivers_every_batch_in_order():
+    dev = torch.device("cuda", 0)
+    ds = pdl.utils.data.SyntheticCIFAR10(1000)
+    loader = torch.utils.data.DataLoader(ds, batch_size=96, shuffle=False, pin_memory=True)
+    pre = pdl.utils.data.CudaPrefetcher(loader, dev)
+    seen = 0
+    acc = torch.zeros((), device=dev, dtype=torch.float64)
+    for (x, y), (rx, ry) in zip(pre, loader):
+        assert x.is_cuda and y.is_cuda and x.shape == rx.shape
+        # keep the GPU busy between batches so the next copy really overlaps queued work
+        acc += (x.double() @ torch.ones(x.shape[-1], device=dev, dtype=torch.float64)).sum()
+        assert torch.equal(x.cpu(), rx) and torch.equal(y.cpu(), ry)
+        seen += x.shape[0]
+    assert seen == 1000 and len(pre) == 11 and torch.isfinite(acc)
+    assert sum(b[0].shape[0] for b in pre) == 1000  # a second epoch works
