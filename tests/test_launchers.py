@@ -69,3 +69,28 @@ def test_launch_failure_stops_the_job(tmp_path):
     rc = subprocess.run([sys.executable, "-m", "pytorch_distributed_learning_b200.launch", "--nproc_per_node=2", "--use_env", str(script)],
                         cwd=ROOT, timeout=120).returncode
     assert rc == 3 and time.time() - t0 < 45
+
+
+def test_two_nodes_on_localhost(tmp_path):
+    """The reference README's worked example is 2 machines x 1 process; here both "nodes" are launcher processes on
+    this host (node_rank 0 and 1) that must rendezvous through node 0's store and train together."""
+    import subprocess
+    import sys
+
+    from conftest import free_port
+
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    port = free_port()
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", OMP_NUM_THREADS="2")
+    procs = []
+    for node in (0, 1):
+        cmd = [sys.executable, "-m", "pytorch_distributed_learning_b200.launch", "--nproc_per_node=1", "--nnodes=2", "--node_rank=%d" % node,
+               "--master_addr=127.0.0.1", "--master_port=%d" % port, "examples/resnet_launch.py", "--max-steps", "1"]
+        procs.append(subprocess.Popen(cmd, cwd=root, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = []
+    for p in procs:
+        out, _ = p.communicate(timeout=600)
+        outs.append(out)
+        assert p.returncode == 0, out[-3000:]
+    assert "[init] == local rank: 0, global rank: 0 ==" in outs[0] and "[init] == local rank: 0, global rank: 1 ==" in outs[1]
+    assert "Training Finished" in outs[0] and "Training Finished" not in outs[1]  # only global rank 0 prints
