@@ -448,6 +448,59 @@ def all_gather(tensor_list, tensor, group=None):
         dst.copy_(src)
 
 
+def all_gather_into_tensor(output_tensor, input_tensor, group=None):
+    """``output_tensor`` (world x the input's size along dim 0, or stacked) receives every rank's input, in rank order."""
+    if _skip(group):
+        return None
+    parts = _resolve(group).allgather(input_tensor)
+    flat = output_tensor.view(len(parts), -1)
+    for i, src in enumerate(parts):
+        flat[i].copy_(src.reshape(-1))
+
+
+def reduce_scatter_tensor(output, input, op=ReduceOp.SUM, group=None):
+    """Rank r receives the r-th of ``world`` equal chunks of the element-wise reduction of ``input`` over the group
+    (composed from the group's allreduce: every variant of it is bit-identical across ranks, so this is too)."""
+    if _skip(group):
+        return None
+    pg = _resolve(group)
+    world = len(pg.ranks)
+    if input.numel() != output.numel() * world:
+        raise ValueError("reduce_scatter_tensor: input must hold world_size (%d) chunks of the output's size" % world)
+    full = input.detach().clone().contiguous()
+    pg.allreduce(full, op)
+    output.copy_(full.view(world, -1)[pg.rank()].view_as(output))
+
+
+def gather(tensor, gather_list=None, dst=0, group=None):
+    """``gather_list`` (on global rank ``dst`` only) receives every rank's tensor."""
+    if _skip(group):
+        return None
+    pg = _resolve(group)
+    parts = pg.allgather(tensor)
+    if pg.rank() == pg.group_rank_of(dst):
+        if gather_list is None or len(gather_list) != len(parts):
+            raise ValueError("gather: the destination rank must pass a gather_list of world_size tensors")
+        for d, s in zip(gather_list, parts):
+            d.copy_(s)
+
+
+def scatter(tensor, scatter_list=None, src=0, group=None):
+    """Rank r receives ``scatter_list[r]`` of global rank ``src``."""
+    if _skip(group):
+        return None
+    pg = _resolve(group)
+    world = len(pg.ranks)
+    stacked = torch.empty((world,) + tuple(tensor.shape), dtype=tensor.dtype, device=tensor.device)
+    if pg.rank() == pg.group_rank_of(src):
+        if scatter_list is None or len(scatter_list) != world:
+            raise ValueError("scatter: the source rank must pass a scatter_list of world_size tensors")
+        for i, s in enumerate(scatter_list):
+            stacked[i].copy_(s)
+    pg.broadcast(stacked, pg.group_rank_of(src))
+    tensor.copy_(stacked[pg.rank()])
+
+
 def all_gather_object(object_list, obj, group=None):
     if _skip(group):
         return None

@@ -239,3 +239,22 @@ def tracing_worker(rank, world, port, outdir):
         step(torch.randn(4, 1, 28, 28), torch.randint(0, 10, (4,)))
     tracing.flush()
     dist.destroy_process_group()
+
+
+def more_collectives(rank, world, port, outdir):
+    _init(rank, world, port)
+    res = {}
+    out = torch.zeros(world, 3)
+    dist.all_gather_into_tensor(out, torch.full((3,), float(rank)))
+    res["agit"] = out.clone()
+    rs = torch.zeros(2)
+    dist.reduce_scatter_tensor(rs, torch.arange(2 * world, dtype=torch.float32) + rank)
+    res["rs"] = rs.clone()
+    glist = [torch.zeros(2) for _ in range(world)] if rank == 1 else None
+    dist.gather(torch.full((2,), float(rank + 1)), glist, dst=1)
+    res["gather"] = torch.stack(glist) if glist is not None else None
+    mine = torch.zeros(2)
+    dist.scatter(mine, [torch.full((2,), 10.0 * i) for i in range(world)] if rank == 0 else None, src=0)
+    res["scatter"] = mine.clone()
+    torch.save(res, os.path.join(outdir, "r%d.pt" % rank))
+    dist.destroy_process_group()

@@ -50,3 +50,17 @@ def test_double_init_and_uninitialised(port, monkeypatch):
         dist.init_process_group("mpi", init_method="tcp://127.0.0.1:%d" % port, world_size=1, rank=0)
     with pytest.raises(ValueError, match="both"):
         dist.init_process_group("gloo", init_method="env://", store=object(), world_size=1, rank=0)
+
+
+def test_gather_scatter_reduce_scatter(tmp_path):
+    world = 3
+    pdl.multiprocessing.spawn(_workers.more_collectives, args=(world, free_port(), str(tmp_path)), nprocs=world)
+    for r in range(world):
+        res = torch.load(tmp_path / ("r%d.pt" % r), weights_only=False)
+        assert res["agit"].tolist() == [[float(i)] * 3 for i in range(world)]
+        full = torch.arange(2 * world, dtype=torch.float32) * world + sum(range(world))
+        assert torch.equal(res["rs"], full.view(world, 2)[r])
+        assert (res["gather"] is None) == (r != 1)
+        if r == 1:
+            assert res["gather"].tolist() == [[float(i + 1)] * 2 for i in range(world)]
+        assert res["scatter"].tolist() == [10.0 * r] * 2
