@@ -47,6 +47,21 @@ int pdl_cpu_recv(void* comm, void* buf, uint64_t nbytes, int src);
  *      compute_bucket_assignment_by_size contract) ------------------------------------------------ */
 int pdl_bucket_assign(const int64_t* sizes, const int32_t* kinds, int n, const int64_t* limits, int nlimits, int32_t* bucket_of);
 
+/* ---- reducer core (reference: torch's C++ Reducer behind DistributedDataParallel, launch_dist.py:61): which buckets
+ *      may be launched when a gradient becomes ready (all members ready AND every earlier bucket launched), what is
+ *      left at the end of backward, the arrival order of the first iteration.  Tensors and kernels stay with the caller.
+ *      mark_ready returns the number of buckets written to `out`, -1 unknown parameter, -2 second gradient for a
+ *      parameter in one iteration, -3 `out` too small. ------------------------------------------------------------- */
+void* pdl_reducer_create(int num_params, const int32_t* bucket_of, int num_buckets);
+void pdl_reducer_destroy(void* reducer);
+int pdl_reducer_set_layout(void* reducer, int num_params, const int32_t* bucket_of, int num_buckets);
+void pdl_reducer_prepare(void* reducer, int record_arrival);
+int pdl_reducer_mark_ready(void* reducer, int param, int32_t* out, int cap);
+int pdl_reducer_finalize(void* reducer, int32_t* out, int cap);
+int pdl_reducer_is_ready(void* reducer, int param);
+int pdl_reducer_next_bucket(void* reducer);
+int pdl_reducer_arrival(void* reducer, int32_t* out, int cap);
+
 #ifdef __cplusplus
 }
 #endif

@@ -60,6 +60,18 @@ def _declare_host(L):
     L.pdl_cpu_send.argtypes = [c_void_p, c_void_p, c_uint64, c_int]
     L.pdl_cpu_recv.argtypes = [c_void_p, c_void_p, c_uint64, c_int]
     L.pdl_bucket_assign.argtypes = [POINTER(c_int64), POINTER(c_int32), c_int, POINTER(c_int64), c_int, POINTER(c_int32)]
+    L.pdl_reducer_create.restype = c_void_p
+    L.pdl_reducer_create.argtypes = [c_int, POINTER(c_int32), c_int]
+    L.pdl_reducer_destroy.restype = None
+    L.pdl_reducer_destroy.argtypes = [c_void_p]
+    L.pdl_reducer_set_layout.argtypes = [c_void_p, c_int, POINTER(c_int32), c_int]
+    L.pdl_reducer_prepare.restype = None
+    L.pdl_reducer_prepare.argtypes = [c_void_p, c_int]
+    L.pdl_reducer_mark_ready.argtypes = [c_void_p, c_int, POINTER(c_int32), c_int]
+    L.pdl_reducer_finalize.argtypes = [c_void_p, POINTER(c_int32), c_int]
+    L.pdl_reducer_is_ready.argtypes = [c_void_p, c_int]
+    L.pdl_reducer_next_bucket.argtypes = [c_void_p]
+    L.pdl_reducer_arrival.argtypes = [c_void_p, POINTER(c_int32), c_int]
 
 
 def cuda_available_lib():

@@ -35,6 +35,7 @@ from torch.autograd import Variable
 from .. import _lib
 from ..utils import tracing as _tracing
 from . import distributed as dist
+from .reducer import ReducerCore
 
 _MiB = 1024 * 1024
 _ALIGN_ELEMS = 4  # every parameter starts on a 16-byte boundary inside the arena (float4 access)
@@ -57,11 +58,11 @@ def compute_bucket_assignment_by_size(sizes_bytes, limits, kinds=None):
 
 
 class _Bucket:
-    __slots__ = ("index", "param_ids", "offset", "numel", "pending", "launched", "fused_group", "fused_params", "first_flag", "grads")
+    __slots__ = ("index", "param_ids", "offset", "numel", "launched", "fused_group", "fused_params", "first_flag", "grads")
 
     def __init__(self, index, param_ids, offset, numel):
         self.index, self.param_ids, self.offset, self.numel = index, param_ids, offset, numel
-        self.pending, self.launched = len(param_ids), False
+        self.launched = False  # pending counts and the launch order live in the C++ reducer core (reducer.py)
         self.fused_group, self.fused_params, self.first_flag = None, (), 1
         self.grads = {}
 
@@ -136,7 +137,7 @@ class DistributedDataParallel(nn.Module):
         self._params = [p for _, p in params]
         self._world = self.process_group.size()
         self._iteration = 0
-        self._arrival = []
+        self._core = None  # C++ reducer state machine, created with the first bucket layout
         self._rebuilt = False
         self._callback_queued = False
         self._comm_hook, self._hook_results = None, []
@@ -207,7 +208,11 @@ class DistributedDataParallel(nn.Module):
         self._in_views = [g_in[self._offset_of[i]:self._offset_of[i] + p.numel()].view_as(p) for i, p in enumerate(ps)]
         self._avg_views = [g_avg[self._offset_of[i]:self._offset_of[i] + p.numel()].view_as(p) for i, p in enumerate(ps)]
         self._order = list(order)
-        self._next_bucket = 0
+        layout = [self._bucket_of[i] for i in range(len(ps))]
+        if self._core is None:
+            self._core = ReducerCore(len(ps), layout)
+        else:
+            self._core.set_layout(len(ps), layout)
         self._fused_checked = False
 
     def bucket_sizes_bytes(self):
@@ -241,18 +246,16 @@ class DistributedDataParallel(nn.Module):
 
     def _prepare_for_backward(self):
         for bk in self._buckets:
-            bk.pending, bk.launched = len(bk.param_ids), False
+            bk.launched = False
             bk.grads.clear()
-        self._next_bucket = 0
+        self._core.prepare(record_arrival=self._iteration == 0)  # pending counts, ready flags, launch cursor (C++)
         self._callback_queued = False
-        if self._iteration == 0:
-            self._arrival = []
 
     def _maybe_rebuild_buckets(self):
         if self._rebuilt or self._iteration != 1:
             return
         self._rebuilt = True
-        seen = list(dict.fromkeys(self._arrival))
+        seen = list(dict.fromkeys(self._core.arrival()))
         seen += [i for i in self._order if i not in set(seen)]
         order = self.process_group.broadcast_object(seen, 0)
         if order != self._order:
@@ -281,21 +284,14 @@ class DistributedDataParallel(nn.Module):
         if not self._callback_queued:
             self._callback_queued = True
             Variable._execution_engine.queue_callback(self._finalize_backward)
-        if self._iteration == 0:
-            self._arrival.append(i)
-        bk = self._buckets[self._bucket_of[i]]
-        if i in bk.grads:
+        try:
+            launchable = self._core.mark_ready(i)  # buckets complete now AND next in the fixed launch order
+        except RuntimeError:
             raise RuntimeError("parameter %r received a second gradient in one backward pass; DDP reduces each parameter once per "
-                               "iteration (use no_sync() for gradient accumulation)" % self._param_names[i])
-        bk.grads[i] = param.grad
-        bk.pending -= 1
-        if bk.pending == 0:
-            self._launch_ready_buckets()
-
-    def _launch_ready_buckets(self):
-        while self._next_bucket < len(self._buckets) and self._buckets[self._next_bucket].pending == 0:
-            self._launch_bucket(self._buckets[self._next_bucket])
-            self._next_bucket += 1
+                               "iteration (use no_sync() for gradient accumulation)" % self._param_names[i]) from None
+        self._buckets[self._bucket_of[i]].grads[i] = param.grad
+        for b in launchable:
+            self._launch_bucket(self._buckets[b])
 
     def _launch_bucket(self, bk):
         if _tracing.enabled():
@@ -333,11 +329,8 @@ class DistributedDataParallel(nn.Module):
         self._callback_queued = False
         if not self.require_backward_grad_sync:
             return
-        if self._next_bucket < len(self._buckets):
-            # some parameters produced no gradient this iteration: they contribute zeros
-            for bk in self._buckets[self._next_bucket:]:
-                bk.pending = 0
-            self._launch_ready_buckets()
+        for b in self._core.finalize():  # some parameters produced no gradient this iteration: they contribute zeros
+            self._launch_bucket(self._buckets[b])
         if self._comm_hook is not None:
             self._finish_comm_hook()
         else:
