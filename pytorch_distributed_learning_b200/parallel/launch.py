@@ -6,7 +6,7 @@ Each worker gets RANK, LOCAL_RANK, WORLD_SIZE, LOCAL_WORLD_SIZE, GROUP_RANK, MAS
 MASTER_PORT and OMP_NUM_THREADS in its environment (what launch_dist.py:45-46 reads) and,
 unless ``--use_env`` is given, ``--local-rank=N`` appended to its argv.  Workers are polled
 every 100 ms; the first non-zero exit terminates the rest and becomes the launcher's exit
-code (no restarts, like ``max_restarts=0``).
+code, unless ``--max_restarts=N`` asks for the whole group to be started again (default 0, as in torch).
 """
 from __future__ import annotations
 
@@ -27,6 +27,7 @@ def build_parser():
     p.add_argument("--master_addr", "--master-addr", type=str, default="127.0.0.1")
     p.add_argument("--master_port", "--master-port", type=int, default=29500)
     p.add_argument("--use_env", "--use-env", action="store_true", help="do not append --local-rank=N to the script's argv")
+    p.add_argument("--max_restarts", "--max-restarts", type=int, default=0, help="restart the whole worker group this many times after a failure (single node)")
     p.add_argument("-m", "--module", action="store_true", help="run the script as a python module")
     p.add_argument("--no_python", "--no-python", action="store_true", help="exec the script directly")
     p.add_argument("training_script", type=str)
@@ -76,10 +77,27 @@ def worker_cmd(args, local_rank):
 
 
 def run(args):
+    """Run the worker group; after a failure, start the WHOLE group again up to ``--max_restarts`` times (what the elastic
+    agent behind ``torch.distributed.launch`` does; default 0 = fail fast, [T] torch/distributed/run.py:491-505).  Restarted
+    workers see TORCHELASTIC_RESTART_COUNT = 1, 2, ... and are expected to resume from their last checkpoint."""
     nproc = _nproc(args.nproc_per_node)
+    max_restarts = max(0, int(getattr(args, "max_restarts", 0) or 0))
+    if max_restarts and args.nnodes > 1:
+        raise SystemExit("--max_restarts needs a re-rendezvous across nodes, which env:// / tcp:// cannot do; use it with --nnodes=1")
+    attempt = 0
+    while True:
+        code = _run_group(args, nproc, attempt, max_restarts)
+        if code == 0 or attempt >= max_restarts:  # (a signal to the launcher itself exits through on_signal, not here)
+            return code
+        attempt += 1
+        sys.stderr.write("launch: restarting the worker group (attempt %d of %d)\n" % (attempt, max_restarts))
+
+
+def _run_group(args, nproc, restart_count, max_restarts):
     procs = []
     for lr in range(nproc):
         env = worker_env(os.environ, args.node_rank, lr, nproc, args.nnodes, args.master_addr, args.master_port)
+        env["TORCHELASTIC_RESTART_COUNT"], env["TORCHELASTIC_MAX_RESTARTS"] = str(restart_count), str(max_restarts)
         procs.append(subprocess.Popen(worker_cmd(args, lr), env=env))
 
     def terminate_all(sig=signal.SIGTERM):

@@ -94,3 +94,35 @@ def test_two_nodes_on_localhost(tmp_path):
         assert p.returncode == 0, out[-3000:]
     assert "[init] == local rank: 0, global rank: 0 ==" in outs[0] and "[init] == local rank: 0, global rank: 1 ==" in outs[1]
     assert "Training Finished" in outs[0] and "Training Finished" not in outs[1]  # only global rank 0 prints
+
+
+def test_launch_max_restarts_runs_the_group_again(tmp_path):
+    """--max_restarts: after a worker fails, the whole group is started again (with TORCHELASTIC_RESTART_COUNT bumped),
+    rendezvouses on the same port and finishes; without attempts left the failure is final."""
+    from conftest import free_port
+
+    script = tmp_path / "flaky.py"
+    script.write_text(
+        "import os, sys\n"
+        "sys.path.insert(0, %r)\n"
+        "import torch, pytorch_distributed_learning_b200 as pdl\n"
+        "attempt, rank = int(os.environ['TORCHELASTIC_RESTART_COUNT']), int(os.environ['RANK'])\n"
+        "pdl.distributed.init_process_group('gloo')\n"
+        "t = torch.ones(3) * (rank + 1)\n"
+        "pdl.distributed.all_reduce(t)\n"
+        "if attempt < int(os.environ['FAIL_UNTIL']) and rank == 1:\n"
+        "    os._exit(7)\n"
+        "pdl.distributed.barrier()\n"
+        "print('rank %%d done on attempt %%d sum %%d' %% (rank, attempt, int(t[0])), flush=True)\n"
+        "pdl.distributed.destroy_process_group()\n" % ROOT)
+    env = dict(os.environ, CUDA_VISIBLE_DEVICES="", FAIL_UNTIL="1")
+    cmd = [sys.executable, "-m", "pytorch_distributed_learning_b200.launch", "--nproc_per_node=2", "--use_env", "--max_restarts=2",
+           "--master_port=%d" % free_port(), str(script)]
+    p = subprocess.run(cmd, cwd=ROOT, env=env, timeout=300, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert p.returncode == 0, p.stdout[-2000:]
+    assert "restarting the worker group (attempt 1 of 2)" in p.stdout
+    assert "rank 0 done on attempt 1 sum 3" in p.stdout and "rank 1 done on attempt 1 sum 3" in p.stdout
+    env["FAIL_UNTIL"] = "5"  # keeps failing: two restarts, then the failure is final
+    cmd[-2] = "--master_port=%d" % free_port()
+    p = subprocess.run(cmd, cwd=ROOT, env=env, timeout=300, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert p.returncode == 7 and p.stdout.count("restarting the worker group") == 2
