@@ -58,16 +58,23 @@ def wrap(model, device):
     return nn.parallel.DistributedDataParallel(model)
 
 
-def train_convnet(model, criterion, optimizer, loader, device, epochs, is_printer, graphed=False, max_steps=None):
-    """Loop body of the reference's ConvNet scripts: loss printed every 100 steps by the node's local rank 0."""
+def train_convnet(model, criterion, optimizer, loader, device, epochs, is_printer, graphed=False, max_steps=None,
+                  checkpoint_path=None, checkpoint_every=0, start_step=0, fail_at=None):
+    """Loop body of the reference's ConvNet scripts: loss printed every 100 steps by the node's local rank 0.
+
+    Not in the reference (it has no checkpoints): every ``checkpoint_every`` steps a full training state goes to
+    ``checkpoint_path`` (rank 0 writes, everyone barriers); ``start_step`` fast-forwards a resumed run past the batches
+    it has already consumed; ``fail_at`` kills this process after that step (fault injection for the restart test)."""
     start = datetime.now()
     total_step = len(loader)
     if is_printer:
         print("Total step: ", total_step)
     step_fn = pdl.TrainStep(model, criterion, optimizer) if graphed else None
-    seen = 0
+    seen = start_step
     for epoch in range(epochs):
         for i, (images, labels) in enumerate(loader):
+            if epoch * total_step + i < start_step:
+                continue  # consumed before the restart
             if step_fn is not None:
                 loss = step_fn(images, labels)
             else:
@@ -81,6 +88,10 @@ def train_convnet(model, criterion, optimizer, loader, device, epochs, is_printe
             if (i + 1) % 100 == 0 and is_printer:
                 print("Epoch [{}/{}], Step [{}/{}], Loss: {:.4f}".format(epoch + 1, epochs, i + 1, total_step, loss.item()))
             seen += 1
+            if checkpoint_every and seen % checkpoint_every == 0:
+                pdl.utils.checkpoint.save_checkpoint(model, checkpoint_path, optimizer=optimizer, epoch=epoch, extra={"step": seen})
+            if fail_at is not None and seen == fail_at:
+                os._exit(17)
             if max_steps and seen >= max_steps:
                 break
         if max_steps and seen >= max_steps:
