@@ -56,7 +56,13 @@ struct CpuComm {
   int rank = 0, world = 1;
   std::vector<int> peer_fd;  // peer_fd[r] = socket to rank r (-1 for self)
   std::vector<char> scratch;
+  double timeout_s = 0;  // per collective; 0 = wait for ever
 };
+
+// Absolute deadline of a collective that starts now, and the error code of one that failed:
+// -1 = a peer exited / the connection dropped, -2 = the deadline passed (a peer is alive but never joined).
+static double deadline_of(const CpuComm* c) { return c->timeout_s > 0 ? now_s() + c->timeout_s : 0; }
+static int failure() { return errno == ETIMEDOUT ? -2 : -1; }
 
 }  // namespace pdl
 
@@ -69,6 +75,7 @@ void* pdl_cpu_comm_create(void* store, const char* prefix, int rank, int world, 
   auto* c = new CpuComm();
   c->rank = rank;
   c->world = world;
+  c->timeout_s = timeout_s;
   c->peer_fd.assign(world, -1);
   if (world == 1) return c;
 
@@ -130,16 +137,17 @@ int pdl_cpu_allreduce(void* h, void* buf, uint64_t count, int dtype, int op) {
   char* base = static_cast<char*>(buf);
   c->scratch.resize(chunk * es);
   const int next = c->peer_fd[(r + 1) % W], prev = c->peer_fd[(r - 1 + W) % W];
+  const double dl = deadline_of(c);
   // reduce-scatter: after W-1 steps rank r owns the fully reduced chunk (r+1)%W
   for (int s = 0; s < W - 1; ++s) {
     int send_i = ((r - s) % W + W) % W, recv_i = ((r - s - 1) % W + W) % W;
-    if (!send_recv(next, base + lo(send_i) * es, len(send_i) * es, prev, c->scratch.data(), len(recv_i) * es)) return -1;
+    if (!send_recv(next, base + lo(send_i) * es, len(send_i) * es, prev, c->scratch.data(), len(recv_i) * es, dl)) return failure();
     reduce_bytes(base + lo(recv_i) * es, c->scratch.data(), len(recv_i), dtype, op);
   }
   // allgather of the owned chunks
   for (int s = 0; s < W - 1; ++s) {
     int send_i = ((r + 1 - s) % W + W) % W, recv_i = ((r - s) % W + W) % W;
-    if (!send_recv(next, base + lo(send_i) * es, len(send_i) * es, prev, base + lo(recv_i) * es, len(recv_i) * es)) return -1;
+    if (!send_recv(next, base + lo(send_i) * es, len(send_i) * es, prev, base + lo(recv_i) * es, len(recv_i) * es, dl)) return failure();
   }
   return 0;
 }
@@ -147,12 +155,13 @@ int pdl_cpu_allreduce(void* h, void* buf, uint64_t count, int dtype, int op) {
 int pdl_cpu_broadcast(void* h, void* buf, uint64_t nbytes, int root) {
   auto* c = static_cast<CpuComm*>(h);
   if (c->world == 1 || nbytes == 0) return 0;
+  const double dl = deadline_of(c);
   if (c->rank == root) {
     for (int p = 0; p < c->world; ++p)
-      if (p != root && !send_all(c->peer_fd[p], buf, nbytes)) return -1;
+      if (p != root && !send_all(c->peer_fd[p], buf, nbytes, dl)) return failure();
     return 0;
   }
-  return recv_all(c->peer_fd[root], buf, nbytes) ? 0 : -1;
+  return recv_all(c->peer_fd[root], buf, nbytes, dl) ? 0 : failure();
 }
 
 // recv holds world blocks of nbytes; block r comes from rank r.
@@ -160,9 +169,10 @@ int pdl_cpu_allgather(void* h, const void* send, void* recv, uint64_t nbytes) {
   auto* c = static_cast<CpuComm*>(h);
   char* out = static_cast<char*>(recv);
   memcpy(out + static_cast<size_t>(c->rank) * nbytes, send, nbytes);
+  const double dl = deadline_of(c);
   for (int s = 1; s < c->world; ++s) {
     int to = (c->rank + s) % c->world, from = (c->rank - s + c->world) % c->world;
-    if (!send_recv(c->peer_fd[to], send, nbytes, c->peer_fd[from], out + static_cast<size_t>(from) * nbytes, nbytes)) return -1;
+    if (!send_recv(c->peer_fd[to], send, nbytes, c->peer_fd[from], out + static_cast<size_t>(from) * nbytes, nbytes, dl)) return failure();
   }
   return 0;
 }
@@ -174,12 +184,12 @@ int pdl_cpu_barrier(void* h) {
 
 int pdl_cpu_send(void* h, const void* buf, uint64_t nbytes, int dst) {
   auto* c = static_cast<CpuComm*>(h);
-  return send_all(c->peer_fd[dst], buf, nbytes) ? 0 : -1;
+  return send_all(c->peer_fd[dst], buf, nbytes, deadline_of(c)) ? 0 : failure();
 }
 
 int pdl_cpu_recv(void* h, void* buf, uint64_t nbytes, int src) {
   auto* c = static_cast<CpuComm*>(h);
-  return recv_all(c->peer_fd[src], buf, nbytes) ? 0 : -1;
+  return recv_all(c->peer_fd[src], buf, nbytes, deadline_of(c)) ? 0 : failure();
 }
 
 }  // extern "C"

@@ -28,13 +28,34 @@ inline void set_nodelay(int fd) {
   setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof(one));
 }
 
-// Write exactly n bytes. Returns false on a closed/broken socket.
-inline bool send_all(int fd, const void* buf, size_t n) {
+// Deadlines are absolute times on the now_s() clock; 0 means "wait for ever".  A missed deadline makes the call return
+// false with errno = ETIMEDOUT (a peer that is alive but never shows up; a dead peer closes its socket and is seen at once).
+inline int poll_ms(double deadline_s) {
+  if (deadline_s <= 0) return 60000;
+  const double left = deadline_s - now_s();
+  if (left <= 0) return -1;
+  return left > 60.0 ? 60000 : static_cast<int>(left * 1000.0) + 1;
+}
+
+// Wait until fd is ready for `events`.  false = deadline missed.
+inline bool wait_ready(int fd, short events, double deadline_s) {
+  for (;;) {
+    const int ms = poll_ms(deadline_s);
+    if (ms < 0) { errno = ETIMEDOUT; return false; }
+    pollfd p{fd, events, 0};
+    const int pr = ::poll(&p, 1, ms);
+    if (pr > 0 || (pr < 0 && errno != EINTR)) return true;  // ready, or let the I/O call report the error
+  }
+}
+
+// Write exactly n bytes. Returns false on a closed/broken socket (or a missed deadline).
+inline bool send_all(int fd, const void* buf, size_t n, double deadline_s = 0) {
   const char* p = static_cast<const char*>(buf);
   while (n > 0) {
-    ssize_t k = ::send(fd, p, n, MSG_NOSIGNAL);
+    if (deadline_s > 0 && !wait_ready(fd, POLLOUT, deadline_s)) return false;
+    ssize_t k = ::send(fd, p, n, MSG_NOSIGNAL | (deadline_s > 0 ? MSG_DONTWAIT : 0));
     if (k < 0) {
-      if (errno == EINTR) continue;
+      if (errno == EINTR || errno == EAGAIN || errno == EWOULDBLOCK) continue;
       return false;
     }
     p += k;
@@ -43,13 +64,14 @@ inline bool send_all(int fd, const void* buf, size_t n) {
   return true;
 }
 
-inline bool recv_all(int fd, void* buf, size_t n) {
+inline bool recv_all(int fd, void* buf, size_t n, double deadline_s = 0) {
   char* p = static_cast<char*>(buf);
   while (n > 0) {
-    ssize_t k = ::recv(fd, p, n, 0);
-    if (k == 0) return false;
+    if (deadline_s > 0 && !wait_ready(fd, POLLIN, deadline_s)) return false;
+    ssize_t k = ::recv(fd, p, n, deadline_s > 0 ? MSG_DONTWAIT : 0);
+    if (k == 0) { errno = ECONNRESET; return false; }
     if (k < 0) {
-      if (errno == EINTR) continue;
+      if (errno == EINTR || errno == EAGAIN || errno == EWOULDBLOCK) continue;
       return false;
     }
     p += k;
@@ -60,7 +82,7 @@ inline bool recv_all(int fd, void* buf, size_t n) {
 
 // Full-duplex exchange on (possibly different) sockets without deadlocking on
 // full kernel buffers: progress whichever direction is ready.
-inline bool send_recv(int send_fd, const void* sbuf, size_t sn, int recv_fd, void* rbuf, size_t rn) {
+inline bool send_recv(int send_fd, const void* sbuf, size_t sn, int recv_fd, void* rbuf, size_t rn, double deadline_s = 0) {
   const char* sp = static_cast<const char*>(sbuf);
   char* rp = static_cast<char*>(rbuf);
   while (sn > 0 || rn > 0) {
@@ -68,7 +90,9 @@ inline bool send_recv(int send_fd, const void* sbuf, size_t sn, int recv_fd, voi
     int nf = 0, si = -1, ri = -1;
     if (sn > 0) { fds[nf] = {send_fd, POLLOUT, 0}; si = nf++; }
     if (rn > 0) { fds[nf] = {recv_fd, POLLIN, 0}; ri = nf++; }
-    int pr = ::poll(fds, nf, 60000);
+    const int ms = poll_ms(deadline_s);
+    if (ms < 0) { errno = ETIMEDOUT; return false; }
+    int pr = ::poll(fds, nf, ms);
     if (pr < 0) { if (errno == EINTR) continue; return false; }
     if (pr == 0) continue;
     if (si >= 0 && (fds[si].revents & (POLLOUT | POLLERR | POLLHUP))) {

@@ -168,8 +168,11 @@ class CpuProcessGroup(ProcessGroup):
         if not self._comm:
             raise RuntimeError("CPU backend: could not connect the ranks of group %r" % name)
         self._lock = threading.Lock()
+        self._timeout_s = float(timeout_s)
 
     def _check(self, rc, what):
+        if rc == -2:  # the group's timeout (init_process_group(timeout=...)) bounds every collective, like NCCL's watchdog
+            raise RuntimeError("CPU backend: %s timed out after %.0f s (a peer is alive but did not join the collective)" % (what, self._timeout_s))
         if rc != 0:
             raise RuntimeError("CPU backend: %s failed (a peer exited or the connection dropped)" % what)
 

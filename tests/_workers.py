@@ -23,6 +23,30 @@ def _init(rank, world, port, method="env"):
         dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, world_size=world, rank=rank)
 
 
+def stuck_peer(rank, world, port, outdir, mode):
+    """Rank 1 never joins the second allreduce: it sleeps ("stuck") or exits ("dead").  Rank 0 must get an error, not hang."""
+    import time
+    from datetime import timedelta
+
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", init_method="env://", world_size=world, rank=rank, timeout=timedelta(seconds=3))
+    t = torch.ones(4)
+    dist.all_reduce(t)  # everyone takes part in the first one
+    if rank == 1:
+        if mode == "stuck":
+            time.sleep(12)
+        os._exit(0)
+    t0 = time.time()
+    try:
+        dist.all_reduce(t)
+        msg = "no error"
+    except RuntimeError as e:
+        msg = str(e)
+    with open(os.path.join(outdir, "r0.txt"), "w") as f:
+        f.write("%.1f|%s" % (time.time() - t0, msg))
+    os._exit(0)
+
+
 def collectives(rank, world, port, method, outdir):
     _init(rank, world, port, method)
     res = {}

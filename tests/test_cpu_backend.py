@@ -64,3 +64,15 @@ def test_gather_scatter_reduce_scatter(tmp_path):
         if r == 1:
             assert res["gather"].tolist() == [[float(i + 1)] * 2 for i in range(world)]
         assert res["scatter"].tolist() == [10.0 * r] * 2
+
+
+@pytest.mark.parametrize("mode", ["stuck", "dead"])
+def test_collective_fails_instead_of_hanging(tmp_path, mode):
+    """A peer that is alive but never joins is reported after the group's timeout (3 s here); a peer that exited is
+    reported at once.  (torch gets the former from its watchdog, the latter from the broken connection.)"""
+    pdl.multiprocessing.spawn(_workers.stuck_peer, args=(2, free_port(), str(tmp_path), mode), nprocs=2)
+    waited, msg = (tmp_path / "r0.txt").read_text().split("|", 1)
+    if mode == "stuck":
+        assert "timed out after 3 s" in msg and 2.5 <= float(waited) < 9.0, (waited, msg)
+    else:
+        assert "a peer exited" in msg and float(waited) < 3.0, (waited, msg)
