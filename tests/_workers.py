@@ -34,7 +34,7 @@ def stuck_peer(rank, world, port, outdir, mode):
     dist.all_reduce(t)  # everyone takes part in the first one
     if rank == 1:
         if mode == "stuck":
-            time.sleep(12)
+            time.sleep(8)
         os._exit(0)
     t0 = time.time()
     try:

@@ -122,7 +122,7 @@ def test_launch_max_restarts_runs_the_group_again(tmp_path):
     assert p.returncode == 0, p.stdout[-2000:]
     assert "restarting the worker group (attempt 1 of 2)" in p.stdout
     assert "rank 0 done on attempt 1 sum 3" in p.stdout and "rank 1 done on attempt 1 sum 3" in p.stdout
-    env["FAIL_UNTIL"] = "5"  # keeps failing: two restarts, then the failure is final
-    cmd[-2] = "--master_port=%d" % free_port()
+    env["FAIL_UNTIL"] = "5"  # keeps failing: one restart, then the failure is final
+    cmd[-2], cmd[-3] = "--master_port=%d" % free_port(), "--max_restarts=1"
     p = subprocess.run(cmd, cwd=ROOT, env=env, timeout=300, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
-    assert p.returncode == 7 and p.stdout.count("restarting the worker group") == 2
+    assert p.returncode == 7 and p.stdout.count("restarting the worker group") == 1
