@@ -26,7 +26,9 @@ def host():
     if _host is None:
         with _lock:
             if _host is None:
-                path = _build.build_host()
+                # PDL_HOST_LIB: load an alternative build of the host runtime (scripts/sanitize_host.sh uses it for the
+                # AddressSanitizer / ThreadSanitizer variants)
+                path = os.environ.get("PDL_HOST_LIB") or _build.build_host()
                 lib = ctypes.CDLL(path)
                 _declare_host(lib)
                 _host = lib
