@@ -83,7 +83,7 @@ class ClockSampler:
                                 self.reasons.add(name)
                     except Exception:
                         pass
-                    self._stop.wait(0.005)
+                    self._stop.wait(0.001)
 
             self.thread = threading.Thread(target=poll, daemon=True)
             self.thread.start()
@@ -114,6 +114,10 @@ class ClockSampler:
         except OSError:
             self.proc = None
 
+    def reset(self):
+        """Forget what was sampled so far (warm-up): the record describes the timed region only."""
+        self.samples, self.reasons = [], set()
+
     def stop(self):
         self._stop.set()
         if self.proc is not None:
@@ -140,6 +144,47 @@ def ensure_reference_tree():
             if os.path.isfile(os.path.join(src, f)):
                 shutil.copy2(os.path.join(src, f), os.path.join(dst, f))
     return dst if os.path.exists(os.path.join(dst, "launch_dist.py")) else None
+
+
+def cross_rank_check(torch, pg, ddp, step_fn, images, labels, rank, world):
+    """What DDP promises (reference README.md:168: every replica holds the same model), checked on the real peers:
+    (a) every rank's parameters are bit-identical after the timed training; (b) for one extra step the raw per-rank
+    gradients are gathered over the CPU mesh, averaged in fp64 on the host, and compared with what the NVLink allreduce
+    kernel left in the averaged arena -- which must also be bit-identical on every rank; (c) no kernel gave up waiting
+    for a peer.  Large models are checked on a strided sample of <= 1M elements per rank."""
+    import hashlib
+
+    import numpy as np
+
+    torch.cuda.synchronize()
+
+    def digest():
+        h = hashlib.sha1()
+        for p in ddp.module.parameters():
+            h.update(p.detach().cpu().contiguous().numpy().tobytes())
+        return h.hexdigest()
+
+    before = pg.allgather_object(digest())
+    step_fn(images, labels)
+    torch.cuda.synchronize()
+    backend = ddp._backend
+    total = int(ddp._total)
+    stride = max(1, total // (1 << 20))
+    raw = backend.g_in[:total:stride].detach().cpu().numpy()
+    avg = backend.g_avg[:total:stride].detach().cpu().numpy()
+    raws = pg.allgather_object(raw)
+    avgs = pg.allgather_object(avg)
+    after = pg.allgather_object(digest())
+    oracle = np.mean(np.stack([r.astype(np.float64) for r in raws]), axis=0)
+    err = max(float(np.max(np.abs(a.astype(np.float64) - oracle))) for a in avgs)
+    scale = float(np.max(np.abs(oracle))) or 1.0
+    avg_same = all(a.tobytes() == avgs[0].tobytes() for a in avgs)
+    moved = after[0] != before[0]  # the extra step really trained
+    timeouts = sum(pg.allgather_object(int(pg.check_device_errors(raise_on_error=False))))
+    identical = len(set(before)) == 1 and len(set(after)) == 1
+    ok = bool(identical and avg_same and moved and timeouts == 0 and err <= 1e-5 * scale + 1e-9)
+    return {"replicas_identical": bool(identical), "averaged_grads_identical": bool(avg_same), "allreduce_max_abs_err": err,
+            "allreduce_grad_scale": scale, "allreduce_checked_elems": int(raw.size), "peer_timeouts": int(timeouts), "cross_rank_ok": ok}
 
 
 def main():
@@ -204,6 +249,12 @@ def main():
         def barrier():
             tdist.barrier()
 
+        _sync_word = torch.zeros(1, device=dev)
+
+        def device_barrier():  # NCCL allreduce on the compute stream: a rendezvous on the device, no host round trip
+            if world > 1:
+                tdist.all_reduce(_sync_word)
+
         def gather_max(v):
             t = torch.tensor([v], dtype=torch.float64, device=dev)
             tdist.all_reduce(t, op=tdist.ReduceOp.MAX)
@@ -229,6 +280,10 @@ def main():
             torch.cuda.synchronize()
             dist.barrier()
 
+        def device_barrier():  # flag kernel over peer memory on the compute stream (B200ProcessGroup.device_barrier)
+            if world > 1:
+                dist._default().device_barrier()
+
         def gather_max(v):
             return max(dist._default().allgather_object(float(v)))
 
@@ -248,27 +303,41 @@ def main():
     dev_y = [t.to(dev) for t in host_y[:dev_pool]]
 
     # ---------------- device-timed run (inputs resident on the GPU) ----------------
+    # Order matters for the 20 x 0.12 ms regions the driver times: everything slow or rank-skewed on the host (NVML
+    # start-up, thread creation, event allocation) happens BEFORE the rendezvous; the last thing in front of
+    # `start.record()` is a barrier executed ON THE DEVICE (ours: a flag kernel over peer memory; reference: NCCL's
+    # barrier allreduce), so every GPU enters the timed region within microseconds of its peers and a late host only
+    # delays its own queue, never another rank's clock.
+    sampler = ClockSampler(local_rank)
+    sampler.start()
     for i in range(max(3, args.warmup)):
         step_fn(dev_x[i % dev_pool], dev_y[i % dev_pool])
     if args.impl == "ours":
         kernels_per_step = train_step.kernels_per_step() or 0
+    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     barrier()
     torch.cuda.synchronize()
-    sampler = ClockSampler(local_rank)
-    sampler.start()
-    start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.reset()
+    device_barrier()
     t_wall0 = time.perf_counter()
     start.record()
     for i in range(args.steps):
         step_fn(dev_x[i % dev_pool], dev_y[i % dev_pool])
+        marks[i].record()
     stop.record()
     torch.cuda.synchronize()
-    barrier()
     wall_ms = (time.perf_counter() - t_wall0) * 1e3
-    dev_ms = start.elapsed_time(stop)
     clocks = sampler.stop()
+    barrier()
+    dev_ms = start.elapsed_time(stop)
+    step_ms = [(start if i == 0 else marks[i - 1]).elapsed_time(marks[i]) for i in range(args.steps)]
     dev_ms = gather_max(dev_ms)
     wall_ms = gather_max(wall_ms)
+    step_ms = [gather_max(v) for v in step_ms] if args.steps <= 64 else step_ms
+    ordered = sorted(step_ms)
+    step_stats = {"p50": ordered[len(ordered) // 2], "p90": ordered[min(len(ordered) - 1, int(len(ordered) * 0.9))], "max": ordered[-1],
+                  "first5": [round(v, 4) for v in step_ms[:5]]}
 
     # ---------------- end to end: pinned host batch -> H2D -> step -> loss D2H, every step ----------------
     # Both arms read every step's loss on the host ONE STEP LATE (step i's value is fetched after step i+1 has been
@@ -281,9 +350,10 @@ def main():
         e2e_step = step_fn
     for i in range(3):
         float(e2e_step(host_x[i % pool], host_y[i % pool]).item())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     torch.cuda.synchronize()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    device_barrier()
     e0.record()
     loss_sum = 0.0
     prev = None
@@ -317,9 +387,10 @@ def main():
             local_step = pdl.TrainStep(twin, criterion, pdl.optim.SGD(twin.parameters(), **opt_kw), use_graph=not args.eager)
         for i in range(max(3, args.warmup)):
             local_step(dev_x[i % dev_pool], dev_y[i % dev_pool])
+        l0, l1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         torch.cuda.synchronize()
-        l0, l1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        device_barrier()
         l0.record()
         for i in range(args.steps):
             local_step(dev_x[i % dev_pool], dev_y[i % dev_pool])
@@ -327,6 +398,11 @@ def main():
         torch.cuda.synchronize()
         barrier()
         local_ms = gather_max(l0.elapsed_time(l1))
+
+    # ---------------- cross-rank correctness (ours, N > 1; outside every timed region) ----------------
+    check = None
+    if args.impl == "ours" and world > 1:
+        check = cross_rank_check(torch, dist._default(), model, step_fn, dev_x[0], dev_y[0], rank, world)
 
     stats = {}
     if args.impl == "ours":
@@ -355,11 +431,16 @@ def main():
         if local_ms is not None:
             out["compute_only_ms_per_step"] = local_ms / args.steps
             out["exposed_comm_ms_per_step"] = max(0.0, (dev_ms - local_ms) / args.steps)
+        out["step_ms"] = step_stats
         if stats:
             out["config"]["allreduce"] = stats.get("algorithms")
+        if check is not None:
+            out.update(check)
         print(json.dumps(out))
         sys.stdout.flush()
     shutdown()
+    if check is not None and not check["cross_rank_ok"]:
+        return 3
     return 0
 
 

@@ -14,23 +14,12 @@
 // Block b of every rank handles the same element range and only synchronises with block b of
 // its peers, so no grid-wide barrier is needed.  After the averaged gradient is final the same
 // threads apply SGD (weight decay, momentum, nesterov) to the local parameters.
-#include "common.cuh"
+#include "comm.cuh"
 
 namespace {
 
-constexpr int kMaxWorld = 8;
-constexpr int kMaxBlocks = 64;
-constexpr int kMaxChannels = 8;
+using namespace pdl_comm;
 constexpr int kThreads = 512;
-
-// Signal pad: flag[channel][block][source rank].  Lives at the start of a symmetric segment.
-__host__ __device__ inline size_t flag_index(int ch, int block, int src) { return (static_cast<size_t>(ch) * kMaxBlocks + block) * kMaxWorld + src; }
-
-struct CommState {  // local (non-symmetric) device memory, one per communicator
-  uint32_t epoch[kMaxChannels];
-  uint32_t finished[kMaxChannels];
-  uint32_t error;  // set to 1 when a peer wait timed out
-};
 
 struct ARParams {
   const float* in[kMaxWorld];   // every rank's raw bucket (own entry = local pointer)
@@ -49,25 +38,6 @@ struct ARParams {
   unsigned long long timeout_ns;
 };
 
-__device__ __forceinline__ void st_release_sys(uint32_t* p, uint32_t v) { asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory"); }
-__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
-  uint32_t v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long globaltimer_ns() {
-  unsigned long long t;
-  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-  return t;
-}
-__device__ __forceinline__ float4 ld_f4(const float* base, long long i) {
-  float4 v;
-  asm volatile("ld.global.relaxed.sys.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(base + 4 * i) : "memory");
-  return v;
-}
-__device__ __forceinline__ void st_f4(float* base, long long i, float4 v) {
-  asm volatile("st.global.relaxed.sys.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(base + 4 * i), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
-}
 __device__ __forceinline__ float4 mc_ld_reduce_f4(const float* base, long long i) {
   float4 v;
   asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
@@ -89,23 +59,21 @@ __device__ __forceinline__ void signal_peers(const ARParams& p, int blk, uint32_
   int t = threadIdx.x;
   if (t < p.world && t != p.rank && (only < 0 || t == only)) st_release_sys(p.pad[t] + flag_index(p.channel, blk, p.rank), v);
 }
-// Wait until the listed source ranks signalled value >= v.
-__device__ __forceinline__ void wait_peers(const ARParams& p, int blk, uint32_t v, int only = -1) {
+// Wait until the listed source ranks signalled value >= v.  Returns false (to every thread of the CTA) when a peer
+// did not show up within the timeout: the caller must then neither publish results nor touch the parameters --
+// whatever it would read from that peer is stale.
+__device__ __forceinline__ bool wait_peers(const ARParams& p, int blk, uint32_t v, int only = -1) {
   int t = threadIdx.x;
-  if (t < p.world && t != p.rank && (only < 0 || t == only)) {
-    const uint32_t* f = p.pad[p.rank] + flag_index(p.channel, blk, t);
-    unsigned long long t0 = 0;
-    uint32_t polls = 0;
-    while (static_cast<int32_t>(ld_acquire_sys(f) - v) < 0) {
-      if ((++polls & 1023u) == 0) {  // consult the clock rarely: the poll itself is the hot path
-        const unsigned long long now = globaltimer_ns();
-        if (t0 == 0) t0 = now;
-        else if (now - t0 > p.timeout_ns) { p.state->error = 1; break; }
-      }
-    }
-  }
-  __syncthreads();
+  int failed = 0;
+  if (t < p.world && t != p.rank && (only < 0 || t == only))
+    failed = poll_flag(p.pad[p.rank] + flag_index(p.channel, blk, t), v, p.timeout_ns, p.state) ? 0 : 1;
+  return __syncthreads_or(failed) == 0;
 }
+#define WAIT_OR_BAIL(...)                                   \
+  if (!wait_peers(__VA_ARGS__)) {                           \
+    retire(p, nblocks, 0, false);                           \
+    return;                                                 \
+  }
 
 template <bool kSgd>
 __device__ __forceinline__ void finish_element(const ARParams& p, long long i, float4 avg, const SgdHyper& h, bool has_mom) {
@@ -162,6 +130,10 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
   const int W = p.world, r = p.rank, tid = threadIdx.x;
   const uint32_t e = p.state->epoch[p.channel];
   const float inv = p.scale;
+  if (p.state->error != 0) {  // a previous collective of this communicator lost a peer: leave gradients and parameters untouched
+    retire(p, nblocks, 0, false);
+    return;
+  }
   SgdHyper h{};
   bool has_mom = false;
   if (kSgd) { h = *p.hyper; has_mom = p.mom != nullptr && h.momentum != 0.0f; }
@@ -189,14 +161,14 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
   if (kAlgo == ONESHOT) {
     long long per = (p.n4 + nblocks - 1) / nblocks, lo = per * blk, hi = min(p.n4, lo + per);
     signal_peers(p, blk, e + 1);
-    wait_peers(p, blk, e + 1);
+    WAIT_OR_BAIL(p, blk, e + 1)
     auto use = [&](long long i, float4 acc) {
       reinterpret_cast<float4*>(p.out[r])[i] = acc;
       finish_element<kSgd>(p, i, acc, h, has_mom);
     };
     if (W <= 4) batched<4>(lo, hi, sum_peers, use); else batched<2>(lo, hi, sum_peers, use);
     signal_peers(p, blk, e + 2);  // "I no longer read your bucket"
-    wait_peers(p, blk, e + 2);
+    WAIT_OR_BAIL(p, blk, e + 2)
     retire(p, nblocks, 2, kSgd);
     return;
   }
@@ -209,7 +181,7 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
 
   if (kAlgo == TWOSHOT || kAlgo == NVLS) {
     signal_peers(p, blk, e + 1);
-    wait_peers(p, blk, e + 1);
+    WAIT_OR_BAIL(p, blk, e + 1)
     if (kAlgo == NVLS) {
       batched<4>(sub_lo(r), sub_hi(r), [&](long long i) { return scale4(mc_ld_reduce_f4(p.mc_in, i), inv); },
                  [&](long long i, float4 acc) { mc_st_f4(p.mc_out, i, acc); });
@@ -222,7 +194,7 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
       if (W <= 4) batched<4>(sub_lo(r), sub_hi(r), sum_peers, push); else batched<2>(sub_lo(r), sub_hi(r), sum_peers, push);
     }
     signal_peers(p, blk, e + 2);  // my slice is in everyone's `out`; I am done reading `in`
-    wait_peers(p, blk, e + 2);
+    WAIT_OR_BAIL(p, blk, e + 2)
     if (kSgd) {
       for (int s = 0; s < W; ++s) batched<4>(sub_lo(s), sub_hi(s), [&](long long i) { return ld_f4(p.out[r], i); }, sgd_use);
     }
@@ -243,7 +215,7 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
                  },
                  [&](long long i, float4 v) { st_f4(p.ring[next], i, v); });
       signal_peers(p, blk, e + 1 + s, next);
-      wait_peers(p, blk, e + 1 + s, prev);
+      WAIT_OR_BAIL(p, blk, e + 1 + s, prev)
     }
     // slice (r+1) is now complete here: average it, keep it, start the all-gather
     {
@@ -256,14 +228,14 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
       signal_peers(p, blk, e + W, next);
     }
     for (int t = 1; t < W - 1; ++t) {
-      wait_peers(p, blk, e + W + t - 1, prev);
+      WAIT_OR_BAIL(p, blk, e + W + t - 1, prev)
       int idx = ((r + 1 - t) % W + W) % W;
       batched<4>(sub_lo(idx), sub_hi(idx), [&](long long i) { return ld_f4(p.out[r], i); }, [&](long long i, float4 v) { st_f4(p.out[next], i, v); });
       signal_peers(p, blk, e + W + t, next);
     }
-    wait_peers(p, blk, e + 2 * W - 2, prev);
+    WAIT_OR_BAIL(p, blk, e + 2 * W - 2, prev)
     signal_peers(p, blk, e + 2 * W - 1);  // full barrier: staging buffers may be reused
-    wait_peers(p, blk, e + 2 * W - 1);
+    WAIT_OR_BAIL(p, blk, e + 2 * W - 1)
     if (kSgd) {
       for (int s = 0; s < W; ++s) batched<4>(sub_lo(s), sub_hi(s), [&](long long i) { return ld_f4(p.out[r], i); }, sgd_use);
     }
@@ -327,7 +299,9 @@ __global__ void __launch_bounds__(kThreads) pull_kernel(CopyParams c) {
   p.state = c.state; p.rank = c.rank; p.world = c.world; p.channel = c.channel; p.timeout_ns = c.timeout_ns;
   const int blk = blockIdx.x, nblocks = gridDim.x;
   const uint32_t e = c.state->epoch[c.channel];
-  if (c.world > 1) { signal_peers(p, blk, e + 1); wait_peers(p, blk, e + 1); }
+  bool alive = c.state->error == 0;
+  if (c.world > 1 && alive) { signal_peers(p, blk, e + 1); alive = wait_peers(p, blk, e + 1); }
+  if (!alive) { retire(p, nblocks, 0, false); return; }
   long long per = (c.n16 + nblocks - 1) / nblocks, lo = per * blk, hi = min(c.n16, lo + per);
   if (c.root >= 0) {
     if (c.rank != c.root)
@@ -336,14 +310,16 @@ __global__ void __launch_bounds__(kThreads) pull_kernel(CopyParams c) {
     for (int q = 0; q < c.world; ++q)
       for (long long i = lo + threadIdx.x; i < hi; i += kThreads) c.dst[q * c.n16 + i] = c.src[q][i];
   }
-  if (c.world > 1) { signal_peers(p, blk, e + 2); wait_peers(p, blk, e + 2); }
-  retire(p, nblocks, c.world > 1 ? 2 : 0, false);
+  if (c.world > 1) { signal_peers(p, blk, e + 2); alive = wait_peers(p, blk, e + 2); }
+  retire(p, nblocks, (c.world > 1 && alive) ? 2 : 0, false);
 }
 
 }  // namespace
 
 // ---- C ABI -------------------------------------------------------------------------------------
 PDL_API int pdl_comm_state_bytes() { return static_cast<int>(sizeof(CommState)); }
+PDL_API int pdl_comm_state_error_offset() { return static_cast<int>(offsetof(CommState, error)); }
+PDL_API int pdl_comm_state_host_error_offset() { return static_cast<int>(offsetof(CommState, host_error)); }
 PDL_API int pdl_signal_pad_bytes() { return static_cast<int>(flag_index(kMaxChannels, 0, 0) * sizeof(uint32_t)); }
 PDL_API int pdl_comm_max_blocks() { return kMaxBlocks; }
 PDL_API int pdl_comm_max_channels() { return kMaxChannels; }

@@ -39,7 +39,11 @@ struct FinalizeArgs {
   long long* num_batches_tracked;
 };
 __device__ void finalize_group(const float* partial, int splits, int C, int cgroup, const FinalizeArgs& f);
-__device__ unsigned int g_bn_done[2048];  // per channel group: CTAs of the running statistics kernel that have published their partials
+// Per channel group: CTAs of the running statistics kernel that have published their partials.  ONE set of counters per
+// device: BatchNorm launches (forward statistics, backward) must be stream-ordered with respect to each other -- two of them
+// overlapping on different streams or graph branches would corrupt each other's last-CTA detection.  This package issues all
+// of them on the compute stream; the rule is repeated in include/pdl_b200.h and INTEGRATION.md.
+__device__ unsigned int g_bn_done[2048];
 
 // Returns true in the LAST CTA of this channel group to finish (its reads of the other CTAs' partials are ordered
 // after their writes); resets the counter for the next launch.  Launches are stream-ordered, so one array suffices.

@@ -4,6 +4,8 @@
 // tcgen05 path has no specialisation, and is the oracle the tensor-core kernels are tested
 // against.  wgrad is split-K over N*P*Q into a scratch buffer followed by a fixed-order
 // second-pass reduction (deterministic), with the bias gradient folded in as one extra column.
+#include <atomic>
+
 #include "igemm_simt.cuh"
 
 namespace {
@@ -153,10 +155,10 @@ PDL_API int pdl_conv2d_wgrad_simt(const float* x, const float* dy, float* dw, fl
 // ------------------------------------------------------------------------------------------------
 // Weight gradient for callers that are not allowed to allocate.
 //
-// Some hosts of this library cannot obtain device memory at the point where they need a wgrad: code
-// running inside a host function enqueued on a stream or in a CUDA callback (the runtime forbids
-// allocation calls there), code that runs while a stream is being captured, and processes in which
-// a framework's pool has already reserved the whole device so a fresh cudaMalloc simply fails.
+// Some hosts of this library cannot obtain device memory at the point where they need a wgrad:
+// processes in which another allocator (a framework's caching pool, a serving runtime's arena) has
+// already reserved the whole device, so a fresh cudaMalloc simply fails; and latency-critical loops
+// that must not call an allocator at all because cudaMalloc/cudaFree may synchronise the device.
 // For them the split-K partial sums live in a fixed array inside the library image instead of a
 // caller-provided buffer.  The array is kNoAllocScratchBytes (8 MiB) and every GPU that loads the
 // library carries it until the process exits; shapes whose partial sums do not fit are refused.
@@ -178,7 +180,8 @@ static __device__ __align__(256) float g_wgrad_noalloc_scratch[kNoAllocScratchBy
 namespace {
 // Device address of g_wgrad_noalloc_scratch per device ordinal.  In host code the symbol's own name is only
 // a host-side shadow, not a device pointer, so it must never be handed to a kernel directly.
-float* g_noalloc_dev_ptr[kNoAllocMaxDevices] = {};
+// Atomic: two host threads may make the first call on a device at the same time; both resolve the same address.
+std::atomic<float*> g_noalloc_dev_ptr[kNoAllocMaxDevices];
 }  // namespace
 
 // Largest scratch requirement (bytes) pdl_conv2d_wgrad_simt_noalloc accepts.
@@ -196,10 +199,10 @@ PDL_API int pdl_conv2d_wgrad_simt_noalloc(const float* x, const float* dy, float
   int dev = -1;
   PDL_CUDA_CHECK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= kNoAllocMaxDevices) { pdl_set_error("wgrad (no-alloc): device ordinal %d out of range", dev); return -11; }
-  if (g_noalloc_dev_ptr[dev] == nullptr) {  // once per device, with that device current
-    float* p = nullptr;
-    PDL_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_wgrad_noalloc_scratch));
-    g_noalloc_dev_ptr[dev] = p;
+  float* scratch = g_noalloc_dev_ptr[dev].load(std::memory_order_acquire);
+  if (scratch == nullptr) {  // once per device, with that device current
+    PDL_CUDA_CHECK(cudaGetSymbolAddress(reinterpret_cast<void**>(&scratch), g_wgrad_noalloc_scratch));
+    g_noalloc_dev_ptr[dev].store(scratch, std::memory_order_release);
   }
-  return pdl_conv2d_wgrad_simt(x, dy, dw, db, g_noalloc_dev_ptr[dev], N, H, W, Cin, Cout, KH, KW, stride, pad, stream);
+  return pdl_conv2d_wgrad_simt(x, dy, dw, db, scratch, N, H, W, Cin, Cout, KH, KW, stride, pad, stream);
 }

@@ -2,10 +2,14 @@
 //   * 2x2 max-pool backward (stride 1 = overlapping windows, or 2) with the preceding ReLU folded in
 //     and the bias gradient of the preceding conv produced as per-CTA partial sums;
 //   * conv1 weight/bias gradient with pool1-backward + ReLU folded into the operand load
-//     (Cin = 1, 25 taps: CUDA cores; dz1 [N][26][26][32] is never materialised).
+//     (Cin = 1, 25 taps: CUDA cores; dz1 [N][26][26][32] is never materialised);
+//   * the same kernel finishing with the cross-GPU exchange of that gradient and the SGD update (the reference's
+//     last gradient -> bucket allreduce -> optimizer.step(), launch_dist.py:91-92): conv1's gradient is the LAST one
+//     backward produces, so whatever reduces it is fully exposed; here the CTA that holds the finished 832 values
+//     pushes them into every peer's inbox over NVLink, raises one flag, and sums the W inbox rows it received.
 // Both are latency-bound at batch 100, so loads are issued branch-free / staged through shared
 // memory to keep many of them in flight.
-#include "common.cuh"
+#include "comm.cuh"
 
 namespace {
 
@@ -70,10 +74,36 @@ constexpr int kC1Threads = 512, kC1Warps = kC1Threads / 32;
 // different banks (with a stride of 32, rows r and r+1 collide and every tap load is a 2-way conflict).
 constexpr int kC1ImgLd = 34;
 constexpr int kC1StageFloats = 30 * kC1ImgLd + 169 * 32 + 169 * 32 / 4;  // img + g + argmax bytes
+
+// Cross-GPU tail of the kernel (kComm): a push-style one-shot allreduce of 832 floats + the SGD update.
+//   inbox[q]  rank q's inbox in symmetric memory: [2 parities][W source ranks][832]; a rank writes its row into EVERY
+//             peer's inbox (fire-and-forget stores), then raises flag[rank] in every peer's pad with st.release.sys.
+//   The receiver polls its LOCAL pad, then reads its LOCAL inbox: no remote load is ever waited for, so the exposed
+//   cost is one NVLink store latency plus the skew between ranks.
+//   One flag round per step is enough because rows alternate between two parities: a rank overwrites parity e&1 again
+//   only in step e+2, after it has seen every peer's flag of step e+1 -- which a peer raises from a kernel that is
+//   stream-ordered after its step-e reads.
+struct TailComm {
+  float* inbox[pdl_comm::kMaxWorld];
+  uint32_t* pad[pdl_comm::kMaxWorld];
+  pdl_comm::CommState* state;
+  float* avg_w;   // averaged gradient out (what param.grad shows), 800 + 32
+  float* avg_b;
+  float* param_w; // parameters / momentum (nullptr: no update)
+  float* param_b;
+  float* mom_w;
+  float* mom_b;
+  SgdHyper* hyper;
+  int rank, world;
+  float scale;
+  unsigned long long timeout_ns;
+};
+
+template <bool kComm>
 __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const float* __restrict__ x, const float* __restrict__ da1,
                                                                        const uint8_t* __restrict__ idx1, const float* __restrict__ a1,
                                                                        float* __restrict__ gw1, float* __restrict__ gb1,
-                                                                       float* __restrict__ partial, int N, int imgs_per_cta) {
+                                                                       float* __restrict__ partial, int N, int imgs_per_cta, TailComm tc) {
   extern __shared__ float c1_smem[];
   float* img = c1_smem;               // [30][kC1ImgLd]
   float* sg = img + 30 * kC1ImgLd;    // [169][32]
@@ -144,11 +174,80 @@ __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const flo
       red4[half * 208 + col4] = s;
     }
     __syncthreads();
+    if (threadIdx.x == 0) g_c1w_done = 0;
+    if (!kComm) {
+      for (int i = threadIdx.x; i < 832; i += kC1Threads) {
+        const float s = red[i] + red[832 + i];
+        if (i < 800) gw1[i] = s; else gb1[i - 800] = s;
+      }
+      return;
+    }
+    using namespace pdl_comm;
+    const int W = tc.world, r = tc.rank;
+    const uint32_t e = tc.state->epoch[0];
+    const bool dead = tc.state->error != 0;  // sticky: an earlier step lost a peer -> leave everything as it is
+    float* row = red + 2 * 832;              // this rank's finished gradient (also the W == 1 "sum")
     for (int i = threadIdx.x; i < 832; i += kC1Threads) {
       const float s = red[i] + red[832 + i];
-      if (i < 800) gw1[i] = s; else gb1[i - 800] = s;
+      row[i] = s;
+      if (i < 800) gw1[i] = s; else gb1[i - 800] = s;  // raw local gradient (bucket `in` view)
     }
-    if (threadIdx.x == 0) g_c1w_done = 0;
+    __syncthreads();
+    if (dead) return;
+    float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (W > 1) {
+      const size_t slot = (static_cast<size_t>(e & 1u) * W + r) * 832;
+      const float4* row4 = reinterpret_cast<const float4*>(row);
+      for (int i = threadIdx.x; i < 208 * W; i += kC1Threads) {  // 208 float4 to each of the W inboxes (own included)
+        const int q = i / 208, j = i % 208;
+        st_f4(tc.inbox[q] + slot, j, row4[j]);
+      }
+      __syncthreads();
+      int failed = 0;
+      if (threadIdx.x < W && threadIdx.x != r) {
+        st_release_sys(tc.pad[threadIdx.x] + flag_index(0, 0, r), e + 1);
+        failed = poll_flag(tc.pad[r] + flag_index(0, 0, threadIdx.x), e + 1, tc.timeout_ns, tc.state) ? 0 : 1;
+      }
+      if (__syncthreads_or(failed)) return;  // a peer is gone: no averaged gradient, no update
+      if (threadIdx.x < 208) {
+        const float* base = tc.inbox[r] + static_cast<size_t>(e & 1u) * W * 832;
+        float4 v[kMaxWorld];
+#pragma unroll
+        for (int q = 0; q < kMaxWorld; ++q)
+          if (q < W) v[q] = ld_f4(base + static_cast<size_t>(q) * 832, threadIdx.x);
+        sum = v[0];
+#pragma unroll
+        for (int q = 1; q < kMaxWorld; ++q)  // fixed rank order: every rank computes the same bits
+          if (q < W) { sum.x += v[q].x; sum.y += v[q].y; sum.z += v[q].z; sum.w += v[q].w; }
+      }
+    } else if (threadIdx.x < 208) {
+      sum = reinterpret_cast<const float4*>(row)[threadIdx.x];
+    }
+    if (threadIdx.x < 208) {
+      const int j = threadIdx.x;
+      float4 avg = make_float4(sum.x * tc.scale, sum.y * tc.scale, sum.z * tc.scale, sum.w * tc.scale);
+      const bool is_w = j < 200;  // float4 200..207 are the 32 bias gradients
+      float4* avg_out = is_w ? reinterpret_cast<float4*>(tc.avg_w) + j : reinterpret_cast<float4*>(tc.avg_b) + (j - 200);
+      *avg_out = avg;
+      if (tc.param_w != nullptr) {
+        const SgdHyper h = *tc.hyper;
+        const bool has_mom = tc.mom_w != nullptr && h.momentum != 0.0f;
+        float4* pp = is_w ? reinterpret_cast<float4*>(tc.param_w) + j : reinterpret_cast<float4*>(tc.param_b) + (j - 200);
+        float4* mp = has_mom ? (is_w ? reinterpret_cast<float4*>(tc.mom_w) + j : reinterpret_cast<float4*>(tc.mom_b) + (j - 200)) : nullptr;
+        float4 w = *pp, m = has_mom ? *mp : make_float4(0.f, 0.f, 0.f, 0.f);
+        w.x = sgd_update(w.x, avg.x, &m.x, h, has_mom);
+        w.y = sgd_update(w.y, avg.y, &m.y, h, has_mom);
+        w.z = sgd_update(w.z, avg.z, &m.z, h, has_mom);
+        w.w = sgd_update(w.w, avg.w, &m.w, h, has_mom);
+        *pp = w;
+        if (has_mom) *mp = m;
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      if (W > 1) tc.state->epoch[0] = e + 1;
+      if (tc.param_w != nullptr) tc.hyper->first_step = 0;
+    }
   }
 }
 
@@ -196,11 +295,45 @@ PDL_API int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_
   const int smem = (kC1StageFloats + kC1Warps * 832) * static_cast<int>(sizeof(float));
   static bool configured = false;
   if (!configured) {
-    PDL_CUDA_CHECK(cudaFuncSetAttribute(conv1_wgrad_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    PDL_CUDA_CHECK(cudaFuncSetAttribute(conv1_wgrad_fused_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  PDL_CUDA_CHECK(launch_dependent(conv1_wgrad_fused_kernel, dim3(c1_blocks(N)), dim3(kC1Threads), smem, stream, x, da1, idx1, a1, gw1, gb1, partial, N,
-                                  c1_imgs_per_cta(N)));
+  PDL_CUDA_CHECK(launch_dependent(conv1_wgrad_fused_kernel<false>, dim3(c1_blocks(N)), dim3(kC1Threads), smem, stream, x, da1, idx1, a1, gw1, gb1,
+                                  partial, N, c1_imgs_per_cta(N), TailComm{}));
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// Bytes of symmetric memory the tail exchange needs behind its signal pad: [2][world][832] floats.
+PDL_API long long pdl_conv1_tail_inbox_bytes(int world) { return 2ll * world * 832 * static_cast<long long>(sizeof(float)); }
+
+// conv1 weight/bias gradient + cross-GPU average (push one-shot over peer memory) + SGD, ONE kernel.
+//   gw1/gb1      raw local gradient (800 / 32 floats)          avg_w/avg_b  averaged gradient out
+//   param_*/mom_*/hyper  SGD operands (param_w NULL: average only; mom_w NULL: no momentum)
+//   inbox/pad    `world` peer-mapped pointers each (inbox: pdl_conv1_tail_inbox_bytes(world); pad: a signal pad of its own --
+//                channel 0 / block 0 of it is used); state: a communicator state used by nothing else.
+// world == 1 skips the exchange (inbox/pad may be NULL).  Calls must be stream-ordered per communicator.
+PDL_API int pdl_conv1_wgrad_fused_comm(const float* x, const float* da1, const uint8_t* idx1, const float* a1, float* gw1, float* gb1, float* partial,
+                                       int N, float* avg_w, float* avg_b, float* param_w, float* param_b, float* mom_w, float* mom_b, void* hyper,
+                                       int rank, int world, float* const* inbox, uint32_t* const* pad, void* state, double scale, double timeout_s,
+                                       cudaStream_t stream) {
+  if (world < 1 || world > pdl_comm::kMaxWorld) { pdl_set_error("conv1 wgrad+allreduce: world %d out of range", world); return -1; }
+  if (world > 1 && (!inbox || !pad || !state)) { pdl_set_error("conv1 wgrad+allreduce: peer pointers missing"); return -1; }
+  if (param_w && !hyper) { pdl_set_error("conv1 wgrad+allreduce: SGD needs hyper-parameters"); return -1; }
+  const int smem = (kC1StageFloats + kC1Warps * 832) * static_cast<int>(sizeof(float));
+  static bool configured = false;
+  if (!configured) {
+    PDL_CUDA_CHECK(cudaFuncSetAttribute(conv1_wgrad_fused_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured = true;
+  }
+  TailComm tc{};
+  for (int q = 0; q < world && world > 1; ++q) { tc.inbox[q] = inbox[q]; tc.pad[q] = pad[q]; }
+  tc.state = static_cast<pdl_comm::CommState*>(state);
+  tc.avg_w = avg_w; tc.avg_b = avg_b; tc.param_w = param_w; tc.param_b = param_b; tc.mom_w = mom_w; tc.mom_b = mom_b;
+  tc.hyper = static_cast<SgdHyper*>(hyper); tc.rank = rank; tc.world = world; tc.scale = static_cast<float>(scale);
+  tc.timeout_ns = static_cast<unsigned long long>(timeout_s * 1e9);
+  PDL_CUDA_CHECK(launch_dependent(conv1_wgrad_fused_kernel<true>, dim3(c1_blocks(N)), dim3(kC1Threads), smem, stream, x, da1, idx1, a1, gw1, gb1,
+                                  partial, N, c1_imgs_per_cta(N), tc));
   PDL_LAUNCH_CHECK();
   return 0;
 }

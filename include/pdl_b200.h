@@ -39,6 +39,11 @@ int pdl_symm_destroy(void* seg);
  * algo: 0 one-shot, 1 two-shot, 2 ring, 3 NVLS multimem.  in/out/ring/pad: `world` peer-mapped pointers.
  * param/mom/hyper non-NULL => the SGD update (weight decay, momentum, nesterov) runs in the same kernel. */
 int pdl_comm_state_bytes(void);
+/* byte offsets inside the communicator state: the sticky error word (1 = a peer wait timed out; every later launch on the
+ * communicator then leaves gradients and parameters untouched), and an optional device-visible pinned host word that the
+ * failing kernel also sets so the host can notice with a plain load */
+int pdl_comm_state_error_offset(void);
+int pdl_comm_state_host_error_offset(void);
 int pdl_signal_pad_bytes(void);
 int pdl_comm_max_blocks(void);
 int pdl_comm_max_channels(void);
@@ -71,13 +76,14 @@ int pdl_conv2d_wgrad_simt(const float* x, const float* dy, float* dw, float* db,
                           int KW, int stride, int pad, cudaStream_t stream);
 
 /* Allocation-free twin of pdl_conv2d_wgrad_simt (no counterpart in the reference; it exists for embedding
- * hosts, not for parity).  Who needs it: code that runs where the CUDA runtime forbids or cannot satisfy an
- * allocation -- host functions and callbacks enqueued on a stream, work issued while a stream is being
- * captured, processes whose device memory is already fully reserved by another allocator.  The split-K
- * partial sums go to an 8 MiB array built into the library (resident on every GPU that loads it, for the life
- * of the process); pdl_conv2d_wgrad_noalloc_max_bytes() is the limit and larger shapes are refused with an
- * error.  The array is shared: calls that can overlap on the GPU race, keep them stream-ordered.  The first
- * call on each device resolves the array's device address; make it before any stream capture starts. */
+ * hosts, not for parity).  Who needs it: processes whose device memory is already fully reserved by another
+ * allocator (a framework's caching pool, a serving runtime's arena), where a fresh cudaMalloc fails, and
+ * latency-critical loops that must stay away from cudaMalloc/cudaFree because those may synchronise the
+ * device.  The split-K partial sums go to an 8 MiB array built into the library (resident on every GPU that
+ * loads it, for the life of the process); pdl_conv2d_wgrad_noalloc_max_bytes() is the limit and larger shapes
+ * are refused with an error.  The array is shared: calls that can overlap on the GPU race, keep them
+ * stream-ordered.  The first call on each device resolves the array's device address; make it before any
+ * stream capture starts.  Safe to call from several host threads. */
 long long pdl_conv2d_wgrad_noalloc_max_bytes(void);
 int pdl_conv2d_wgrad_simt_noalloc(const float* x, const float* dy, float* dw, float* db, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                                   int stride, int pad, cudaStream_t stream);
@@ -163,6 +169,16 @@ int pdl_pool2_bwd_dbias(const float* da, const uint8_t* idx, const float* pooled
                         int stride, cudaStream_t stream);
 int pdl_conv1_wgrad_fused(const float* x, const float* da1, const uint8_t* idx1, const float* a1, float* gw1, float* gb1, float* partial, int N,
                           cudaStream_t stream);
+/* The same kernel finishing with the cross-GPU exchange of its result and the SGD update (reference: the last gradient ->
+ * DDP bucket allreduce -> optimizer.step(), launch_dist.py:91-92).  conv1's gradient is the last one backward produces, so its
+ * reduction cannot overlap anything: the CTA that holds the finished 832 values pushes them into every peer's inbox
+ * (symmetric memory: [2][world][832] floats behind a signal pad of its own), raises ONE flag per peer, sums the rows it
+ * received in rank order and updates conv1's parameters.  world == 1: no exchange.  param_w NULL: average only. */
+long long pdl_conv1_tail_inbox_bytes(int world);
+int pdl_conv1_wgrad_fused_comm(const float* x, const float* da1, const uint8_t* idx1, const float* a1, float* gw1, float* gb1, float* partial,
+                               int N, float* avg_w, float* avg_b, float* param_w, float* param_b, float* mom_w, float* mom_b, void* hyper, int rank,
+                               int world, float* const* inbox, uint32_t* const* pad, void* state, double scale, double timeout_s,
+                               cudaStream_t stream);
 
 /* ---- BatchNorm2d with the block's ReLU / residual add fused in, NHWC rows [M = N*H*W][C]:
  *      y = act(bn(x) [+ residual]) (reference: torchvision resnet18 at example_launch.py:26).

@@ -66,13 +66,6 @@ def nvcc_path():
     return None
 
 
-NVCC_FLAGS = [
-    "-gencode", "arch=compute_100a,code=sm_100a",
-    "-O3", "-std=c++17", "-lineinfo", "--use_fast_math",
-    "-Xcompiler", "-fPIC", "-shared",
-]
-
-
 def build_cuda(force=False, verbose=False):
     """Compile csrc/cuda/*.cu -> libpdl_cuda.so for sm_100a only (no other arch, no PTX fallback)."""
     os.makedirs(NATIVE_DIR, exist_ok=True)

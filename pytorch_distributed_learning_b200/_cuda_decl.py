@@ -29,6 +29,8 @@ def declare(L):
     sig("pdl_symm_destroy", [P])
     # collectives
     sig("pdl_comm_state_bytes", [])
+    sig("pdl_comm_state_error_offset", [])
+    sig("pdl_comm_state_host_error_offset", [])
     sig("pdl_signal_pad_bytes", [])
     sig("pdl_comm_max_blocks", [])
     sig("pdl_comm_max_channels", [])
@@ -89,6 +91,8 @@ def declare(L):
     sig("pdl_pool2_bwd_blocks", [I, I, I, I])
     sig("pdl_pool2_bwd_dbias", [P, P, P, P, P, I, I, I, I, I, P])
     sig("pdl_conv1_wgrad_fused", [P, P, P, P, P, P, P, I, P])
+    sig("pdl_conv1_tail_inbox_bytes", [I], LL)
+    sig("pdl_conv1_wgrad_fused_comm", [P, P, P, P, P, P, P, I, P, P, P, P, P, P, P, I, I, P, P, P, c_double, c_double, P])
     # batch norm
     sig("pdl_bn_scratch_floats", [LL, I], LL)
     sig("pdl_bn_fwd_train", [P, P, P, P, P, P, P, F, F, P, P, P, P, LL, I, I, P])

@@ -36,7 +36,9 @@ class _SoloArena:
         self.p_flat = torch.zeros(off, dtype=torch.float32, device=device)
         self.m_flat = torch.zeros(off, dtype=torch.float32, device=device) if opt_group["momentum"] != 0 else None
         self.state = torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device=device)
-        self.hyper = torch.zeros(8, dtype=torch.float32, device=device)
+        # one device-resident SgdHyper per kernel that applies an update (each clears its own first_step flag): [whole, early, tail]
+        self.hypers = [torch.zeros(8, dtype=torch.float32, device=device) for _ in range(3)]
+        self.hyper = self.hypers[0]
         self.hyper_vals = None
         self.first = 1
         with torch.no_grad():
@@ -50,7 +52,11 @@ class _SoloArena:
                     if old is not None:
                         mv.copy_(old)
                         self.first = 0
-                    optimizer.state[p]["momentum_buffer"] = mv
+                    optimizer.bind_momentum_view(p, mv)
+        optimizer.add_reload_listener(self._on_optimizer_reload)
+
+    def _on_optimizer_reload(self, first):
+        self.hyper_vals, self.first = None, first
 
     def refresh_hyper(self, group):
         vals = (float(group["lr"]), float(group["momentum"]), float(group["dampening"]), float(group["weight_decay"]), int(bool(group["nesterov"])))
@@ -59,16 +65,18 @@ class _SoloArena:
             h[0], h[1], h[2], h[3] = vals[:4]
             hi = h.view(torch.int32)
             hi[4], hi[5] = vals[4], self.first
-            self.hyper.copy_(h)
+            for dev_h in self.hypers:
+                dev_h.copy_(h)
             self.hyper_vals, self.first = vals, 0
 
-    def launch(self, stream_handle):
+    def launch(self, stream_handle, numel=None, which=0):
+        """Fused scale+SGD over the first ``numel`` floats of the arena (default: all of it) -- world size 1, no peers."""
         L = _lib.cuda()
-        n4 = (self.total + 3) // 4
+        n4 = ((self.total if numel is None else numel) + 3) // 4
         ins = (ctypes.c_void_p * 1)(self.g_in.data_ptr())
         outs = (ctypes.c_void_p * 1)(self.g_avg.data_ptr())
         NF._ok(L.pdl_allreduce_launch(0, 0, 1, 0, n4, ins, outs, None, None, None, None, _p(self.p_flat), _p(self.m_flat) if self.m_flat is not None else None,
-                                      _p(self.hyper), _p(self.state), L.pdl_allreduce_blocks(n4, 1, 0), 1.0, 30.0, ctypes.c_void_p(stream_handle)),
+                                      _p(self.hypers[which]), _p(self.state), L.pdl_allreduce_blocks(n4, 1, 0), 1.0, 30.0, ctypes.c_void_p(stream_handle)),
                "fused SGD kernel")
 
 
@@ -96,7 +104,7 @@ class ConvNetEngine:
         owned = {id(p) for p in optimizer.param_groups[0]["params"]}
         if any(id(p) not in owned for p in params.values()):
             return None
-        if ddp is not None and (len(ddp._buckets) != 1 or not getattr(ddp._backend, "supports_fused_sgd", False)):
+        if ddp is not None and (len(ddp._buckets) != 1 or not getattr(ddp._backend, "supports_fused_sgd", False) or not ddp.fused_optimizer):
             return None
         return cls(module, ddp, optimizer)
 
@@ -104,7 +112,6 @@ class ConvNetEngine:
         self.module, self.ddp, self.optimizer = module, ddp, optimizer
         self.params = [dict(module.named_parameters())[n] for n in self.NAMES]
         self.device = self.params[0].device
-        self.group = optimizer.param_groups[0]
         self.L = _lib.cuda()
         if ddp is not None:
             if not ddp._fused_checked:
@@ -126,10 +133,84 @@ class ConvNetEngine:
             self.world = 1
         for p, v in zip(self.params, self.avg_views):
             p.grad = v
+        self._setup_split()
+        optimizer.add_reload_listener(self._on_optimizer_reload)
         self.graphs = {}
         self.kernel_count = 0
         self._branch = torch.cuda.Stream(device=self.device)  # off-critical-path kernels (see _record_tc)
         self._ring = self._d2h = None  # pinned loss ring + its copy stream, created by the first step(pending=True)
+
+    def _on_optimizer_reload(self, first):
+        self._first_cleared = False  # the restored state decides the first-step flags again (see _clear_first_flags)
+
+    @property
+    def group(self):
+        return self.optimizer.param_groups[0]  # looked up every time: load_state_dict() replaces the dict
+
+    # ------------------------------------------------------------------ two-part gradient exchange
+    def _setup_split(self):
+        """The arena is laid out in gradient-arrival order, so conv1's bias+weight gradient (832 floats, the LAST one backward
+        produces) is its tail and everything else a contiguous prefix.  The prefix is exchanged by an allreduce+SGD kernel on
+        the branch stream as soon as conv2's weight gradient is done -- hidden behind conv2's dgrad and conv1's wgrad -- and the
+        tail inside the conv1-wgrad kernel itself (push one-shot over peer memory, csrc/cuda/convnet_bwd.cu).  What stays
+        exposed per step is one NVLink store latency instead of a whole 444 KiB collective after the last kernel."""
+        from ..parallel.ddp import _Bucket
+
+        self.split = None
+        if os.environ.get("PDL_CONVNET_SPLIT", "1") == "0":
+            return
+        flat_in = self.backend.g_in if self.ddp is not None else self.arena.g_in
+        gw1, gb1 = self.g_views[0], self.g_views[1]
+        esz = flat_in.element_size()
+        base = self.bucket.offset if self.ddp is not None else 0
+        total = (self.bucket.offset + self.bucket.numel) if self.ddp is not None else self.arena.total
+        off_b = (gb1.data_ptr() - flat_in.data_ptr()) // esz
+        off_w = (gw1.data_ptr() - flat_in.data_ptr()) // esz
+        if not (off_b + 32 == off_w and off_w + 800 == total and off_b % 4 == 0 and off_b > base):
+            return  # unexpected layout (e.g. a user-forced bucket order): keep the single whole-bucket kernel
+        split = {"early_numel": off_b - base, "inbox": None, "pads": None, "state": None}
+        if self.ddp is not None:
+            early = _Bucket(1000, [], base, off_b - base)
+            early.fused_group, early.first_flag = self.bucket.fused_group, self.bucket.first_flag
+            early.channel = self.backend.reserve_channel()  # launched from the branch stream: never shares flags with the comm stream's buckets
+            tail = _Bucket(1001, [], off_b, 832)
+            tail.fused_group, tail.first_flag = self.bucket.fused_group, self.bucket.first_flag
+            split["early"], split["tail"] = early, tail
+            if self.world > 1:
+                pg, L = self.backend.pg, self.L
+                pad = (L.pdl_signal_pad_bytes() + 4095) // 4096 * 4096
+                seg = pg.new_segment(pad + int(L.pdl_conv1_tail_inbox_bytes(self.world)), want_multicast=False)
+                split["seg"], split["state"] = seg, pg.new_comm_state()
+                split["pads"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r) for r in range(self.world)])
+                split["inbox"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r, pad) for r in range(self.world)])
+        self.split = split
+
+    def _tail_hyper(self):
+        if self.ddp is not None:
+            return self.backend._hyper_for(self.split["tail"])
+        return self.arena.hypers[2]
+
+    def _launch_early(self, stream_handle):
+        if self.ddp is not None:
+            self.backend.launch_bucket_kernel(self.split["early"], self.world, self.ddp.algorithm, stream_handle, fused=True)
+        else:
+            self.arena.launch(stream_handle, numel=self.split["early_numel"], which=1)
+
+    def _launch_conv1_wgrad_comm(self, b, N, st):
+        """conv1 weight gradient + cross-GPU average + SGD in one kernel (the tail of the arena)."""
+        sp = self.split
+        w1, b1 = self.params[0], self.params[1]
+        gw1, gb1 = self.g_views[0], self.g_views[1]
+        aw1, ab1 = self.avg_views[0], self.avg_views[1]
+        mom = self.group["momentum"] != 0
+        mw = _p(self.optimizer.state[w1]["momentum_buffer"]) if mom else None
+        mb = _p(self.optimizer.state[b1]["momentum_buffer"]) if mom else None
+        rank = self.backend.pg.rank() if self.ddp is not None else 0
+        timeout = self.backend.pg.timeout_s if self.ddp is not None else 30.0
+        NF._ok(self.L.pdl_conv1_wgrad_fused_comm(_p(b["x"]), _p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(gw1), _p(gb1), _p(b["c1part"]), N,
+                                                 _p(aw1), _p(ab1), _p(w1), _p(b1), mw, mb, _p(self._tail_hyper()), rank, self.world, sp["inbox"], sp["pads"],
+                                                 _p(sp["state"]) if sp["state"] is not None else None, 1.0 / self.world, timeout, st),
+               "conv1 wgrad + gradient exchange + SGD")
 
     # ------------------------------------------------------------------ buffers + capture
     def _build(self, N):
@@ -195,6 +276,8 @@ class ConvNetEngine:
         return entry
 
     def _record(self, b, N, stream_handle, reduce):
+        if self.use_tc and self.split is not None:
+            return self._record_tc(b, N, stream_handle, reduce)  # the gradient exchange is part of the schedule
         k = self._record_tc(b, N, stream_handle) if self.use_tc else self._record_simt(b, N, stream_handle)
         # gradient averaging + SGD (one kernel; over NVLink when world > 1)
         if reduce:
@@ -205,7 +288,7 @@ class ConvNetEngine:
             k += 1
         return k
 
-    def _record_tc(self, b, N, stream_handle):
+    def _record_tc(self, b, N, stream_handle, reduce=False):
         """Tensor-core path: 15 launches (tcgen05 conv2/conv3 fwd+dgrad+wgrad, fused CUDA-core kernels for the rest).
 
         At batch 100 every kernel is a fraction of one wave and latency-bound, so the step time is the length of the
@@ -264,9 +347,16 @@ class ConvNetEngine:
         branch.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
                                  3, 3, 0, err, sb), "conv2 wgrad"); k += 2
+        if reduce and self.split is not None:
+            # every gradient of the arena's prefix (fc1, conv3, conv2) is final on the branch: exchange + SGD there, hidden
+            # behind the two kernels the main chain still has to run
+            self._launch_early(branch.cuda_stream); k += 1
         ok(L.pdl_tc_conv2d_dgrad(_p(b["dz2"]), _p(b["p2b"]), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 dgrad"); k += 1
-        ok(L.pdl_conv1_wgrad_fused(_p(b["x"]), _p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(gw1), _p(gb1), _p(b["c1part"]), N, st), "conv1 wgrad"); k += 1
-        main.wait_stream(branch)  # join: every gradient is in the bucket before the allreduce
+        if reduce and self.split is not None:
+            self._launch_conv1_wgrad_comm(b, N, st); k += 1
+        else:
+            ok(L.pdl_conv1_wgrad_fused(_p(b["x"]), _p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(gw1), _p(gb1), _p(b["c1part"]), N, st), "conv1 wgrad"); k += 1
+        main.wait_stream(branch)  # join: every gradient is in the bucket before the allreduce / the step ends
         return k
 
     def _record_simt(self, b, N, stream_handle):
@@ -303,8 +393,22 @@ class ConvNetEngine:
     def _refresh_hyper(self):
         if self.ddp is not None:
             self.backend._hyper_for(self.bucket)
+            if self.split is not None:
+                self.backend._hyper_for(self.split["early"])
+                self.backend._hyper_for(self.split["tail"])
         else:
             self.arena.refresh_hyper(self.group)
+
+    def _clear_first_flags(self):
+        """After the first real step every SgdHyper copy -- also the ones whose kernel did not run in this configuration --
+        must say "momentum history exists" (stream-ordered behind the step)."""
+        if self.ddp is not None:
+            tensors = [e["dev"] for e in self.backend._hyper.values()]
+        else:
+            tensors = self.arena.hypers
+        for t in tensors:
+            t.view(torch.int32)[5:6].zero_()
+        self._first_cleared = True
 
     def step(self, images, labels, pending=False):
         """One iteration.  Returns the loss as a device scalar, or (``pending=True``) as a ``PendingLoss`` whose value is
@@ -320,6 +424,8 @@ class ConvNetEngine:
             self._refresh_hyper()
             entry = self.graphs[key] = self._build(N)
         self._refresh_hyper()
+        if self.ddp is not None:
+            self.backend.pg.poll_errors()  # a lost peer reported by an earlier replay's allreduce kernel raises here (one host load)
         main = torch.cuda.current_stream(self.device)
         stager = entry["stager"]
         if not images.is_cuda and not labels.is_cuda:
@@ -337,6 +443,8 @@ class ConvNetEngine:
             main.wait_event(s["read"])
             s["read"] = None
         s["graph"].replay()
+        if not getattr(self, "_first_cleared", False):
+            self._clear_first_flags()
         stager.consumed(slot, main)
         self.kernel_count = entry["kernels"]
         self.last_key = key

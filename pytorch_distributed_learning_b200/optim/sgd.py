@@ -26,10 +26,10 @@ def lookup_optimizer(param):
     opt = _registry.get(id(param))
     if opt is None:
         return None
-    for group in opt.param_groups:
+    for gi, group in enumerate(opt.param_groups):
         for p in group["params"]:
             if p is param:
-                return opt, id(group)
+                return opt, gi  # the group's INDEX: load_state_dict() replaces the dict objects, positions stay
     return None
 
 
@@ -45,6 +45,8 @@ class SGD(torch.optim.SGD):
         self._fused_done = set()  # ids of params already updated by a fused bucket this iteration
         self._attached = []  # (weakref(ddp), bucket, group_id)
         self._native_tables = {}
+        self._momentum_views = {}  # id(param) -> view of a flat momentum arena that fused kernels update in place
+        self._reload_listeners = []  # weak callables(first_step) run after load_state_dict (device-resident hyper-parameters)
 
     def add_param_group(self, param_group):
         super().add_param_group(param_group)
@@ -52,10 +54,54 @@ class SGD(torch.optim.SGD):
             _registry[id(p)] = self
 
     def group_by_id(self, gid):
-        for g in self.param_groups:
-            if id(g) == gid:
-                return g
-        raise KeyError("parameter group no longer exists")
+        """Parameter group by position (``gid`` as returned by ``lookup_optimizer``)."""
+        try:
+            return self.param_groups[gid]
+        except (IndexError, TypeError):
+            raise KeyError("parameter group %r no longer exists" % (gid,)) from None
+
+    # -- flat-arena bookkeeping (called by the fused back ends) ---------------------------
+    def bind_momentum_view(self, param, view):
+        """``view`` (a slice of a flat arena that the fused kernels read and write) IS this parameter's momentum buffer."""
+        self._momentum_views[id(param)] = view
+        self.state[param]["momentum_buffer"] = view
+
+    def unbind_momentum_view(self, param):
+        self._momentum_views.pop(id(param), None)
+
+    def add_reload_listener(self, bound_method):
+        self._reload_listeners.append(weakref.WeakMethod(bound_method))
+
+    def load_state_dict(self, state_dict):
+        """torch's ``load_state_dict`` replaces every group dict and every state tensor.  The fused kernels keep updating the
+        flat arenas, so the loaded momentum is copied INTO the arena views (and the views put back as the state), and whoever
+        mirrors hyper-parameters in device memory is told to upload them again -- a resumed run continues exactly like an
+        uninterrupted one (reference convention: rank-0 ``state_dict`` checkpoints)."""
+        super().load_state_dict(state_dict)
+        have_history = False
+        with torch.no_grad():
+            for group in self.param_groups:
+                for p in group["params"]:
+                    view = self._momentum_views.get(id(p))
+                    st = self.state.get(p)
+                    loaded = st.get("momentum_buffer") if st is not None else None
+                    if loaded is not None:
+                        have_history = True
+                    if view is None:
+                        continue
+                    if loaded is None:
+                        view.zero_()
+                    elif loaded is not view:
+                        view.copy_(loaded)
+                    self.state[p]["momentum_buffer"] = view
+        self._fused_done = set()
+        alive = []
+        for ref in self._reload_listeners:
+            fn = ref()
+            if fn is not None:
+                fn(0 if have_history else 1)
+                alive.append(ref)
+        self._reload_listeners = alive
 
     # -- called by DistributedDataParallel ---------------------------------------------
     def attach_bucket(self, ddp, bucket, params, offsets, group_id):

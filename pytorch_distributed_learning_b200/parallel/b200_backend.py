@@ -124,6 +124,9 @@ class B200ProcessGroup(dist.ProcessGroup):
         self._staging = None
         self._segments = []
         self._comm_stream = None
+        self._comm_states = []
+        self._host_errors = None
+        self._host_error_slots = 0
         if device_index is not None:
             self._ensure_cuda(device_index)
 
@@ -149,11 +152,28 @@ class B200ProcessGroup(dist.ProcessGroup):
         return seg
 
     def new_comm_state(self):
-        st = torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device="cuda:%d" % self._ensure_cuda())
-        if not hasattr(self, "_comm_states"):
-            self._comm_states = []
+        """Device-side state of one communicator (epochs, retire counters, the sticky error word).  The error word is
+        mirrored into a pinned host word that the failing kernel writes itself, so ``poll_errors()`` costs a host load."""
+        L = _lib.cuda()
+        st = torch.zeros(L.pdl_comm_state_bytes(), dtype=torch.uint8, device="cuda:%d" % self._ensure_cuda())
+        if self._host_errors is None:
+            self._host_errors = torch.zeros(64, dtype=torch.int32).pin_memory()
+            self._host_error_slots = 0
+        if self._host_error_slots < self._host_errors.numel():
+            slot = self._host_error_slots
+            self._host_error_slots += 1
+            off = L.pdl_comm_state_host_error_offset()
+            st[off:off + 8].view(torch.int64).fill_(self._host_errors.data_ptr() + 4 * slot)
         self._comm_states.append(weakref.ref(st))  # every communicator state of this group: checked by check_device_errors()
         return st
+
+    def poll_errors(self):
+        """Cheap failure check for the step path (no synchronisation, no copy): raises once a kernel of this group has
+        reported a lost peer through its pinned host word.  Kernels launched after the failure leave gradients and
+        parameters untouched, so the replica stays at its last consistent state."""
+        if self._host_errors is not None and bool(self._host_errors.any()):
+            raise RuntimeError("[rank %d] a device collective of group %r timed out waiting for a peer GPU (PDL_KERNEL_TIMEOUT_S=%gs): a rank "
+                               "died or hung.  Parameters were left as they were before the failed step." % (self.rank(), self.name, self.timeout_s))
 
     def _stage(self):
         if self._staging is None:
@@ -301,9 +321,10 @@ class B200ProcessGroup(dist.ProcessGroup):
         copy per communicator, so it is called at host synchronisation points: ``barrier()``, checkpoints, group
         destruction, or explicitly) and raises.  The data produced by a timed-out kernel is garbage."""
         bad = 0
-        for ref in getattr(self, "_comm_states", []):
+        word = _lib.cuda().pdl_comm_state_error_offset() // 4
+        for ref in self._comm_states:
             st = ref()
-            if st is not None and int(st.view(torch.int32)[-1].item()) != 0:
+            if st is not None and int(st.view(torch.int32)[word].item()) != 0:
                 bad += 1
         if bad and raise_on_error:
             raise RuntimeError("[rank %d] %d device communicator(s) of group %r timed out waiting for a peer GPU (PDL_KERNEL_TIMEOUT_S=%gs): "
@@ -318,8 +339,10 @@ class B200ProcessGroup(dist.ProcessGroup):
         return self._ctl.broadcast(t, src)
 
     def destroy(self):
+        failed = 0
         if self.device_index is not None:
             torch.cuda.synchronize(self.device_index)
+            failed = self.check_device_errors(raise_on_error=False)
         try:
             self._ctl.barrier()
         except Exception:
@@ -329,6 +352,9 @@ class B200ProcessGroup(dist.ProcessGroup):
         self._segments = []
         self._staging = None
         self._ctl.destroy()
+        if failed:
+            raise RuntimeError("[rank %d] group %r is being destroyed after %d of its device communicators lost a peer GPU; results of the "
+                               "last steps are not valid" % (self.rank(), self.name, failed))
 
 
 class B200ReducerBackend:
@@ -351,6 +377,7 @@ class B200ReducerBackend:
         self._bw_end = None
         self._algo_used = {}
         self._attached = []
+        self._reserved_channels = 0
 
     def allocate(self, total, dtype, device, bucket_ranges):
         if dtype != torch.float32:
@@ -371,6 +398,24 @@ class B200ReducerBackend:
         W = pg.size()
         self._pads = _ptr_array([self.seg.ptr(r) for r in range(W)])
 
+    # -- signal-pad channels ------------------------------------------------------------------
+    # A channel is one epoch counter + one set of flag slots.  Two kernels may share a channel only if they can never be in
+    # flight together, i.e. they are ordered on one stream.  DDP's own buckets all run on pg.comm_stream and share the
+    # channels [0, shared); a caller that launches bucket kernels from any other stream takes a private channel from the top.
+    def reserve_channel(self):
+        top = self.L.pdl_comm_max_channels()
+        if self._reserved_channels + 1 >= top:
+            raise RuntimeError("no free signal-pad channel left (%d reserved of %d)" % (self._reserved_channels, top))
+        self._reserved_channels += 1
+        self._launch_cache.clear()
+        return top - self._reserved_channels
+
+    def _channel_of(self, bk):
+        ch = getattr(bk, "channel", None)
+        if ch is not None:
+            return ch
+        return bk.index % (self.L.pdl_comm_max_channels() - self._reserved_channels)
+
     # -- fused optimizer plumbing -----------------------------------------------------------
     def _detach_fused_params(self):
         with torch.no_grad():
@@ -380,6 +425,7 @@ class B200ReducerBackend:
                     st = opt.state.get(p)
                     if st is not None and st.get("momentum_buffer") is not None:
                         st["momentum_buffer"] = st["momentum_buffer"].clone()
+                    opt.unbind_momentum_view(p)
         self._attached = []
         self._hyper = {}
 
@@ -403,9 +449,17 @@ class B200ReducerBackend:
                     if old is not None:
                         mview.copy_(old)
                         had_state = True
-                    opt.state[p]["momentum_buffer"] = mview
+                    opt.bind_momentum_view(p, mview)
+        if not any(o is opt for o, _, _ in self._attached):
+            opt.add_reload_listener(self._on_optimizer_reload)
         self._attached.append((opt, group, list(params)))
         return {"first": 0 if had_state else 1}
+
+    def _on_optimizer_reload(self, first):
+        """``optimizer.load_state_dict`` ran: upload every device-resident SgdHyper again (new learning rate etc.), with the
+        first-step flag saying whether the restored state carries momentum history."""
+        for entry in self._hyper.values():
+            entry["vals"], entry["first"] = None, first
 
     def _hyper_for(self, bk):
         """Device-resident SgdHyper of a bucket, re-uploaded only when the optimizer's numbers change."""
@@ -446,7 +500,7 @@ class B200ReducerBackend:
                 "ring": _ptr_array([seg.ptr(r, self.pad_bytes + 2 * self.area + off) for r in range(W)]),
                 "mc_in": ctypes.c_void_p(seg.mc_ptr + self.pad_bytes + off) if seg.mc_ptr else None,
                 "mc_out": ctypes.c_void_p(seg.mc_ptr + self.pad_bytes + self.area + off) if seg.mc_ptr else None,
-                "channel": bk.index % self.L.pdl_comm_max_channels(),
+                "channel": self._channel_of(bk),
             }
             self._launch_cache[key] = c
             self._algo_used[bk.index] = ALGO_NAMES[algo]
@@ -466,13 +520,14 @@ class B200ReducerBackend:
                                            c["mc_in"], c["mc_out"], param, mom, hyper, ctypes.c_void_p(self.state.data_ptr()), c["blocks"],
                                            1.0 / world, self.pg.timeout_s, ctypes.c_void_p(stream_handle)), "bucket allreduce kernel")
 
-    def reduce_bucket(self, bk, world, algorithm):
+    def reduce_bucket(self, bk, world, algorithm, fused=None):
         comm = self.pg.comm_stream
         cur = torch.cuda.current_stream(self.device)
         ready = torch.cuda.Event()
         ready.record(cur)
         comm.wait_event(ready)
-        fused = bk.fused_group is not None
+        if fused is None:
+            fused = bk.fused_group is not None
         with torch.cuda.stream(comm):
             self.launch_bucket_kernel(bk, world, algorithm, comm.cuda_stream, fused)
         done = torch.cuda.Event(enable_timing=self.collect_stats)
@@ -483,6 +538,7 @@ class B200ReducerBackend:
             opt.mark_fused_done(bk.fused_params)
 
     def finish(self, buckets):
+        self.pg.poll_errors()  # one host load: a lost peer reported by an earlier step's kernel raises here
         cur = torch.cuda.current_stream(self.device)
         if self.collect_stats:
             self._bw_end = torch.cuda.Event(enable_timing=True)

@@ -58,10 +58,14 @@ def compute_bucket_assignment_by_size(sizes_bytes, limits, kinds=None):
 
 
 class _Bucket:
-    __slots__ = ("index", "param_ids", "offset", "numel", "launched", "fused_group", "fused_params", "first_flag", "grads")
+    __slots__ = ("index", "param_ids", "offset", "numel", "launched", "fused_group", "fused_params", "first_flag", "grads", "channel")
 
     def __init__(self, index, param_ids, offset, numel):
         self.index, self.param_ids, self.offset, self.numel = index, param_ids, offset, numel
+        # signal-pad channel (epoch counter + flag slots).  None = assigned by the backend: DDP launches every bucket on the ONE
+        # communication stream, where sharing a channel is safe because the kernels are stream-ordered.  Anything launched from
+        # another stream must own its channel (B200ReducerBackend.reserve_channel).
+        self.channel = None
         self.launched = False  # pending counts and the launch order live in the C++ reducer core (reducer.py)
         self.fused_group, self.fused_params, self.first_flag = None, (), 1
         self.grads = {}
@@ -99,8 +103,17 @@ def _align(n, a=_ALIGN_ELEMS):
 class DistributedDataParallel(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True, process_group=None,
                  bucket_cap_mb=25, find_unused_parameters=False, check_reduction=False, gradient_as_bucket_view=True,
-                 static_graph=False, algorithm=None, first_bucket_mb=1):
+                 static_graph=False, algorithm=None, first_bucket_mb=1, fused_optimizer=None):
+        """``fused_optimizer`` (default on; ``PDL_FUSED_OPTIMIZER=0`` or ``False`` turns it off): when the parameters belong to
+        this package's ``optim.SGD`` the bucket kernel applies the update itself, i.e. the weights change DURING
+        ``loss.backward()`` and ``optimizer.step()`` has nothing left to do.  Anything placed between ``backward()`` and
+        ``step()`` -- gradient clipping, edits of ``.grad``, skipping the step on a NaN -- needs ``fused_optimizer=False``:
+        the kernel then only averages, ``.grad`` holds the averaged gradient and ``step()`` performs the whole update, exactly
+        like the reference's loop (launch_dist.py:91-92)."""
         super().__init__()
+        if fused_optimizer is None:
+            fused_optimizer = os.environ.get("PDL_FUSED_OPTIMIZER", "1") != "0"
+        self.fused_optimizer = bool(fused_optimizer)
         self.process_group = process_group if process_group is not None else dist._default()
         params = [(n, p) for n, p in module.named_parameters() if p.requires_grad]
         if not params:
@@ -301,11 +314,13 @@ class DistributedDataParallel(nn.Module):
 
     def _launch_bucket_impl(self, bk):
         srcs, dsts = [], []
+        unused = []
         for i in bk.param_ids:
             g = bk.grads.get(i)
             view = self._in_views[i]
             if g is None:  # parameter took no part in this backward: contributes zeros
                 view.zero_()
+                unused.append(i)
             elif g.data_ptr() != view.data_ptr():
                 srcs.append(g)
                 dsts.append(view)
@@ -316,13 +331,20 @@ class DistributedDataParallel(nn.Module):
             return
         if not self._fused_checked:
             self._resolve_fused_optimizers()
-        self._backend.reduce_bucket(bk, self._world, self.algorithm)
+        # A parameter without a gradient must not be touched by the optimizer (torch skips ``grad is None``: no weight decay,
+        # no momentum step).  The fused kernel updates whole buckets, so such a bucket is only averaged this iteration and
+        # optimizer.step() updates the parameters that did receive a gradient.
+        fused = bk.fused_group is not None and not unused
+        self._backend.reduce_bucket(bk, self._world, self.algorithm, fused=fused) if bk.fused_group is not None else \
+            self._backend.reduce_bucket(bk, self._world, self.algorithm)
+        skip = set(unused)
         for i in bk.param_ids:
-            self._params[i].grad = self._avg_views[i]
+            if i not in skip:
+                self._params[i].grad = self._avg_views[i]
         bk.launched = True
         bk.grads.clear()
         self._stats["buckets_launched"] += 1
-        if bk.fused_group is not None:
+        if fused:
             self._stats["fused_buckets"] += 1
 
     def _finalize_backward(self):
@@ -386,7 +408,7 @@ class DistributedDataParallel(nn.Module):
         """Look up (lazily: the optimizer may be created before or after the wrap, reference
         launch_dist.py:59-61 vs example_launch.py:29,64) which buckets can take the fused update."""
         self._fused_checked = True
-        if not self._backend.supports_fused_sgd:
+        if not self._backend.supports_fused_sgd or not self.fused_optimizer:
             return
         from ..optim.sgd import lookup_optimizer
 

@@ -36,3 +36,49 @@ def test_registry_lookup_and_state_dict_roundtrip():
     opt2.load_state_dict(opt.state_dict())
     assert opt2.param_groups[0]["lr"] == 0.1
     assert torch.equal(opt2.state[w]["momentum_buffer"], torch.ones(3))
+
+
+def test_load_state_dict_refills_flat_momentum_views_and_notifies_mirrors():
+    """What the fused GPU path relies on: after load_state_dict the arena views are still the momentum buffers,
+    hold the loaded values, and whoever mirrors hyper-parameters on the device is told to upload them again."""
+    torch.manual_seed(0)
+    shapes = [(5, 3), (7,)]
+
+    def make():
+        ps = [torch.nn.Parameter(torch.randn(*s)) for s in shapes]
+        opt = pdl.optim.SGD(ps, lr=0.02, momentum=0.9, nesterov=True)
+        flat = torch.zeros(sum(p.numel() for p in ps))
+        off = 0
+        for p in ps:
+            opt.bind_momentum_view(p, flat[off:off + p.numel()].view_as(p))
+            off += p.numel()
+        return ps, opt, flat
+
+    class Mirror:
+        calls = []
+
+        def on_reload(self, first):
+            self.calls.append(first)
+
+    pa, oa, flat_a = make()
+    for _ in range(3):
+        for p in pa:
+            p.grad = torch.randn_like(p)
+        oa.step()
+    assert flat_a.abs().sum() > 0  # step() updated the arena through the views
+    pb, ob, flat_b = make()
+    mirror = Mirror()
+    ob.add_reload_listener(mirror.on_reload)
+    sd = oa.state_dict()
+    sd["param_groups"][0]["lr"] = 0.5
+    ob.load_state_dict(sd)
+    assert torch.equal(flat_b, flat_a)
+    for p in pb:
+        assert ob.state[p]["momentum_buffer"].data_ptr() >= flat_b.data_ptr()
+        assert ob.state[p]["momentum_buffer"].data_ptr() < flat_b.data_ptr() + flat_b.numel() * 4
+    assert mirror.calls == [0]  # history present -> first_step = 0
+    assert ob.group_by_id(pdl.optim.lookup_optimizer(pb[0])[1])["lr"] == 0.5  # groups are found by position after the reload
+    # a state dict without history resets the views and says "first step"
+    fresh = pdl.optim.SGD([torch.nn.Parameter(torch.randn(*s)) for s in shapes], lr=0.1, momentum=0.9).state_dict()
+    ob.load_state_dict(fresh)
+    assert mirror.calls == [0, 1] and flat_b.abs().sum() == 0

@@ -1,11 +1,12 @@
 """The allocation-free wgrad entry point, driven through the C ABI exactly as an embedding host would.
 
-Hosts that may not allocate when they need a weight gradient (code inside stream callbacks or under
-stream capture, processes whose device memory is fully owned by someone else's pool) call
-``pdl_conv2d_wgrad_simt_noalloc``: its split-K partial sums live in a fixed 8 MiB array inside the
-library.  It must give the same numbers as ``pdl_conv2d_wgrad_simt`` (caller-provided scratch), also on
+Hosts that may not allocate when they need a weight gradient (processes whose device memory is fully
+owned by someone else's pool, loops that must not risk the device synchronisation an allocator call can
+cause) call ``pdl_conv2d_wgrad_simt_noalloc``: its split-K partial sums live in a fixed 8 MiB array inside
+the library.  It must give the same numbers as ``pdl_conv2d_wgrad_simt`` (caller-provided scratch), also on
 a second call that finds the previous call's leftovers in the array, and must refuse shapes that do
-not fit.  This file sorts last on purpose: a ``-x`` run has already executed every other test.
+not fit.  The comparison is against the scratch-taking twin, not against torch: the twin itself is
+checked against a strict-fp32 torch oracle in tests/test_gpu_ops.py.  This file sorts last on purpose: a ``-x`` run has already executed every other test.
 """
 import ctypes
 
