@@ -11,6 +11,8 @@
 //   two-shot  rank r reduces slice r, pushes the averaged slice to all peers   2 hops, 2(W-1)/W*S
 //   ring      2(W-1) neighbour steps through a symmetric staging buffer        the textbook ring
 //   nvls      multimem.ld_reduce on own slice + multimem.st broadcast          in-switch reduction
+//   push      every rank STORES its bucket into each peer's inbox, one flag round,     lowest latency: no remote load
+//             then sums the W rows of its LOCAL inbox in rank order                    is ever waited for; (W-1)*S out
 // Block b of every rank handles the same element range and only synchronises with block b of
 // its peers, so no grid-wide barrier is needed.  After the averaged gradient is final the same
 // threads apply SGD (weight decay, momentum, nesterov) to the local parameters.
@@ -33,6 +35,7 @@ struct ARParams {
   SgdHyper* hyper;              // device-resident hyper-parameters
   CommState* state;
   long long n4;                 // bucket length in float4
+  long long row4;               // push only: distance between two inbox rows in float4 (>= n4; fixed per inbox)
   int rank, world, channel;
   float scale;                  // 1/W for gradient averaging, 1 for a plain SUM
   unsigned long long timeout_ns;
@@ -104,7 +107,7 @@ __device__ __forceinline__ void retire(const ARParams& p, int nblocks, uint32_t 
   }
 }
 
-enum Algo : int { ONESHOT = 0, TWOSHOT = 1, RING = 2, NVLS = 3 };
+enum Algo : int { ONESHOT = 0, TWOSHOT = 1, RING = 2, NVLS = 3, PUSH = 4 };
 
 // NVLink round trips are ~2-3 us: a thread must have several independent peer loads in flight.  The loads are
 // volatile asm (program order is kept), so every load of a batch is issued BEFORE the first dependent store.
@@ -170,6 +173,37 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
     signal_peers(p, blk, e + 2);  // "I no longer read your bucket"
     WAIT_OR_BAIL(p, blk, e + 2)
     retire(p, nblocks, 2, kSgd);
+    return;
+  }
+
+  if (kAlgo == PUSH) {
+    // p.ring[q] = rank q's inbox for THIS bucket: [2 parities][W source ranks][n4] float4.  One flag round per launch is
+    // enough because rows alternate between two parities: a rank overwrites parity e&1 again only in launch e+2, after it has
+    // seen every peer's flag of launch e+1 -- raised by a kernel that is stream-ordered after that peer's reads of launch e.
+    long long per = (p.n4 + nblocks - 1) / nblocks, lo = per * blk, hi = min(p.n4, lo + per);
+    const long long row = (static_cast<long long>(e & 1u) * W + r) * p.row4;
+    const float4* mine = reinterpret_cast<const float4*>(p.in[r]);
+    batched<4>(lo, hi, [&](long long i) { return mine[i]; },
+               [&](long long i, float4 v) {
+#pragma unroll
+                 for (int q = 0; q < kMaxWorld; ++q)
+                   if (q < W && q != r) st_f4(p.ring[q], row + i, v);
+               });
+    signal_peers(p, blk, e + 1);
+    WAIT_OR_BAIL(p, blk, e + 1)
+    const float* inbox = p.ring[r] + 4 * (static_cast<long long>(e & 1u) * W * p.row4);
+    auto sum_rows = [&](long long i) {  // fixed rank order 0..W-1: every rank computes the same bits
+      float4 acc = r == 0 ? mine[i] : ld_f4(inbox, i);
+#pragma unroll
+      for (int q = 1; q < kMaxWorld; ++q)
+        if (q < W) acc = add4(acc, q == r ? mine[i] : ld_f4(inbox, q * p.row4 + i));
+      return scale4(acc, inv);
+    };
+    batched<2>(lo, hi, sum_rows, [&](long long i, float4 acc) {
+      reinterpret_cast<float4*>(p.out[r])[i] = acc;
+      finish_element<kSgd>(p, i, acc, h, has_mom);
+    });
+    retire(p, nblocks, 1, kSgd);
     return;
   }
 
@@ -279,6 +313,8 @@ int launch_algo(K kernel, const P& p, int blocks, cudaStream_t stream, bool coop
     case 5: return launch_algo(KERNEL<RING, true>, P, BLOCKS, stream, COOP);                           \
     case 6: return launch_algo(KERNEL<NVLS, false>, P, BLOCKS, stream, COOP);                          \
     case 7: return launch_algo(KERNEL<NVLS, true>, P, BLOCKS, stream, COOP);                           \
+    case 8: return launch_algo(KERNEL<PUSH, false>, P, BLOCKS, stream, COOP);                          \
+    case 9: return launch_algo(KERNEL<PUSH, true>, P, BLOCKS, stream, COOP);                           \
     default: pdl_set_error("unknown allreduce algorithm %d", algo); return -1;                         \
   }
 
@@ -331,32 +367,45 @@ PDL_API int pdl_allreduce_blocks(long long n4, int world, int algo) {
   long long per_block = 1024;  // float4 per CTA: two per thread, all of a thread's peer loads in flight at once
   long long b = (n4 + per_block - 1) / per_block;
   if (b < 1) b = 1;
-  int cap = kMaxBlocks;
+  int cap = 64;  // the default rule; the measured table (parallel/allreduce_table.json) may ask for up to kMaxBlocks
   if (b > cap) b = cap;
   (void)world;
   return static_cast<int>(b);
 }
 
-// Launch one bucket allreduce (+ optional fused SGD) on `stream`.
-//  in/out/ring/pad: arrays of `world` peer-mapped base pointers (already offset to the bucket / pad)
-PDL_API int pdl_allreduce_launch(int algo, int rank, int world, int channel, long long n4, const float* const* in, float* const* out,
-                                 float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, float* param, float* mom,
-                                 void* hyper, void* state, int blocks, double scale, double timeout_s, cudaStream_t stream) {
+// Launch one bucket allreduce (+ optional fused SGD) on `stream`.  (pdl_allreduce_launch_ex: the same with an explicit inbox
+// row distance for the push variant, for inboxes shared by launches of different lengths.)
+//  in/out/ring/pad: arrays of `world` peer-mapped base pointers (already offset to the bucket / pad).
+//  ring: the ring variant's staging buffer (n4 float4 per rank); for the push variant the bucket's inbox,
+//  pdl_allreduce_push_inbox_bytes(n4, world) per rank, used by no other bucket.
+PDL_API long long pdl_allreduce_push_inbox_bytes(long long n4, int world) { return 2ll * world * n4 * 16; }
+
+PDL_API int pdl_allreduce_launch_ex(int algo, int rank, int world, int channel, long long n4, long long inbox_row4, const float* const* in,
+                                    float* const* out, float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, float* param,
+                                    float* mom, void* hyper, void* state, int blocks, double scale, double timeout_s, cudaStream_t stream) {
   if (world > kMaxWorld) { pdl_set_error("allreduce: world %d > %d", world, kMaxWorld); return -1; }
   if (channel < 0 || channel >= kMaxChannels) { pdl_set_error("allreduce: bad channel %d", channel); return -1; }
   if (blocks < 1 || blocks > kMaxBlocks) { pdl_set_error("allreduce: bad block count %d", blocks); return -1; }
   if (algo == NVLS && (!mc_in || !mc_out)) { pdl_set_error("allreduce: nvls needs multicast pointers"); return -1; }
-  if (algo == RING && world > 1 && !ring) { pdl_set_error("allreduce: ring needs staging buffers"); return -1; }
+  if ((algo == RING || algo == PUSH) && world > 1 && !ring) { pdl_set_error("allreduce: ring/push need their staging buffers"); return -1; }
   ARParams p{};
   for (int q = 0; q < world; ++q) {
     p.in[q] = in[q]; p.out[q] = out[q]; p.pad[q] = pad ? pad[q] : nullptr; p.ring[q] = ring ? ring[q] : nullptr;
   }
   p.mc_in = mc_in; p.mc_out = mc_out; p.param = param; p.mom = mom;
   p.hyper = static_cast<SgdHyper*>(hyper); p.state = static_cast<CommState*>(state);
-  p.n4 = n4; p.rank = rank; p.world = world; p.channel = channel; p.scale = static_cast<float>(scale);
+  if (algo == PUSH && inbox_row4 < n4) { pdl_set_error("allreduce: push inbox rows (%lld float4) shorter than the bucket (%lld)", inbox_row4, n4); return -1; }
+  p.n4 = n4; p.row4 = inbox_row4; p.rank = rank; p.world = world; p.channel = channel; p.scale = static_cast<float>(scale);
   p.timeout_ns = static_cast<unsigned long long>(timeout_s * 1e9);
   const bool sgd = param != nullptr;
   DISPATCH_ALGO(allreduce_kernel, p, blocks, false)
+}
+
+PDL_API int pdl_allreduce_launch(int algo, int rank, int world, int channel, long long n4, const float* const* in, float* const* out,
+                                 float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, float* param, float* mom,
+                                 void* hyper, void* state, int blocks, double scale, double timeout_s, cudaStream_t stream) {
+  return pdl_allreduce_launch_ex(algo, rank, world, channel, n4, n4, in, out, ring, pad, mc_in, mc_out, param, mom, hyper, state, blocks, scale,
+                                 timeout_s, stream);
 }
 
 // Test harness: run `world` virtual ranks on ONE GPU in a single cooperative launch.
@@ -373,7 +422,7 @@ PDL_API int pdl_allreduce_emulated(int algo, int world, long long n4, const floa
     for (int q = 0; q < world; ++q) { p.in[q] = in[q]; p.out[q] = out[q]; p.ring[q] = ring ? ring[q] : nullptr; p.pad[q] = pad[q]; }
     p.param = sgd ? param[v] : nullptr; p.mom = (sgd && mom) ? mom[v] : nullptr;
     p.hyper = hyper ? static_cast<SgdHyper*>(hyper[v]) : nullptr; p.state = static_cast<CommState*>(state[v]);
-    p.n4 = n4; p.rank = v; p.world = world; p.channel = 0; p.scale = 1.0f / world; p.timeout_ns = 5ull * 1000000000ull;
+    p.n4 = n4; p.row4 = n4; p.rank = v; p.world = world; p.channel = 0; p.scale = 1.0f / world; p.timeout_ns = 5ull * 1000000000ull;
   }
   DISPATCH_ALGO(allreduce_emulated_kernel, ep, blocks * world, true)
 }

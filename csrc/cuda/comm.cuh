@@ -9,7 +9,7 @@
 namespace pdl_comm {
 
 constexpr int kMaxWorld = 8;
-constexpr int kMaxBlocks = 64;
+constexpr int kMaxBlocks = 128;
 constexpr int kMaxChannels = 8;
 
 // Signal pad: flag[channel][block][source rank].  Lives at the start of a symmetric segment.

@@ -184,8 +184,8 @@ __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const flo
     }
     using namespace pdl_comm;
     const int W = tc.world, r = tc.rank;
-    const uint32_t e = tc.state->epoch[0];
-    const bool dead = tc.state->error != 0;  // sticky: an earlier step lost a peer -> leave everything as it is
+    const uint32_t e = W > 1 ? tc.state->epoch[0] : 0u;  // no communicator state without peers
+    const bool dead = W > 1 && tc.state->error != 0;     // sticky: an earlier step lost a peer -> leave everything as it is
     float* row = red + 2 * 832;              // this rank's finished gradient (also the W == 1 "sum")
     for (int i = threadIdx.x; i < 832; i += kC1Threads) {
       const float s = red[i] + red[832 + i];

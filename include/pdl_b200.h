@@ -36,7 +36,9 @@ int pdl_symm_destroy(void* seg);
 
 /* ---- gradient-bucket allreduce fused with 1/W averaging and SGD (reference: loss.backward() ->
  *      DDP bucket allreduce -> optimizer.step(), launch_dist.py:91-92) ----
- * algo: 0 one-shot, 1 two-shot, 2 ring, 3 NVLS multimem.  in/out/ring/pad: `world` peer-mapped pointers.
+ * algo: 0 one-shot, 1 two-shot, 2 ring, 3 NVLS multimem, 4 push (stores into the peers' inboxes, one flag round).
+ * in/out/ring/pad: `world` peer-mapped pointers; `ring` is the ring's staging buffer or, for push, the bucket's own inbox
+ * of pdl_allreduce_push_inbox_bytes(n4, world) bytes per rank.
  * param/mom/hyper non-NULL => the SGD update (weight decay, momentum, nesterov) runs in the same kernel. */
 int pdl_comm_state_bytes(void);
 /* byte offsets inside the communicator state: the sticky error word (1 = a peer wait timed out; every later launch on the
@@ -49,9 +51,14 @@ int pdl_comm_max_blocks(void);
 int pdl_comm_max_channels(void);
 int pdl_sgd_hyper_bytes(void);
 int pdl_allreduce_blocks(long long n4, int world, int algo);
+long long pdl_allreduce_push_inbox_bytes(long long n4, int world);
 int pdl_allreduce_launch(int algo, int rank, int world, int channel, long long n4, const float* const* in, float* const* out,
                          float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, float* param, float* mom, void* hyper,
                          void* state, int blocks, double scale, double timeout_s, cudaStream_t stream);
+/* the same with an explicit distance between inbox rows (push variant; an inbox shared by launches of different lengths) */
+int pdl_allreduce_launch_ex(int algo, int rank, int world, int channel, long long n4, long long inbox_row4, const float* const* in,
+                            float* const* out, float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, float* param,
+                            float* mom, void* hyper, void* state, int blocks, double scale, double timeout_s, cudaStream_t stream);
 /* all `world` ranks as one cooperative launch on one GPU (tests) */
 int pdl_allreduce_emulated(int algo, int world, long long n4, const float* const* in, float* const* out, float* const* ring,
                            uint32_t* const* pad, float* const* param, float* const* mom, void* const* hyper, void* const* state, int blocks,

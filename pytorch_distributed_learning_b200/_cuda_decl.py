@@ -36,7 +36,9 @@ def declare(L):
     sig("pdl_comm_max_channels", [])
     sig("pdl_sgd_hyper_bytes", [])
     sig("pdl_allreduce_blocks", [LL, I, I])
+    sig("pdl_allreduce_push_inbox_bytes", [LL, I], LL)
     sig("pdl_allreduce_launch", [I, I, I, I, LL, P, P, P, P, P, P, P, P, P, P, I, c_double, c_double, P])
+    sig("pdl_allreduce_launch_ex", [I, I, I, I, LL, LL, P, P, P, P, P, P, P, P, P, P, I, c_double, c_double, P])
     sig("pdl_allreduce_emulated", [I, I, LL, P, P, P, P, P, P, P, P, I, P])
     sig("pdl_pull_launch", [I, I, I, I, LL, P, P, P, P, I, c_double, P])
     # optimizer

@@ -22,7 +22,7 @@ from .. import _lib
 from . import distributed as dist
 from ..utils.logging import debug
 
-ALGOS = {"oneshot": 0, "twoshot": 1, "ring": 2, "nvls": 3}
+ALGOS = {"oneshot": 0, "twoshot": 1, "ring": 2, "nvls": 3, "push": 4}
 ALGO_NAMES = {v: k for k, v in ALGOS.items()}
 
 
@@ -89,10 +89,39 @@ def _ptr_array(values):
     return (ctypes.c_void_p * len(values))(*values)
 
 
-def choose_algorithm(nbytes, world, has_multicast, override=None):
-    """Per-bucket variant, from the measured sweep (profiles/allreduce_sweep.md): with NVSwitch multicast the
-    in-switch reduction (NVLS) is the fastest variant at every size on 2 and 8 GPUs; without it the 1-hop
-    one-shot kernel wins for latency-bound buckets and two-shot for everything larger."""
+_TABLE = None
+
+
+def _load_table():
+    """The measured selection table (``allreduce_table.json`` next to this file; written by ``bench/allreduce_sweep.py
+    --emit-table`` on an 8 x B200 NVSwitch box): per world size, ascending size classes, each with the fastest variant and
+    its CTA count -- with NVSwitch multicast and without.  ``PDL_ALLREDUCE_TABLE`` points at another file."""
+    global _TABLE
+    if _TABLE is None:
+        import json
+
+        path = os.environ.get("PDL_ALLREDUCE_TABLE") or os.path.join(os.path.dirname(os.path.abspath(__file__)), "allreduce_table.json")
+        with open(path) as f:
+            raw = json.load(f)
+        _TABLE = {int(w): rows for w, rows in raw["worlds"].items()}
+    return _TABLE
+
+
+def table_row(nbytes, world):
+    table = _load_table()
+    worlds = sorted(table)
+    w = next((x for x in worlds if x >= world), worlds[-1])  # a world size that was not measured uses the next larger one
+    for row in table[w]:
+        if row["max_bytes"] is None or nbytes <= row["max_bytes"]:
+            return row
+    return table[w][-1]
+
+
+def choose_algorithm(nbytes, world, has_multicast, override=None, table=True):
+    """Per-bucket variant from MEASURED bus bandwidth (north star; SURVEY 5.9 "Selection"): the sweep's table says, per world
+    size and size class, which kernel was fastest on this fabric.  ``override`` (``PDL_ALGO`` /
+    ``DistributedDataParallel(algorithm=...)``) wins; ``table=False`` is the rule of thumb used for the process group's own
+    staged collectives (control-plane traffic, not tuned)."""
     if override:
         name = override.lower()
         if name not in ALGOS:
@@ -102,15 +131,31 @@ def choose_algorithm(nbytes, world, has_multicast, override=None):
         return ALGOS[name]
     if world == 1:
         return ALGOS["oneshot"]
+    if table and os.environ.get("PDL_ALLREDUCE_TABLE", "") != "off":
+        row = table_row(nbytes, world)
+        return ALGOS[row["algo"] if has_multicast else row["algo_no_mc"]]
     if has_multicast:
         return ALGOS["nvls"]
     threshold = int(os.environ.get("PDL_ONESHOT_MAX_BYTES", 32 << 10))
     return ALGOS["oneshot"] if nbytes <= threshold else ALGOS["twoshot"]
 
 
+def choose_blocks(nbytes, world, algo, has_multicast, override=None):
+    """CTA count for a bucket kernel: the table's tuned value when the table chose the variant, else the library's rule."""
+    n4 = (nbytes + 15) // 16
+    L = _lib.cuda()
+    if not override and world > 1 and os.environ.get("PDL_ALLREDUCE_TABLE", "") != "off":
+        row = table_row(nbytes, world)
+        name, blocks = (row["algo"], row.get("blocks")) if has_multicast else (row["algo_no_mc"], row.get("blocks_no_mc"))
+        if ALGOS[name] == algo and blocks:
+            return max(1, min(int(blocks), L.pdl_comm_max_blocks(), int(n4)))
+    return L.pdl_allreduce_blocks(n4, world, algo)
+
+
 class B200ProcessGroup(dist.ProcessGroup):
     backend = "b200"
     STAGING_BYTES = 64 << 20
+    PUSH_STAGE_BYTES = 256 << 10  # per-pass payload of the push variant in pg.allreduce (its inbox holds 2 x W rows of this size)
 
     def __init__(self, store, group_rank, ranks, name, master_host, timeout_s, device_index=None):
         super().__init__(store, group_rank, ranks, name)
@@ -271,20 +316,29 @@ class B200ProcessGroup(dist.ProcessGroup):
         recv = seg.tensor(st["pad"] + half, half // 4)
         cap = half // 4 // 2  # floats per pass (second half of the send window is the ring staging area)
         scale = 1.0 if op == dist.ReduceOp.SUM else 1.0 / W
-        for off in range(0, flat.numel(), cap):
-            n = min(cap, flat.numel() - off)
+        ins = _ptr_array([seg.ptr(r, st["pad"]) for r in range(W)])
+        outs = _ptr_array([seg.ptr(r, st["pad"] + half) for r in range(W)])
+        rings = _ptr_array([seg.ptr(r, st["pad"] + cap * 4) for r in range(W)])
+        push_row4 = self.PUSH_STAGE_BYTES // 16
+        off = 0
+        while off < flat.numel():
+            algo = choose_algorithm(min(cap, flat.numel() - off) * 4, W, False, algorithm, table=False)
+            n = min(push_row4 * 4 if algo == ALGOS["push"] else cap, flat.numel() - off)
             n4 = (n + 3) // 4
             send[:n].copy_(flat[off:off + n])
             if n4 * 4 > n:
                 send[n:n4 * 4].zero_()
-            algo = choose_algorithm(n * 4, W, False, algorithm)
             blocks = L.pdl_allreduce_blocks(n4, W, algo)
-            ins = _ptr_array([seg.ptr(r, st["pad"]) for r in range(W)])
-            outs = _ptr_array([seg.ptr(r, st["pad"] + half) for r in range(W)])
-            rings = _ptr_array([seg.ptr(r, st["pad"] + cap * 4) for r in range(W)])
-            _check(L.pdl_allreduce_launch(algo, self.rank(), W, 0, n4, ins, outs, rings, st["pads"], None, None, None, None, None,
-                                          ctypes.c_void_p(st["state"].data_ptr()), blocks, scale, self.timeout_s, self._stream()), "allreduce kernel")
+            aux, row4 = rings, n4
+            if algo == ALGOS["push"]:  # the group's own inbox: fixed rows, so launches of any length <= a row can share it
+                if "push" not in st:
+                    pseg = self.new_segment(int(L.pdl_allreduce_push_inbox_bytes(push_row4, W)), want_multicast=False)
+                    st["push"] = _ptr_array([pseg.ptr(r) for r in range(W)])
+                aux, row4 = st["push"], push_row4
+            _check(L.pdl_allreduce_launch_ex(algo, self.rank(), W, 0, n4, row4, ins, outs, aux, st["pads"], None, None, None, None, None,
+                                             ctypes.c_void_p(st["state"].data_ptr()), blocks, scale, self.timeout_s, self._stream()), "allreduce kernel")
             flat[off:off + n].copy_(recv[:n])
+            off += n
         if work is not tensor:
             tensor.copy_(work)
         return tensor
@@ -493,11 +547,17 @@ class B200ReducerBackend:
             off = bk.offset * 4
             n4 = (bk.numel + 3) // 4
             algo = choose_algorithm(bk.numel * 4, W, bool(seg.mc_ptr), algorithm)
+            ring = [seg.ptr(r, self.pad_bytes + 2 * self.area + off) for r in range(W)]
+            if algo == ALGOS["push"] and W > 1:
+                # the bucket's own inbox ([2][W][n4] float4, collective allocation -- every rank resolves its buckets in the same
+                # order): only with a private inbox does one flag round per launch suffice (csrc/cuda/allreduce.cu, PUSH)
+                inbox = self.pg.new_segment(int(self.L.pdl_allreduce_push_inbox_bytes(n4, W)), want_multicast=False)
+                ring = [inbox.ptr(r) for r in range(W)]
             c = {
-                "algo": algo, "n4": n4, "blocks": self.L.pdl_allreduce_blocks(n4, W, algo),
+                "algo": algo, "n4": n4, "blocks": choose_blocks(bk.numel * 4, W, algo, bool(seg.mc_ptr), algorithm),
                 "in": _ptr_array([seg.ptr(r, self.pad_bytes + off) for r in range(W)]),
                 "out": _ptr_array([seg.ptr(r, self.pad_bytes + self.area + off) for r in range(W)]),
-                "ring": _ptr_array([seg.ptr(r, self.pad_bytes + 2 * self.area + off) for r in range(W)]),
+                "ring": _ptr_array(ring),
                 "mc_in": ctypes.c_void_p(seg.mc_ptr + self.pad_bytes + off) if seg.mc_ptr else None,
                 "mc_out": ctypes.c_void_p(seg.mc_ptr + self.pad_bytes + self.area + off) if seg.mc_ptr else None,
                 "channel": self._channel_of(bk),

@@ -59,6 +59,8 @@ def test_ddp_argument_validation(port):
         with pytest.raises(ValueError, match="device_ids"):
             pdl.DistributedDataParallel(torch.nn.Linear(2, 2), device_ids=[0])
         ddp = pdl.DistributedDataParallel(torch.nn.Linear(2, 2))
+        assert ddp.fused_optimizer  # default on (only GPU buckets of optim.SGD can take it)
+        assert not pdl.DistributedDataParallel(torch.nn.Linear(2, 2), fused_optimizer=False).fused_optimizer
         assert list(ddp.state_dict().keys()) == ["module.weight", "module.bias"]
         ddp(torch.ones(1, 2)).sum().backward()
         assert ddp.get_step_stats()["iterations"] == 1
@@ -77,3 +79,28 @@ def test_register_comm_hook(tmp_path):
     # tiny caps => several buckets per iteration; the hook saw each of them, the last one flagged
     per_iter = len(r0["seen"]) // 2
     assert per_iter >= 2 and r0["seen"][per_iter - 1][1] and not r0["seen"][0][1]
+
+
+def test_unused_parameter_is_left_alone_by_the_optimizer(port):
+    """A parameter that took no part in backward keeps ``grad is None`` and is not decayed (torch skips it)."""
+    dist = pdl.distributed
+    dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%d" % port, world_size=1, rank=0)
+    try:
+        class Two(torch.nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.used, self.unused = torch.nn.Linear(3, 3), torch.nn.Linear(3, 3)
+
+            def forward(self, x):
+                return self.used(x)
+
+        m = Two()
+        before = m.unused.weight.detach().clone()
+        opt = pdl.optim.SGD(m.parameters(), lr=0.1, weight_decay=0.5)
+        ddp = pdl.DistributedDataParallel(m, find_unused_parameters=True)
+        ddp(torch.ones(2, 3)).sum().backward()
+        opt.step()
+        assert m.unused.weight.grad is None and torch.equal(m.unused.weight.detach(), before)
+        assert m.used.weight.grad is not None
+    finally:
+        dist.destroy_process_group()

@@ -198,3 +198,86 @@ def test_resnet18_modules_train_step_matches_torchvision():
     assert cos > 0.99, cos
     for (n, a), (_, b) in zip(ours.named_buffers(), ref.named_buffers()):
         torch.testing.assert_close(a.float(), b.float(), rtol=1e-3, atol=1e-4, msg=lambda m, n=n: "%s: %s" % (n, m))
+
+
+def test_ddp_unfused_optimizer_lets_the_user_edit_gradients():
+    """``fused_optimizer=False``: the bucket kernel only averages, so what the reference's loop leaves room for between
+    ``backward()`` and ``step()`` (launch_dist.py:91-92) -- here gradient clipping -- takes effect exactly as with torch."""
+    dist = pdl.distributed
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % free_port(), world_size=1, rank=0)
+    try:
+        torch.manual_seed(0)
+        model = pdl.models.ConvNet().cuda()
+        ref = RefConvNet().cuda()
+        ref.load_state_dict(copy.deepcopy(model.state_dict()))
+        kw = dict(lr=0.05, momentum=0.9)
+        opt, ropt = pdl.optim.SGD(model.parameters(), **kw), torch.optim.SGD(ref.parameters(), **kw)
+        ddp = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[0], fused_optimizer=False)
+        crit = pdl.nn.CrossEntropyLoss()
+        g = torch.Generator().manual_seed(7)
+        for _ in range(3):
+            x, y = torch.randn(12, 1, 28, 28, generator=g).cuda(), torch.randint(0, 10, (12,), generator=g).cuda()
+            before = [p.detach().clone() for p in model.parameters()]
+            loss = crit(ddp(x), y)
+            opt.zero_grad()
+            loss.backward()
+            torch.cuda.synchronize()
+            assert all(torch.equal(a, p.detach()) for a, p in zip(before, model.parameters())), "backward() must not update the weights"
+            torch.nn.utils.clip_grad_norm_(model.parameters(), 0.05)
+            opt.step()
+            rl = F.cross_entropy(ref(x), y)
+            ropt.zero_grad()
+            rl.backward()
+            torch.nn.utils.clip_grad_norm_(ref.parameters(), 0.05)
+            ropt.step()
+        assert ddp.get_step_stats()["fused_buckets"] == 0
+        for a, b in zip(model.parameters(), ref.parameters()):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=1e-5)
+        step = pdl.TrainStep(ddp, crit, opt)  # still graphable: the captured iteration ends with the stand-alone SGD kernel
+        assert step.graphed and type(step.engine).__name__ == "GenericGraphEngine"
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("wrapped", [False, True])
+def test_resume_from_optimizer_state_dict_matches_uninterrupted_run(wrapped):
+    """Momentum lives in a flat arena that the fused kernels update; ``load_state_dict`` must refill it: a run
+    that is checkpointed after 3 steps and resumed in fresh objects ends where the uninterrupted run ends."""
+    dist = pdl.distributed
+    if wrapped:
+        dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % free_port(), world_size=1, rank=0)
+    try:
+        kw = dict(lr=0.05, momentum=0.9, weight_decay=1e-4, nesterov=True)
+        g = torch.Generator().manual_seed(11)
+        batches = [(torch.randn(16, 1, 28, 28, generator=g).cuda(), torch.randint(0, 10, (16,), generator=g).cuda()) for _ in range(6)]
+
+        def make(state=None):
+            torch.manual_seed(0)
+            m = pdl.models.ConvNet().cuda()
+            if state is not None:
+                m.load_state_dict(state)
+            o = pdl.optim.SGD(m.parameters(), **kw)
+            w = pdl.nn.parallel.DistributedDataParallel(m, device_ids=[0]) if wrapped else m
+            return m, o, pdl.TrainStep(w, pdl.nn.CrossEntropyLoss(), o)
+
+        m_full, _, s_full = make()
+        for x, y in batches:
+            s_full(x, y)
+        m_a, o_a, s_a = make()
+        for x, y in batches[:3]:
+            s_a(x, y)
+        torch.cuda.synchronize()
+        ckpt_model, ckpt_opt = copy.deepcopy(m_a.state_dict()), copy.deepcopy(o_a.state_dict())
+        ckpt_opt["param_groups"][0]["lr"] = kw["lr"]
+        m_b, o_b, s_b = make(ckpt_model)
+        s_b(*batches[0])  # builds the graph and the arenas BEFORE the load (the harder order); then restore both
+        m_b.load_state_dict(ckpt_model)
+        o_b.load_state_dict(ckpt_opt)
+        for x, y in batches[3:]:
+            s_b(x, y)
+        torch.cuda.synchronize()
+        for (n, a), (_, b) in zip(m_full.named_parameters(), m_b.named_parameters()):
+            torch.testing.assert_close(a, b, rtol=1e-5, atol=1e-6, msg=lambda m, n=n: "%s: %s" % (n, m))
+    finally:
+        if wrapped:
+            dist.destroy_process_group()

@@ -158,7 +158,7 @@ def _emulated_allreduce(algo, world, n, sgd, steps=2, blocks=3):
     g = torch.Generator(device="cpu").manual_seed(5)
     ins = [torch.zeros(n4 * 4, device=dev) for _ in range(world)]
     outs = [torch.full((n4 * 4,), float("nan"), device=dev) for _ in range(world)]
-    rings = [torch.zeros(n4 * 4, device=dev) for _ in range(world)]
+    rings = [torch.zeros(n4 * 4 * (2 * world if algo == 4 else 1), device=dev) for _ in range(world)]  # push: the bucket's inbox
     pads = [torch.zeros(L.pdl_signal_pad_bytes() // 4, dtype=torch.int32, device=dev) for _ in range(world)]
     states = [torch.zeros(L.pdl_comm_state_bytes(), dtype=torch.uint8, device=dev) for _ in range(world)]
     p0 = torch.randn(n4 * 4, generator=g)
@@ -184,7 +184,7 @@ def _emulated_allreduce(algo, world, n, sgd, steps=2, blocks=3):
         for v in range(world):
             torch.testing.assert_close(outs[v].cpu().double(), mean, rtol=1e-5, atol=1e-6)
             assert torch.equal(outs[v], outs[0]), "replicas must receive bit-identical averages"
-            assert int(states[v].view(torch.int32)[-1].item()) == 0, "peer wait timed out"
+            assert int(states[v].view(torch.int32)[L.pdl_comm_state_error_offset() // 4].item()) == 0, "peer wait timed out"
         if sgd:
             gg = mean + 1e-3 * ref_p
             ref_m = gg.clone() if step == 0 else 0.9 * ref_m + gg
@@ -194,14 +194,14 @@ def _emulated_allreduce(algo, world, n, sgd, steps=2, blocks=3):
                 assert torch.equal(params[v], params[0])
 
 
-@pytest.mark.parametrize("algo", [0, 1, 2])
+@pytest.mark.parametrize("algo", [0, 1, 2, 4])
 @pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("n", [113674, 1000, 7])
 def test_allreduce_variants_emulated(algo, world, n):
     _emulated_allreduce(algo, world, n, sgd=False)
 
 
-@pytest.mark.parametrize("algo", [0, 1, 2])
+@pytest.mark.parametrize("algo", [0, 1, 2, 4])
 def test_allreduce_fused_sgd_emulated(algo):
     _emulated_allreduce(algo, 4, 113674, sgd=True, steps=3)
 
@@ -209,6 +209,7 @@ def test_allreduce_fused_sgd_emulated(algo):
 def test_allreduce_soak_emulated():
     _emulated_allreduce(0, 8, 4096, sgd=False, steps=200, blocks=4)
     _emulated_allreduce(2, 8, 4096, sgd=False, steps=100, blocks=4)
+    _emulated_allreduce(4, 8, 4096, sgd=False, steps=201, blocks=4)  # push: odd count, so both inbox parities end up reused
 
 
 @pytest.mark.parametrize("shape", [(8, 64, 8, 8), (4, 128, 4, 4), (16, 256, 2, 2), (3, 64, 16, 16), (64, 512, 1, 1)])
