@@ -35,9 +35,11 @@ class _SoloArena:
         self.g_avg = torch.zeros(off, dtype=torch.float32, device=device)
         self.p_flat = torch.zeros(off, dtype=torch.float32, device=device)
         self.m_flat = torch.zeros(off, dtype=torch.float32, device=device) if opt_group["momentum"] != 0 else None
-        self.state = torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device=device)
-        # one device-resident SgdHyper per kernel that applies an update (each clears its own first_step flag): [whole, early, tail]
-        self.hypers = [torch.zeros(8, dtype=torch.float32, device=device) for _ in range(3)]
+        self.states = [torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device=device) for _ in range(4)]
+        self.state = self.states[0]
+        # one device-resident SgdHyper per kernel that applies an update (each clears its own first_step flag):
+        # [whole arena, fc1 part, conv3+conv2 part, conv1 tail]
+        self.hypers = [torch.zeros(8, dtype=torch.float32, device=device) for _ in range(4)]
         self.hyper = self.hypers[0]
         self.hyper_vals = None
         self.first = 1
@@ -69,15 +71,19 @@ class _SoloArena:
                 dev_h.copy_(h)
             self.hyper_vals, self.first = vals, 0
 
-    def launch(self, stream_handle, numel=None, which=0):
-        """Fused scale+SGD over the first ``numel`` floats of the arena (default: all of it) -- world size 1, no peers."""
+    def launch(self, stream_handle, offset=0, numel=None, which=0):
+        """Fused scale+SGD over ``numel`` floats of the arena starting at ``offset`` (default: all of it) -- world size 1, no
+        peers.  Parts launched from different streams use different communicator states (retire counters)."""
         L = _lib.cuda()
         n4 = ((self.total if numel is None else numel) + 3) // 4
-        ins = (ctypes.c_void_p * 1)(self.g_in.data_ptr())
-        outs = (ctypes.c_void_p * 1)(self.g_avg.data_ptr())
-        NF._ok(L.pdl_allreduce_launch(0, 0, 1, 0, n4, ins, outs, None, None, None, None, _p(self.p_flat), _p(self.m_flat) if self.m_flat is not None else None,
-                                      _p(self.hypers[which]), _p(self.state), L.pdl_allreduce_blocks(n4, 1, 0), 1.0, 30.0, ctypes.c_void_p(stream_handle)),
-               "fused SGD kernel")
+        ins = (ctypes.c_void_p * 1)(self.g_in.data_ptr() + 4 * offset)
+        outs = (ctypes.c_void_p * 1)(self.g_avg.data_ptr() + 4 * offset)
+        if which >= len(self.states):
+            raise IndexError(which)
+        mom = ctypes.c_void_p(self.m_flat.data_ptr() + 4 * offset) if self.m_flat is not None else None
+        NF._ok(L.pdl_allreduce_launch(0, 0, 1, 0, n4, ins, outs, None, None, None, None, ctypes.c_void_p(self.p_flat.data_ptr() + 4 * offset), mom,
+                                      _p(self.hypers[which]), _p(self.states[which]), L.pdl_allreduce_blocks(n4, 1, 0), 1.0, 30.0,
+                                      ctypes.c_void_p(stream_handle)), "fused SGD kernel")
 
 
 class ConvNetEngine:
@@ -137,7 +143,8 @@ class ConvNetEngine:
         optimizer.add_reload_listener(self._on_optimizer_reload)
         self.graphs = {}
         self.kernel_count = 0
-        self._branch = torch.cuda.Stream(device=self.device)  # off-critical-path kernels (see _record_tc)
+        self._branch = torch.cuda.Stream(device=self.device)   # off-critical-path kernels (see _record_tc): pack, fc1 wgrad
+        self._branch2 = torch.cuda.Stream(device=self.device)  # conv3 / conv2 weight gradients
         self._ring = self._d2h = None  # pinned loss ring + its copy stream, created by the first step(pending=True)
 
     def _on_optimizer_reload(self, first):
@@ -149,33 +156,40 @@ class ConvNetEngine:
 
     # ------------------------------------------------------------------ two-part gradient exchange
     def _setup_split(self):
-        """The arena is laid out in gradient-arrival order, so conv1's bias+weight gradient (832 floats, the LAST one backward
-        produces) is its tail and everything else a contiguous prefix.  The prefix is exchanged by an allreduce+SGD kernel on
-        the branch stream as soon as conv2's weight gradient is done -- hidden behind conv2's dgrad and conv1's wgrad -- and the
-        tail inside the conv1-wgrad kernel itself (push one-shot over peer memory, csrc/cuda/convnet_bwd.cu).  What stays
-        exposed per step is one NVLink store latency instead of a whole 444 KiB collective after the last kernel."""
+        """The arena is laid out in gradient-arrival order -- fc1 | conv3 | conv2 | conv1 -- so each layer group is a contiguous
+        range.  Instead of ONE exchange after the last gradient (fully exposed: nothing is left to overlap it with), the step
+        exchanges three parts, each the moment it is final, each fused with its SGD update:
+          * fc1            on branch stream A, right behind fc1's weight-gradient kernel;
+          * conv3 + conv2  on branch stream B, behind conv2's weight gradient -- hidden under conv2's dgrad and conv1's wgrad;
+          * conv1 (832 floats, the LAST gradient) inside the conv1-wgrad kernel itself: push one-shot over peer memory
+            (csrc/cuda/convnet_bwd.cu), one NVLink store latency instead of a kernel + two flag rounds.
+        Kernels on different streams can be in flight together, so each part owns a signal-pad channel (and, for the push
+        variant, an inbox)."""
         from ..parallel.ddp import _Bucket
 
         self.split = None
         if os.environ.get("PDL_CONVNET_SPLIT", "1") == "0":
             return
         flat_in = self.backend.g_in if self.ddp is not None else self.arena.g_in
-        gw1, gb1 = self.g_views[0], self.g_views[1]
         esz = flat_in.element_size()
+        off = lambda i: (self.g_views[i].data_ptr() - flat_in.data_ptr()) // esz  # noqa: E731
         base = self.bucket.offset if self.ddp is not None else 0
         total = (self.bucket.offset + self.bucket.numel) if self.ddp is not None else self.arena.total
-        off_b = (gb1.data_ptr() - flat_in.data_ptr()) // esz
-        off_w = (gw1.data_ptr() - flat_in.data_ptr()) // esz
-        if not (off_b + 32 == off_w and off_w + 800 == total and off_b % 4 == 0 and off_b > base):
+        off_fcb, off_c3b, off_c1b, off_c1w = off(7), off(5), off(1), off(0)
+        ok = off_fcb == base and base < off_c3b < off_c1b and off_c1b + 32 == off_c1w and off_c1w + 800 == total \
+            and off_c3b % 4 == 0 and off_c1b % 4 == 0 and off(6) < off_c3b and off_c3b <= off(4) < off_c1b and off_c3b <= off(2) < off_c1b
+        if not ok:
             return  # unexpected layout (e.g. a user-forced bucket order): keep the single whole-bucket kernel
-        split = {"early_numel": off_b - base, "inbox": None, "pads": None, "state": None}
+        split = {"fc": (base, off_c3b - base), "c32": (off_c3b, off_c1b - off_c3b), "inbox": None, "pads": None, "state": None}
         if self.ddp is not None:
-            early = _Bucket(1000, [], base, off_b - base)
-            early.fused_group, early.first_flag = self.bucket.fused_group, self.bucket.first_flag
-            early.channel = self.backend.reserve_channel()  # launched from the branch stream: never shares flags with the comm stream's buckets
-            tail = _Bucket(1001, [], off_b, 832)
-            tail.fused_group, tail.first_flag = self.bucket.fused_group, self.bucket.first_flag
-            split["early"], split["tail"] = early, tail
+            parts = {}
+            for name, index, (o, n) in (("fc", 1000, split["fc"]), ("c32", 1002, split["c32"]), ("tail", 1001, (off_c1b, 832))):
+                bk = _Bucket(index, [], o, n)
+                bk.fused_group, bk.first_flag = self.bucket.fused_group, self.bucket.first_flag
+                parts[name] = bk
+            parts["fc"].channel = self.backend.reserve_channel()   # launched from branch streams: never share flags with the
+            parts["c32"].channel = self.backend.reserve_channel()  # communication stream's buckets or with each other
+            split["parts"] = parts
             if self.world > 1:
                 pg, L = self.backend.pg, self.L
                 pad = (L.pdl_signal_pad_bytes() + 4095) // 4096 * 4096
@@ -183,18 +197,22 @@ class ConvNetEngine:
                 split["seg"], split["state"] = seg, pg.new_comm_state()
                 split["pads"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r) for r in range(self.world)])
                 split["inbox"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r, pad) for r in range(self.world)])
+                for name in ("fc", "c32"):  # resolve variant / CTAs / inbox now: collective allocations stay out of graph capture
+                    self.backend.bucket_launch_args(parts[name], self.world, self.ddp.algorithm)
         self.split = split
 
     def _tail_hyper(self):
         if self.ddp is not None:
-            return self.backend._hyper_for(self.split["tail"])
-        return self.arena.hypers[2]
+            return self.backend._hyper_for(self.split["parts"]["tail"])
+        return self.arena.hypers[3]
 
-    def _launch_early(self, stream_handle):
+    def _launch_part(self, name, stream_handle):
+        """Exchange + SGD of one contiguous part of the arena ("fc" or "c32") on the given stream."""
         if self.ddp is not None:
-            self.backend.launch_bucket_kernel(self.split["early"], self.world, self.ddp.algorithm, stream_handle, fused=True)
+            self.backend.launch_bucket_kernel(self.split["parts"][name], self.world, self.ddp.algorithm, stream_handle, fused=True)
         else:
-            self.arena.launch(stream_handle, numel=self.split["early_numel"], which=1)
+            o, n = self.split[name]
+            self.arena.launch(stream_handle, offset=o, numel=n, which={"fc": 1, "c32": 2}[name])
 
     def _launch_conv1_wgrad_comm(self, b, N, st):
         """conv1 weight gradient + cross-GPU average + SGD in one kernel (the tail of the arena)."""
@@ -303,7 +321,12 @@ class ConvNetEngine:
         main = torch.cuda.ExternalStream(stream_handle, device=self.device)
         fork = os.environ.get("PDL_CONVNET_FORK", "1") != "0"
         branch = self._branch if fork else main
+        # the conv weight gradients do not depend on fc1's: a second branch lets conv3's wgrad start as soon as dz3 exists
+        # instead of queueing behind fc1's 20 us weight-gradient kernel (timeline: profiles/convnet_timeline_w2.txt)
+        branch2 = self._branch2 if fork and os.environ.get("PDL_CONVNET_BRANCHES", "2") != "1" else branch
         sb = ctypes.c_void_p(branch.cuda_stream)
+        sb2 = ctypes.c_void_p(branch2.cuda_stream)
+        exchange = reduce and self.split is not None
         branch.wait_stream(main)
         ok(L.pdl_convnet_pack(_p(w2), _p(w3), _p(wf), _p(b["p2f"]), _p(b["p2b"]), _p(b["p3f"]), _p(b["p3b"]), _p(b["wfp"]), sb), "weight pack"); k += 1
         # forward: conv+bias+ReLU+pool fused per layer
@@ -327,6 +350,8 @@ class ConvNetEngine:
             branch.wait_stream(main)
             ok(L.pdl_fc_bwd_pool3_part(1, _p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
                                        _p(b["db3part"]), N, sb), "fc1 weight gradient"); k += 1
+            if exchange:
+                self._launch_part("fc", branch.cuda_stream); k += 1
             if part2:
                 ok(L.pdl_fc_bwd_pool3_part(2, _p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]),
                                            _p(b["dz3"]), _p(b["db3part"]), N, st), "fc1 dgrad + pool3 backward"); k += 1
@@ -335,28 +360,32 @@ class ConvNetEngine:
                "fc1 + loss"); k += 1
             ok(L.pdl_fc_bwd_pool3_fused(_p(b["a3"]), _p(b["i3"]), _p(b["dlogits"]), _p(b["wfp"]), _p(gwf), _p(gbf), _p(b["fc_scratch"]), _p(b["dz3"]),
                                         _p(b["db3part"]), N, st), "fc1 backward + pool3 backward"); k += 1
-        branch.wait_stream(main)  # dz3 / db3part are ready
+        if exchange and not fork:
+            self._launch_part("fc", branch.cuda_stream); k += 1
+        branch2.wait_stream(main)  # dz3 / db3part are ready
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a2"]), _p(b["dz3"]), _p(gw3), _p(gb3), _p(b["db3part"]), N, _p(b["wg_scratch"]), N, 10, 10, 64, 128, 3, 3, 0,
-                                 err, sb), "conv3 wgrad"); k += 2
+                                 err, sb2), "conv3 wgrad"); k += 2
         if self.fuse_pool2:  # conv3 dgrad with pool2's backward + ReLU mask + bias partials in its epilogue
             ok(L.pdl_tc_conv2d_dgrad_poolbwd(_p(b["dz3"]), _p(b["p3b"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 10, 10, 64, 128,
                                              3, 3, 0, 1, err, st), "conv3 dgrad + pool2 backward"); k += 1
         else:
             ok(L.pdl_tc_conv2d_dgrad(_p(b["dz3"]), _p(b["p3b"]), _p(b["da2"]), N, 10, 10, 64, 128, 3, 3, 0, err, st), "conv3 dgrad"); k += 1
             ok(L.pdl_pool2_bwd_dbias(_p(b["da2"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 11, 11, 64, 1, st), "pool2 backward"); k += 1
-        branch.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
+        branch2.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
-                                 3, 3, 0, err, sb), "conv2 wgrad"); k += 2
-        if reduce and self.split is not None:
-            # every gradient of the arena's prefix (fc1, conv3, conv2) is final on the branch: exchange + SGD there, hidden
-            # behind the two kernels the main chain still has to run
-            self._launch_early(branch.cuda_stream); k += 1
+                                 3, 3, 0, err, sb2), "conv2 wgrad"); k += 2
+        if exchange:
+            # conv3's and conv2's gradients are final on this branch: exchange + SGD here, hidden behind the two kernels the
+            # main chain still has to run
+            self._launch_part("c32", branch2.cuda_stream); k += 1
         ok(L.pdl_tc_conv2d_dgrad(_p(b["dz2"]), _p(b["p2b"]), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 dgrad"); k += 1
         if reduce and self.split is not None:
             self._launch_conv1_wgrad_comm(b, N, st); k += 1
         else:
             ok(L.pdl_conv1_wgrad_fused(_p(b["x"]), _p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(gw1), _p(gb1), _p(b["c1part"]), N, st), "conv1 wgrad"); k += 1
         main.wait_stream(branch)  # join: every gradient is in the bucket before the allreduce / the step ends
+        if branch2 is not branch:
+            main.wait_stream(branch2)
         return k
 
     def _record_simt(self, b, N, stream_handle):
@@ -394,8 +423,8 @@ class ConvNetEngine:
         if self.ddp is not None:
             self.backend._hyper_for(self.bucket)
             if self.split is not None:
-                self.backend._hyper_for(self.split["early"])
-                self.backend._hyper_for(self.split["tail"])
+                for bk in self.split["parts"].values():
+                    self.backend._hyper_for(bk)
         else:
             self.arena.refresh_hyper(self.group)
 
