@@ -408,6 +408,75 @@ PDL_API int pdl_allreduce_launch(int algo, int rank, int world, int channel, lon
                                  timeout_s, stream);
 }
 
+// ---- one call per bucket: the reducer's launch path (reference: Reducer::mark_bucket_ready -> all_reduce_bucket on the
+// process group's stream) -------------------------------------------------------------------------------
+// A handle keeps everything that is fixed for a bucket (peer pointers, variant, CTA count, two events).  pdl_bucket_reduce
+// then does what the autograd hook needs when the bucket's last gradient has arrived, in ONE native call:
+//   record `ready` on the compute stream -> make the communication stream wait for it -> launch the fused kernel there ->
+//   record `done` on the communication stream.   pdl_bucket_wait makes a stream wait for `done` (end of backward).
+// Works under stream capture (the event edges become graph dependencies).
+namespace {
+struct BucketHandle {
+  ARParams p;
+  int algo, blocks;
+  cudaEvent_t ready, done;
+};
+}  // namespace
+
+PDL_API int pdl_bucket_create(int algo, int rank, int world, int channel, long long n4, long long inbox_row4, const float* const* in,
+                              float* const* out, float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, void* state,
+                              int blocks, double scale, double timeout_s, void** handle) {
+  if (world > kMaxWorld || channel < 0 || channel >= kMaxChannels || blocks < 1 || blocks > kMaxBlocks) {
+    pdl_set_error("bucket: bad world/channel/block count (%d, %d, %d)", world, channel, blocks);
+    return -1;
+  }
+  if (algo == NVLS && (!mc_in || !mc_out)) { pdl_set_error("bucket: nvls needs multicast pointers"); return -1; }
+  if (algo == PUSH && inbox_row4 < n4) { pdl_set_error("bucket: push inbox rows shorter than the bucket"); return -1; }
+  BucketHandle* h = new BucketHandle();
+  for (int q = 0; q < world; ++q) {
+    h->p.in[q] = in[q]; h->p.out[q] = out[q]; h->p.pad[q] = pad ? pad[q] : nullptr; h->p.ring[q] = ring ? ring[q] : nullptr;
+  }
+  h->p.mc_in = mc_in; h->p.mc_out = mc_out; h->p.state = static_cast<CommState*>(state);
+  h->p.n4 = n4; h->p.row4 = inbox_row4; h->p.rank = rank; h->p.world = world; h->p.channel = channel;
+  h->p.scale = static_cast<float>(scale); h->p.timeout_ns = static_cast<unsigned long long>(timeout_s * 1e9);
+  h->algo = algo; h->blocks = blocks;
+  PDL_CUDA_CHECK(cudaEventCreateWithFlags(&h->ready, cudaEventDisableTiming));
+  PDL_CUDA_CHECK(cudaEventCreateWithFlags(&h->done, cudaEventDisableTiming));
+  *handle = h;
+  return 0;
+}
+
+PDL_API int pdl_bucket_destroy(void* handle) {
+  BucketHandle* h = static_cast<BucketHandle*>(handle);
+  if (!h) return 0;
+  cudaEventDestroy(h->ready);
+  cudaEventDestroy(h->done);
+  delete h;
+  return 0;
+}
+
+static int bucket_launch(const ARParams& p, int algo, int blocks, cudaStream_t stream) {
+  const bool sgd = p.param != nullptr;
+  DISPATCH_ALGO(allreduce_kernel, p, blocks, false)
+}
+
+PDL_API int pdl_bucket_reduce(void* handle, float* param, float* mom, void* hyper, cudaStream_t compute, cudaStream_t comm) {
+  BucketHandle* h = static_cast<BucketHandle*>(handle);
+  ARParams p = h->p;
+  p.param = param; p.mom = mom; p.hyper = static_cast<SgdHyper*>(hyper);
+  PDL_CUDA_CHECK(cudaEventRecord(h->ready, compute));
+  PDL_CUDA_CHECK(cudaStreamWaitEvent(comm, h->ready, 0));
+  if (int rc = bucket_launch(p, h->algo, h->blocks, comm)) return rc;
+  PDL_CUDA_CHECK(cudaEventRecord(h->done, comm));
+  return 0;
+}
+
+PDL_API int pdl_bucket_wait(void* handle, cudaStream_t stream) {
+  BucketHandle* h = static_cast<BucketHandle*>(handle);
+  PDL_CUDA_CHECK(cudaStreamWaitEvent(stream, h->done, 0));
+  return 0;
+}
+
 // Test harness: run `world` virtual ranks on ONE GPU in a single cooperative launch.
 // Pointer arrays are [world][world]: entry [v][q] = what virtual rank v uses for peer q.
 PDL_API int pdl_allreduce_emulated(int algo, int world, long long n4, const float* const* in, float* const* out, float* const* ring,

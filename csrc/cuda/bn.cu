@@ -210,6 +210,7 @@ __device__ void bwd_finalize_group(const float* partial, int splits, int C, int 
 // partial[(split * C + c) * 2 + {0,1}] = (sum g, sum g * xhat) over the rows of the split
 template <int kMask>
 __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                                const float* __restrict__ dy2,  // second addend of the incoming gradient or nullptr
                                                                 const uint8_t* __restrict__ relu_mask, const float* __restrict__ saved,
                                                                 float* __restrict__ partial, long long M, int C, long long rows_per_split,
                                                                 const BwdFinalizeArgs fin) {
@@ -221,6 +222,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __r
     const long long ld = C / 4;
     const float4* xp = reinterpret_cast<const float4*>(x + c);
     const float4* gp = reinterpret_cast<const float4*>(dy + c);
+    const float4* gp2 = dy2 ? reinterpret_cast<const float4*>(dy2 + c) : nullptr;
     const uint8_t* mp = relu_mask + c / 4;
     const float4 mu = *reinterpret_cast<const float4*>(saved + c), is = *reinterpret_cast<const float4*>(saved + C + c);
     const float4 sc = *reinterpret_cast<const float4*>(saved + 2 * C + c), sf = *reinterpret_cast<const float4*>(saved + 3 * C + c);
@@ -229,6 +231,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_stats_kernel(const float* __r
     for (long long r = r_lo + rl; r < r_hi; r += kRL) {
       const float4 v = __ldg(xp + r * ld);
       float4 g = __ldg(gp + r * ld);
+      if (gp2) { const float4 g2 = __ldg(gp2 + r * ld); g.x += g2.x; g.y += g2.y; g.z += g2.z; g.w += g2.w; }
       unsigned m = 0;
       if (kMask == 2) m = __ldg(mp + r * ld);
       g = act_grad<kMask>(g, v, m, sc, sf);
@@ -281,6 +284,7 @@ __device__ void bwd_finalize_group(const float* partial, int splits, int C, int 
 
 template <int kMask, bool kRes>
 __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const float4* __restrict__ x, const float4* __restrict__ dy,
+                                                                const float4* __restrict__ dy2,
                                                                 const uint8_t* __restrict__ relu_mask, float4* __restrict__ dx,
                                                                 float4* __restrict__ dres, const float* __restrict__ coef,
                                                                 const float* __restrict__ saved, long long total4, int C4) {
@@ -289,6 +293,7 @@ __global__ void __launch_bounds__(kThreads) bn_bwd_apply_kernel(const float4* __
   const int c = quad_channel(i, C4), C = 4 * C4;
   const float4 v = x[i];
   float4 g = dy[i];
+  if (dy2) { const float4 g2 = dy2[i]; g.x += g2.x; g.y += g2.y; g.z += g2.z; g.w += g2.w; }
   unsigned m = 0;
   if (kMask == 2) m = relu_mask[i];
   if (kMask != 0) {
@@ -399,8 +404,11 @@ PDL_API int pdl_bn_fwd_eval(const float* x, const float* residual, const float* 
 // Training backward of y = act(bn(x) [+ residual]): dx, dgamma, dbeta and, when dres != nullptr, the gradient
 // of the residual input (= dy through the activation).  relu_mask (written by the forward pass) is only read when
 // relu != 0 and dres != nullptr; the plain ReLU form recomputes the mask from x.
-PDL_API int pdl_bn_bwd(const float* x, const float* dy, const uint8_t* relu_mask, const float* gamma, const float* saved, float* dx,
-                       float* dres, float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
+// dy2 (optional): a second tensor to be ADDED to dy -- the block output feeds both the next block's first convolution and
+// its skip connection, and instead of autograd summing the two gradients in a pass of its own (read 2, write 1) this kernel
+// reads both where it reads dy anyway.
+PDL_API int pdl_bn_bwd2(const float* x, const float* dy, const float* dy2, const uint8_t* relu_mask, const float* gamma, const float* saved,
+                        float* dx, float* dres, float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
   if (check_c(C)) return -1;
   const int splits = choose_splits(M, C);
   const long long rps = (M + splits - 1) / splits;
@@ -414,17 +422,22 @@ PDL_API int pdl_bn_bwd(const float* x, const float* dy, const uint8_t* relu_mask
   const BwdFinalizeArgs fin{static_cast<float>(M), gamma, dgamma, dbeta, coef};
   const uint8_t* y = relu_mask;
   const uint8_t* y4 = relu_mask;
-  if (mask == 0) bn_bwd_stats_kernel<0><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
-  else if (mask == 1) bn_bwd_stats_kernel<1><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
-  else bn_bwd_stats_kernel<2><<<grid, kThreads, 0, stream>>>(x, dy, y, saved, partial, M, C, rps, fin);
+  if (mask == 0) bn_bwd_stats_kernel<0><<<grid, kThreads, 0, stream>>>(x, dy, dy2, y, saved, partial, M, C, rps, fin);
+  else if (mask == 1) bn_bwd_stats_kernel<1><<<grid, kThreads, 0, stream>>>(x, dy, dy2, y, saved, partial, M, C, rps, fin);
+  else bn_bwd_stats_kernel<2><<<grid, kThreads, 0, stream>>>(x, dy, dy2, y, saved, partial, M, C, rps, fin);
   const long long total4 = M * C / 4;
   const unsigned blocks = static_cast<unsigned>(pdl_ceil_div(total4, kThreads));
-  const float4 *x4 = reinterpret_cast<const float4*>(x), *g4 = reinterpret_cast<const float4*>(dy);
+  const float4 *x4 = reinterpret_cast<const float4*>(x), *g4 = reinterpret_cast<const float4*>(dy), *h4 = reinterpret_cast<const float4*>(dy2);
   float4 *dx4 = reinterpret_cast<float4*>(dx), *dr4 = reinterpret_cast<float4*>(dres);
-  if (mask == 0 && !dres) bn_bwd_apply_kernel<0, false><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
-  else if (mask == 0) bn_bwd_apply_kernel<0, true><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
-  else if (mask == 1) bn_bwd_apply_kernel<1, false><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
-  else bn_bwd_apply_kernel<2, true><<<blocks, kThreads, 0, stream>>>(x4, g4, y4, dx4, dr4, coef, saved, total4, C / 4);
+  if (mask == 0 && !dres) bn_bwd_apply_kernel<0, false><<<blocks, kThreads, 0, stream>>>(x4, g4, h4, y4, dx4, dr4, coef, saved, total4, C / 4);
+  else if (mask == 0) bn_bwd_apply_kernel<0, true><<<blocks, kThreads, 0, stream>>>(x4, g4, h4, y4, dx4, dr4, coef, saved, total4, C / 4);
+  else if (mask == 1) bn_bwd_apply_kernel<1, false><<<blocks, kThreads, 0, stream>>>(x4, g4, h4, y4, dx4, dr4, coef, saved, total4, C / 4);
+  else bn_bwd_apply_kernel<2, true><<<blocks, kThreads, 0, stream>>>(x4, g4, h4, y4, dx4, dr4, coef, saved, total4, C / 4);
   PDL_LAUNCH_CHECK();
   return 0;
+}
+
+PDL_API int pdl_bn_bwd(const float* x, const float* dy, const uint8_t* relu_mask, const float* gamma, const float* saved, float* dx,
+                       float* dres, float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream) {
+  return pdl_bn_bwd2(x, dy, nullptr, relu_mask, gamma, saved, dx, dres, dgamma, dbeta, scratch, M, C, relu, stream);
 }

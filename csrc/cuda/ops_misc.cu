@@ -335,6 +335,48 @@ PDL_API int pdl_global_avgpool_bwd(const float* dy, float* dx, int N, int HW, in
   return 0;
 }
 
+namespace {
+// part[s][c] = sum of x[r][c] over the rows r of split s (NHWC rows [M][C]): the bias gradient of a convolution as partial
+// sums that the weight-gradient kernel's deterministic second pass folds in (reference: the db reduction autograd runs for
+// nn.Conv2d(bias=True), launch_dist.py:15-25).  256 threads = 8 row lanes x 32 channels; fixed summation order.
+__global__ void __launch_bounds__(256) colsum_partial_kernel(const float* __restrict__ x, float* __restrict__ part, long long M, int C,
+                                                             long long rows_per_split) {
+  const int cl = threadIdx.x % 32, rl = threadIdx.x / 32;
+  const int c = blockIdx.x * 32 + cl;
+  const long long r_lo = blockIdx.y * rows_per_split, r_hi = min(M, r_lo + rows_per_split);
+  float s = 0.f;
+  if (c < C) {
+#pragma unroll 4
+    for (long long r = r_lo + rl; r < r_hi; r += 8) s += __ldg(x + r * C + c);
+  }
+  __shared__ float sm[8][33];
+  sm[rl][cl] = s;
+  __syncthreads();
+  if (rl == 0 && c < C) {
+    float t = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) t += sm[i][cl];
+    part[static_cast<long long>(blockIdx.y) * C + c] = t;
+  }
+}
+}  // namespace
+
+// Number of row splits pdl_colsum_partial uses (= rows of `part`).
+PDL_API int pdl_colsum_splits(long long M, int C) {
+  long long want = 296 / ((C + 31) / 32);  // about two waves of CTAs in total
+  if (want < 1) want = 1;
+  long long by_rows = (M + 63) / 64;       // at least 64 rows per split
+  if (want > by_rows) want = by_rows;
+  return static_cast<int>(want < 1 ? 1 : want);
+}
+PDL_API int pdl_colsum_partial(const float* x, float* part, long long M, int C, cudaStream_t stream) {
+  const int splits = pdl_colsum_splits(M, C);
+  const long long rps = (M + splits - 1) / splits;
+  colsum_partial_kernel<<<dim3((C + 31) / 32, splits), 256, 0, stream>>>(x, part, M, C, rps);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
 PDL_API int pdl_permute_nhwc_nchw(const float* x, float* y, int N, int HW, int C, int to_nchw, cudaStream_t stream) {
   long long total = static_cast<long long>(N) * HW * C;
   if (total) permute_nhwc_nchw_kernel<<<launch_1d(total), kThreads, 0, stream>>>(x, y, N, HW, C, to_nchw);

@@ -59,6 +59,16 @@ int pdl_allreduce_launch(int algo, int rank, int world, int channel, long long n
 int pdl_allreduce_launch_ex(int algo, int rank, int world, int channel, long long n4, long long inbox_row4, const float* const* in,
                             float* const* out, float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, float* param,
                             float* mom, void* hyper, void* state, int blocks, double scale, double timeout_s, cudaStream_t stream);
+/* The reducer's launch path as one native call per bucket (reference: Reducer::mark_bucket_ready -> allreduce on the process
+ * group's stream).  A handle fixes peer pointers, variant and CTA count; pdl_bucket_reduce records "gradients ready" on the
+ * compute stream, makes the communication stream wait for it, launches the fused kernel there and records "done";
+ * pdl_bucket_wait orders a stream behind "done".  Capturable. */
+int pdl_bucket_create(int algo, int rank, int world, int channel, long long n4, long long inbox_row4, const float* const* in,
+                      float* const* out, float* const* ring, uint32_t* const* pad, const float* mc_in, float* mc_out, void* state, int blocks,
+                      double scale, double timeout_s, void** handle);
+int pdl_bucket_reduce(void* handle, float* param, float* mom, void* hyper, cudaStream_t compute, cudaStream_t comm);
+int pdl_bucket_wait(void* handle, cudaStream_t stream);
+int pdl_bucket_destroy(void* handle);
 /* all `world` ranks as one cooperative launch on one GPU (tests) */
 int pdl_allreduce_emulated(int algo, int world, long long n4, const float* const* in, float* const* out, float* const* ring,
                            uint32_t* const* pad, float* const* param, float* const* mom, void* const* hyper, void* const* state, int blocks,
@@ -199,6 +209,10 @@ int pdl_bn_fwd_train_prestats(const float* x, const float* residual, const float
                               uint8_t* relu_mask, const float* partial, int splits, long long M, int C, int relu, cudaStream_t stream);
 int pdl_bn_fwd_eval(const float* x, const float* residual, const float* gamma, const float* beta, const float* running_mean,
                     const float* running_var, float eps, float* y, float* scratch, long long M, int C, int relu, cudaStream_t stream);
+/* dy2 (may be NULL): a second tensor added to dy on the fly -- the gradient of a block output that feeds both the next
+ * block's first convolution and its skip connection arrives in two pieces; reading both here replaces autograd's add pass */
+int pdl_bn_bwd2(const float* x, const float* dy, const float* dy2, const uint8_t* relu_mask, const float* gamma, const float* saved, float* dx,
+                float* dres, float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream);
 int pdl_bn_bwd(const float* x, const float* dy, const uint8_t* relu_mask, const float* gamma, const float* saved, float* dx, float* dres,
                float* dgamma, float* dbeta, float* scratch, long long M, int C, int relu, cudaStream_t stream);
 
@@ -213,6 +227,10 @@ int pdl_maxpool_bwd(const float* dy, const uint8_t* idx, const float* pooled, fl
 int pdl_global_avgpool_fwd(const float* x, float* y, int N, int HW, int C, cudaStream_t stream);
 int pdl_global_avgpool_bwd(const float* dy, float* dx, int N, int HW, int C, cudaStream_t stream);
 int pdl_permute_nhwc_nchw(const float* x, float* y, int N, int HW, int C, int to_nchw, cudaStream_t stream);
+/* part[pdl_colsum_splits(M, C)][C]: column sums of NHWC rows x[M][C] per row split -- a convolution's bias gradient as partial
+ * sums for the weight-gradient kernel's second pass (reference: the db reduction of nn.Conv2d, launch_dist.py:15-25) */
+int pdl_colsum_splits(long long M, int C);
+int pdl_colsum_partial(const float* x, float* part, long long M, int C, cudaStream_t stream);
 int pdl_linear_fwd(const float* x, const float* w, const float* b, float* y, int M, int N, int K, cudaStream_t stream);
 int pdl_linear_dgrad(const float* dy, const float* w, float* dx, int M, int N, int K, cudaStream_t stream);
 int pdl_linear_wgrad(const float* x, const float* dy, float* dw, float* db, int M, int N, int K, cudaStream_t stream);

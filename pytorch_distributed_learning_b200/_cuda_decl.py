@@ -39,6 +39,10 @@ def declare(L):
     sig("pdl_allreduce_push_inbox_bytes", [LL, I], LL)
     sig("pdl_allreduce_launch", [I, I, I, I, LL, P, P, P, P, P, P, P, P, P, P, I, c_double, c_double, P])
     sig("pdl_allreduce_launch_ex", [I, I, I, I, LL, LL, P, P, P, P, P, P, P, P, P, P, I, c_double, c_double, P])
+    sig("pdl_bucket_create", [I, I, I, I, LL, LL, P, P, P, P, P, P, P, I, c_double, c_double, POINTER(P)])
+    sig("pdl_bucket_reduce", [P, P, P, P, P, P])
+    sig("pdl_bucket_wait", [P, P])
+    sig("pdl_bucket_destroy", [P])
     sig("pdl_allreduce_emulated", [I, I, LL, P, P, P, P, P, P, P, P, I, P])
     sig("pdl_pull_launch", [I, I, I, I, LL, P, P, P, P, I, c_double, P])
     # optimizer
@@ -100,6 +104,7 @@ def declare(L):
     sig("pdl_bn_fwd_train", [P, P, P, P, P, P, P, F, F, P, P, P, P, LL, I, I, P])
     sig("pdl_bn_fwd_eval", [P, P, P, P, P, P, F, P, P, LL, I, I, P])
     sig("pdl_bn_bwd", [P, P, P, P, P, P, P, P, P, P, LL, I, I, P])
+    sig("pdl_bn_bwd2", [P, P, P, P, P, P, P, P, P, P, P, LL, I, I, P])
     # element-wise / pooling / linear / loss
     sig("pdl_relu_fwd", [P, P, LL, P])
     sig("pdl_relu_bwd", [P, P, P, LL, P])
@@ -109,6 +114,8 @@ def declare(L):
     sig("pdl_global_avgpool_fwd", [P, P, I, I, I, P])
     sig("pdl_global_avgpool_bwd", [P, P, I, I, I, P])
     sig("pdl_permute_nhwc_nchw", [P, P, I, I, I, I, P])
+    sig("pdl_colsum_splits", [LL, I])
+    sig("pdl_colsum_partial", [P, P, LL, I, P])
     sig("pdl_linear_fwd", [P, P, P, P, I, I, I, P])
     sig("pdl_linear_dgrad", [P, P, P, I, I, I, P])
     sig("pdl_linear_wgrad", [P, P, P, P, I, I, I, P])

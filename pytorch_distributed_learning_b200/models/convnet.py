@@ -9,7 +9,11 @@ runs its fused conv+bias+ReLU+pool pipeline inside one CUDA graph.
 """
 from __future__ import annotations
 
+import torch
+
 from .. import nn
+
+_CHANNELS_LAST = torch.channels_last
 
 
 class ConvNet(nn.Module):
@@ -25,9 +29,24 @@ class ConvNet(nn.Module):
         self.dropout = nn.Dropout(p=0.5)
         self.fc1 = nn.Linear(in_features=128 * 4 * 4, out_features=10)
 
+    def _block(self, conv, pool, x):
+        """``pool(relu(conv(x)))``: one fused kernel on a B200 (``ops.functional.conv_relu_pool``), the three layers otherwise."""
+        if x.is_cuda and x.dtype == torch.float32 and type(conv) is nn.Conv2d and type(pool) is nn.MaxPool2d:
+            from ..ops import functional as NF
+
+            y = NF.conv_relu_pool(x, conv, pool)
+            if y is not None:
+                return y
+        return pool(self.relu(conv(x)))
+
     def forward(self, x):
-        x = self.maxpool1(self.relu(self.conv1(x)))
-        x = self.maxpool2(self.relu(self.conv2(x)))
-        x = self.maxpool3(self.relu(self.conv3(x)))
-        x = x.reshape(-1, 128 * 4 * 4)
+        x = self._block(self.conv1, self.maxpool1, x)
+        x = self._block(self.conv2, self.maxpool2, x)
+        x = self._block(self.conv3, self.maxpool3, x)
+        if x.is_cuda and x.dim() == 4 and x.is_contiguous(memory_format=_CHANNELS_LAST) and not x.is_contiguous():
+            from ..ops import functional as NF
+
+            x = NF.flatten_nchw(x)  # the reference's reshape(-1, 2048) in NCHW element order, as one permute kernel
+        else:
+            x = x.reshape(-1, 128 * 4 * 4)
         return self.fc1(x)

@@ -23,14 +23,27 @@ def _conv1x1(cin, cout, stride=1):
     return nn.Conv2d(cin, cout, kernel_size=1, stride=stride, bias=False)
 
 
-def _conv_bn(conv, bn, x, relu=False, residual=None):
+def _conv_bn(conv, bn, x, relu=False, residual=None, dual=False):
     """conv -> batch norm (-> + residual) (-> ReLU) as the fused kernels see it: the convolution's epilogue reduces the
     normalisation statistics (``bn_stats=True`` is a hint, ignored where it does not apply), and the normalisation,
-    skip connection and activation are one pass over the tensor."""
+    skip connection and activation are one pass over the tensor.  ``dual``: see ``_split``."""
+    if dual:
+        return bn(conv(x, bn_stats=True), relu=relu, residual=residual, dual=True)
     return bn(conv(x, bn_stats=True), relu=relu, residual=residual)
 
 
-def _open_block(conv, bn, x):
+_DUAL = os.environ.get("PDL_RESNET_DUAL_OUTPUT", "1") != "0"
+
+
+def _split(x):
+    """A block's output feeds two consumers in the next block (its first convolution and its skip connection or downsample
+    branch), so in backward two gradients come back for it.  Blocks therefore hand their output on as a PAIR of aliases of
+    the same memory -- one per consumer -- and the closing BatchNorm's backward kernel adds the two gradients while it reads
+    them (``pdl_bn_bwd2``) instead of autograd running an add kernel over two full tensors first (16 per ResNet-50 step)."""
+    return x if isinstance(x, tuple) else (x, x)
+
+
+def _open_block(conv, bn, x, skip=None):
     """First conv+bn+relu of an identity block, and the skip connection.  With PDL_SKIP_VIA_CONV=1 the skip is routed
     through the convolution's autograd node, so that in backward its gradient is added in that convolution's dgrad
     epilogue instead of by autograd's separate pass over two full tensors.  Measured on B200 (ResNet-50, batch 64):
@@ -39,7 +52,7 @@ def _open_block(conv, bn, x):
     if os.environ.get("PDL_SKIP_VIA_CONV", "0") == "1":
         y, skip = conv(x, bn_stats=True, skip=True)
         return bn(y, relu=True), skip
-    return bn(conv(x, bn_stats=True), relu=True), x
+    return bn(conv(x, bn_stats=True), relu=True), (x if skip is None else skip)
 
 
 def _downsample(ds, x):
@@ -63,12 +76,13 @@ class BasicBlock(nn.Module):
         self.stride = stride
 
     def forward(self, x):
+        x, skip = _split(x)
         if self.downsample is None:
-            out, identity = _open_block(self.conv1, self.bn1, x)
+            out, identity = _open_block(self.conv1, self.bn1, x, skip)
         else:
-            identity = _downsample(self.downsample, x)
+            identity = _downsample(self.downsample, skip)
             out = _conv_bn(self.conv1, self.bn1, x, relu=True)
-        return _conv_bn(self.conv2, self.bn2, out, relu=True, residual=identity)
+        return _conv_bn(self.conv2, self.bn2, out, relu=True, residual=identity, dual=_DUAL)
 
 
 class Bottleneck(nn.Module):
@@ -87,13 +101,14 @@ class Bottleneck(nn.Module):
         self.stride = stride
 
     def forward(self, x):
+        x, skip = _split(x)
         if self.downsample is None:
-            out, identity = _open_block(self.conv1, self.bn1, x)
+            out, identity = _open_block(self.conv1, self.bn1, x, skip)
         else:
-            identity = _downsample(self.downsample, x)
+            identity = _downsample(self.downsample, skip)
             out = _conv_bn(self.conv1, self.bn1, x, relu=True)
         out = _conv_bn(self.conv2, self.bn2, out, relu=True)
-        return _conv_bn(self.conv3, self.bn3, out, relu=True, residual=identity)
+        return _conv_bn(self.conv3, self.bn3, out, relu=True, residual=identity, dual=_DUAL)
 
 
 class ResNet(nn.Module):
@@ -130,6 +145,8 @@ class ResNet(nn.Module):
     def forward(self, x):
         x = self.maxpool(_conv_bn(self.conv1, self.bn1, x, relu=True))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
+        if isinstance(x, tuple):
+            x = x[0]  # the last block's output has a single consumer
         x = self.avgpool(x)
         x = x.flatten(1)
         return self.fc(x)

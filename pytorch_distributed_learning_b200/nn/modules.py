@@ -94,17 +94,21 @@ class BatchNorm2d(tnn.BatchNorm2d):
     """``bn(x)``; the optional arguments fuse what follows it in a ResNet block into the same kernels:
     ``bn(x, relu=True)`` = ``relu(bn(x))`` and ``bn(x, relu=True, residual=r)`` = ``relu(bn(x) + r)``."""
 
-    def forward(self, x, relu=False, residual=None):
+    def forward(self, x, relu=False, residual=None, dual=False):
+        """``dual=True`` returns ``(y, y')``: the output as two tensor objects over the same memory, for a consumer pair such
+        as the next residual block's first convolution and its skip connection (their two gradients are then added inside
+        this layer's backward kernel instead of by a separate autograd pass)."""
         if _native(x) and self.affine and self.track_running_stats and self.momentum is not None and (residual is None or _native(residual)):
             from ..ops import functional as NF
 
             return NF.batch_norm(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum, self.eps,
                                  relu, residual, self.num_batches_tracked,  # the step counter is bumped by the finalize kernel
-                                 partial=getattr(x, "_pdl_bn_partial", None) if self.training else None)
+                                 partial=getattr(x, "_pdl_bn_partial", None) if self.training else None, dual=dual)
         y = super().forward(x)
         if residual is not None:
             y = y + residual
-        return torch.relu(y) if relu else y
+        y = torch.relu(y) if relu else y
+        return (y, y) if dual else y
 
 
 class AdaptiveAvgPool2d(tnn.AdaptiveAvgPool2d):

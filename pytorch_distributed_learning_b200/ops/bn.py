@@ -9,14 +9,17 @@ from __future__ import annotations
 import torch
 
 from .. import _lib
-from .functional import _nhwc, _ok, _p, _stream, scratch
+from .functional import _nhwc, _ok, _p, _stream, grad_buffer, scratch
 
 _CL = torch.channels_last
 
 
 class _BatchNormAct(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, residual, weight, bias, running_mean, running_var, num_batches_tracked, momentum, eps, relu, partial=None):
+    def forward(ctx, x, residual, weight, bias, running_mean, running_var, num_batches_tracked, momentum, eps, relu, partial=None, dual=False):
+        """``dual``: return the output twice (two tensor objects over the same memory).  A residual block hands one to the next
+        block's first convolution and the other to its skip connection; their gradients then arrive here as two tensors and
+        the backward kernel adds them while it reads them, instead of autograd summing them in a pass of its own."""
         L = _lib.cuda()
         x = _nhwc(x)
         if residual is not None:
@@ -38,28 +41,48 @@ class _BatchNormAct(torch.autograd.Function):
             _ok(L.pdl_bn_fwd_train(_p(x), _p(residual), _p(weight), _p(bias), _p(running_mean), _p(running_var), _p(num_batches_tracked),
                                    float(momentum), float(eps), _p(y), _p(saved), _p(mask), _p(sc), M, C, int(relu), _stream(x)), "batch norm forward")
         ctx.save_for_backward(x, weight, saved, mask)
+        ctx.bias_ref = bias.detach()
+        if dual:
+            ctx.set_materialize_grads(False)
+            return y, y.view_as(y)
         return y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dy2=None):
         L = _lib.cuda()
         x, weight, saved, mask = ctx.saved_tensors
+        if dy is None:
+            dy, dy2 = dy2, None
+        if dy is None:
+            return (None,) * 12
         dy = _nhwc(dy)
+        if dy2 is not None:
+            dy2 = _nhwc(dy2)
         N, C, H, W = x.shape
         M = N * H * W
         dx = torch.empty_like(x, memory_format=_CL)
         dres = torch.empty_like(x, memory_format=_CL) if ctx.has_res else None
-        dgamma = torch.empty(C, dtype=x.dtype, device=x.device)
-        dbeta = torch.empty(C, dtype=x.dtype, device=x.device)
+        dgamma = grad_buffer(weight)   # straight into DDP's gradient arena when one is installed
+        dbeta = grad_buffer(ctx.bias_ref)
         sc = scratch(L.pdl_bn_scratch_floats(M, C) * 4, x.device, "bn")
-        _ok(L.pdl_bn_bwd(_p(x), _p(dy), _p(mask), _p(weight), _p(saved), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(sc), M, C, int(ctx.relu),
-                         _stream(x)), "batch norm backward")
-        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None
+        _ok(L.pdl_bn_bwd2(_p(x), _p(dy), _p(dy2), _p(mask), _p(weight), _p(saved), _p(dx), _p(dres), _p(dgamma), _p(dbeta), _p(sc), M, C,
+                          int(ctx.relu), _stream(x)), "batch norm backward")
+        return dx, dres, dgamma, dbeta, None, None, None, None, None, None, None, None
 
 
 def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None, num_batches_tracked=None,
-               partial=None):
-    """``num_batches_tracked`` (int64 tensor or None) is incremented by the training forward, on the device."""
+               partial=None, dual=False):
+    """``num_batches_tracked`` (int64 tensor or None) is incremented by the training forward, on the device.  ``dual=True``
+    returns the output as a pair of aliases when the fused training kernel runs (see ``_BatchNormAct.forward``), else a
+    pair holding the same tensor twice."""
+    if dual:
+        C = x.shape[1]
+        if training and C % 4 == 0:
+            if partial is not None and (partial.dim() != 3 or partial.shape[1] != C or not x.is_contiguous(memory_format=_CL)):
+                partial = None
+            return _BatchNormAct.apply(x, residual, weight, bias, running_mean, running_var, num_batches_tracked, momentum, eps, relu, partial, True)
+        y = batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual, num_batches_tracked, partial)
+        return y, y
     C = x.shape[1]
     if C % 4 != 0:
         if training and num_batches_tracked is not None:

@@ -46,6 +46,32 @@ def scratch(nbytes, device, tag="default"):
     return buf
 
 
+# ---- gradient sinks --------------------------------------------------------------------------------------------------
+# DistributedDataParallel keeps every gradient bucket in one symmetric arena that the allreduce kernels read.  While a
+# synchronised backward runs it installs, per parameter, the arena view its gradient belongs in; the backward functions
+# below then let their kernels write dW / db / dgamma / dbeta THERE and return an alias of that view, which autograd adopts
+# as ``param.grad`` without a copy.  No intermediate gradient tensor, no copy-in (the reference's reducer copies every
+# gradient into its bucket: SURVEY T10).  Keyed by the parameter's storage address.
+_grad_sinks = {}
+
+
+def install_grad_sinks(mapping):
+    _grad_sinks.update(mapping)
+
+
+def remove_grad_sinks(keys):
+    for k in keys:
+        _grad_sinks.pop(k, None)
+
+
+def grad_buffer(param):
+    """Where the gradient of ``param`` should be written: a fresh alias of its arena view, or a new tensor."""
+    sink = _grad_sinks.get(param.data_ptr())
+    if sink is not None and sink.shape == param.shape and sink.dtype == param.dtype:
+        return sink.view(sink.shape)  # a new tensor object over the same memory: autograd may adopt it
+    return torch.empty_like(param, memory_format=torch.contiguous_format)
+
+
 def conv_out(h, k, s, p):
     return (h + 2 * p - k) // s + 1
 
@@ -68,6 +94,7 @@ class _Conv2d(torch.autograd.Function):
         from . import tc_conv
 
         ctx.geom = (stride, pad, b is not None)
+        ctx.bias_ref = b.detach() if b is not None else None  # only its address/shape are used (gradient sink lookup)
         ctx.x_shape = tuple(x.shape)
         ctx.stem = tc_conv.stem_supported(x, w, stride, pad)
         partial = None
@@ -113,12 +140,12 @@ class _Conv2d(torch.autograd.Function):
         elif dskip is not None:
             dx = dskip
         if ctx.stem and (ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2])):
-            dw = torch.empty_like(w)
+            dw = grad_buffer(w)
             tc_conv.stem_wgrad(x, dy, dw, ctx.x_shape, stride, pad)  # x is the padded NHWC4 copy here
             db = dy.sum(dim=(0, 2, 3)) if has_bias else None
         elif ctx.needs_input_grad[1] or (has_bias and ctx.needs_input_grad[2]):
-            dw = torch.empty_like(w)
-            db = torch.empty(Cout, dtype=w.dtype, device=w.device) if has_bias else None
+            dw = grad_buffer(w)
+            db = grad_buffer(ctx.bias_ref) if has_bias else None
             if not tc_conv.conv2d_wgrad(x, dy, dw, db, stride, pad):
                 nbytes = L.pdl_conv2d_wgrad_scratch_bytes(N, H, W, Cin, Cout, KH, KW, stride, pad)
                 sc = scratch(nbytes, x.device, "wgrad")
@@ -195,6 +222,7 @@ class _Linear(torch.autograd.Function):
         _ok(_lib.cuda().pdl_linear_fwd(_p(x), _p(w), _p(b), _p(y), M, N, K, _stream(x)), "linear forward")
         ctx.save_for_backward(x, w)
         ctx.has_bias = b is not None
+        ctx.bias_ref = b.detach() if b is not None else None
         return y
 
     @staticmethod
@@ -209,8 +237,8 @@ class _Linear(torch.autograd.Function):
             dx = torch.empty_like(x)
             _ok(L.pdl_linear_dgrad(_p(dy), _p(w), _p(dx), M, N, K, _stream(x)), "linear dgrad")
         if ctx.needs_input_grad[1] or (ctx.has_bias and ctx.needs_input_grad[2]):
-            dw = torch.empty_like(w)
-            db = torch.empty(N, dtype=w.dtype, device=w.device) if ctx.has_bias else None
+            dw = grad_buffer(w)
+            db = grad_buffer(ctx.bias_ref) if ctx.has_bias else None
             _ok(L.pdl_linear_wgrad(_p(x), _p(dy), _p(dw), _p(db), M, N, K, _stream(x)), "linear wgrad")
         return dx, dw, db
 
@@ -227,14 +255,22 @@ class _CrossEntropy(torch.autograd.Function):
         loss = torch.empty((), dtype=logits.dtype, device=logits.device)
         row = torch.empty(N, dtype=logits.dtype, device=logits.device)
         dlogits = torch.empty_like(logits)
-        _ok(_lib.cuda().pdl_cross_entropy(_p(logits), _p(target), N, C, _p(row), _p(loss), _p(dlogits), None, _stream(logits)), "cross entropy")
-        ctx.save_for_backward(dlogits)
+        _ok(_lib.cuda().pdl_cross_entropy(_p(logits), _p(target), N, C, _p(row), _p(loss), None, None, _stream(logits)), "cross entropy")
+        ctx.save_for_backward(logits, target, row)
         return loss
 
     @staticmethod
     def backward(ctx, dloss):
-        (dlogits,) = ctx.saved_tensors
-        return dlogits * dloss, None
+        # d loss / d logits = (softmax - onehot) / N, times the incoming scalar: the same kernel again with the scalar as a
+        # DEVICE pointer (its loss outputs go to scratch) -- no elementwise multiply afterwards, nothing read on the host
+        logits, target, row = ctx.saved_tensors
+        N, C = logits.shape
+        dlogits = torch.empty_like(logits)
+        scale = dloss.detach().to(logits.dtype).contiguous()
+        tmp = torch.empty((), dtype=logits.dtype, device=logits.device)
+        _ok(_lib.cuda().pdl_cross_entropy(_p(logits), _p(target), N, C, _p(row), _p(tmp), _p(dlogits), _p(scale), _stream(logits)),
+            "cross entropy backward")
+        return dlogits, None
 
 
 def cross_entropy(logits, target):
@@ -242,12 +278,123 @@ def cross_entropy(logits, target):
 
 
 def batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu=False, residual=None, num_batches_tracked=None,
-               partial=None):
+               partial=None, dual=False):
     """``act(bn(x) [+ residual])`` in one pass (the tail of every ResNet block).  ``partial``: statistics partials of x
-    left by the convolution that produced it (``conv2d(..., bn_stats=True)``); x is then read once instead of twice."""
+    left by the convolution that produced it (``conv2d(..., bn_stats=True)``); x is then read once instead of twice.
+    ``dual=True`` returns the output as two aliases (see ``ops.bn._BatchNormAct``)."""
     from . import bn
 
-    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual, num_batches_tracked, partial)
+    return bn.batch_norm(x, weight, bias, running_mean, running_var, training, momentum, eps, relu, residual, num_batches_tracked, partial, dual)
+
+
+class _ConvReluPool(torch.autograd.Function):
+    """conv + bias + ReLU + 2x2 max-pool (stride 1 or 2) as ONE forward kernel, and a backward of pool-backward-with-ReLU-mask
+    (bias-gradient partials as a by-product) -> dgrad / wgrad on the tensor cores.  This is what the reference's
+    ``maxpool(relu(conv(x)))`` lines (launch_dist.py:36-38) become when the six-call loop is left unchanged; the graphed
+    ``TrainStep`` runs the same kernels from a hand-scheduled graph.  ``kind``: "tc" (tcgen05 implicit GEMM) or "conv1"
+    (the 1 -> 32 channel 5x5 first layer on CUDA cores)."""
+
+    @staticmethod
+    def forward(ctx, x, w, b, pool_stride, kind):
+        L = _lib.cuda()
+        from . import tc_conv
+
+        N, Cin, H, W = x.shape
+        Cout, _, KH, KW = w.shape
+        x = _nhwc(x)
+        ctx.kind, ctx.ps = kind, pool_stride
+        if kind == "conv1":
+            y = torch.empty((N, 32, 13, 13), dtype=x.dtype, device=x.device, memory_format=_CL)
+            idx = torch.empty((N, 13, 13, 32), dtype=torch.uint8, device=x.device)
+            _ok(L.pdl_conv1_fused_fwd(_p(x), _p(w), _p(b), _p(y), _p(idx), N, _stream(x)), "conv1 + relu + pool forward")
+        else:
+            y, idx = tc_conv.conv2d_fwd_relu_pool(x, w, b, pool_stride)
+        ctx.save_for_backward(x, w, y, idx)
+        ctx.bias_ref = b.detach()
+        return y
+
+    @staticmethod
+    def backward(ctx, da):
+        L = _lib.cuda()
+        from . import tc_conv
+
+        x, w, y, idx = ctx.saved_tensors
+        da = _nhwc(da)
+        N, Cin, H, W = x.shape
+        Cout, _, KH, KW = w.shape
+        st = _stream(x)
+        dw, db = grad_buffer(w), grad_buffer(ctx.bias_ref)
+        if ctx.kind == "conv1":  # pool backward + ReLU mask folded into the weight-gradient kernel's operand load; no dx (input)
+            part = scratch(L.pdl_bwd_blocks(N) * 832 * 4, x.device, "conv1_wgrad")
+            _ok(L.pdl_conv1_wgrad_fused(_p(x), _p(da), _p(idx), _p(y), _p(dw), _p(db), _p(part), N, st), "conv1 wgrad")
+            return None, dw, db, None, None
+        P, Q = H - KH + 1, W - KW + 1
+        dz = torch.empty((N, Cout, P, Q), dtype=x.dtype, device=x.device, memory_format=_CL)
+        blocks = L.pdl_pool2_bwd_blocks(N, P, Q, Cout)
+        dbpart = torch.empty((blocks, Cout), dtype=x.dtype, device=x.device)
+        _ok(L.pdl_pool2_bwd_dbias(_p(da), _p(idx), _p(y), _p(dz), _p(dbpart), N, P, Q, Cout, ctx.ps, st), "pool backward + relu mask")
+        dx = None
+        if ctx.needs_input_grad[0]:
+            dx = torch.empty((N, Cin, H, W), dtype=x.dtype, device=x.device, memory_format=_CL)
+            if not tc_conv.conv2d_dgrad(dz, w, dx, 1, 0):
+                _ok(L.pdl_conv2d_dgrad_simt(_p(dz), _p(w), _p(dx), N, H, W, Cin, Cout, KH, KW, 1, 0, st), "conv2d dgrad")
+        sc = scratch(L.pdl_tc_wgrad_scratch_bytes(N, H, W, Cin, Cout, KH, KW, 0), x.device, "tc_wgrad")
+        _ok(L.pdl_tc_conv2d_wgrad(_p(x), _p(dz), _p(dw), _p(db), _p(dbpart), blocks, _p(sc), N, H, W, Cin, Cout, KH, KW, 0,
+                                  _p(tc_conv.error_flag(x.device)), st), "conv2d wgrad")
+        return dx, dw, db, None, None
+
+
+def conv_relu_pool(x, conv, pool):
+    """``pool(relu(conv(x)))`` through the fused kernels, or None when the layer triple is not one they cover (the caller then
+    runs the three layers one by one).  Covers what the reference's ConvNet uses: 2x2 pooling with stride 1 or 2, stride-1
+    unpadded 3x3 convolutions with 32/64/128-channel tiles, and the 1 -> 32 channel 5x5 first layer on 28x28 inputs."""
+    from . import tc_conv
+
+    if not (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and conv.bias is not None and tc_conv.enabled()):
+        return None
+    k = pool.kernel_size if isinstance(pool.kernel_size, int) else (pool.kernel_size[0] if pool.kernel_size[0] == pool.kernel_size[1] else None)
+    ps = pool.stride if isinstance(pool.stride, int) else (pool.stride[0] if pool.stride[0] == pool.stride[1] else None)
+    pp = pool.padding if isinstance(pool.padding, int) else pool.padding[0]
+    if k != 2 or ps not in (1, 2) or pp != 0 or pool.ceil_mode or pool.return_indices or pool.dilation not in (1, (1, 1)):
+        return None
+    if conv.groups != 1 or conv.dilation != (1, 1) or conv.stride != (1, 1) or conv.padding_mode != "zeros" or isinstance(conv.padding, str):
+        return None
+    N, Cin, H, W = x.shape
+    Cout, KH = conv.out_channels, conv.kernel_size[0]
+    L = _lib.cuda()
+    if (Cin, Cout, H, W) == (1, 32, 28, 28) and conv.kernel_size == (5, 5) and conv.padding == (1, 1) and ps == 2:
+        return _ConvReluPool.apply(x, conv.weight, conv.bias, 2, "conv1")
+    if conv.padding != (0, 0) or conv.kernel_size[0] != conv.kernel_size[1] or Cout not in (32, 64, 128):
+        return None
+    if not L.pdl_tc_conv_supported(H, W, Cin, Cout, KH, KH, 1, 0, 1) or not L.pdl_tc_wgrad_supported(N, H, W, Cin, Cout, KH, KH, 1, 0):
+        return None
+    return _ConvReluPool.apply(x, conv.weight, conv.bias, ps, "tc")
+
+
+class _FlattenNCHW(torch.autograd.Function):
+    """``x.reshape(N, -1)`` of a channels-last activation in NCHW element order (what ``x.reshape(-1, 128 * 4 * 4)`` means in
+    the reference, launch_dist.py:39) as one first-party permute kernel each way."""
+
+    @staticmethod
+    def forward(ctx, x):
+        x = _nhwc(x)
+        N, C, H, W = x.shape
+        y = torch.empty((N, C * H * W), dtype=x.dtype, device=x.device)
+        _ok(_lib.cuda().pdl_permute_nhwc_nchw(_p(x), _p(y), N, H * W, C, 1, _stream(x)), "flatten")
+        ctx.geom = (N, C, H, W)
+        return y
+
+    @staticmethod
+    def backward(ctx, dy):
+        N, C, H, W = ctx.geom
+        dy = dy.contiguous()
+        dx = torch.empty((N, C, H, W), dtype=dy.dtype, device=dy.device, memory_format=_CL)
+        _ok(_lib.cuda().pdl_permute_nhwc_nchw(_p(dy), _p(dx), N, H * W, C, 0, _stream(dy)), "unflatten")
+        return dx
+
+
+def flatten_nchw(x):
+    return _FlattenNCHW.apply(x)
 
 
 class _GlobalAvgPool(torch.autograd.Function):

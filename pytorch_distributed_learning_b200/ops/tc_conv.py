@@ -251,9 +251,12 @@ def conv2d_wgrad(x, dy, dw, db, stride, pad):
     from .functional import scratch
 
     sc = scratch(L.pdl_tc_wgrad_scratch_bytes_strided(N, H, W, Cin, Cout, KH, KW, stride, pad), x.device, "tc_wgrad")
-    db_part = None
-    if db is not None:
-        db_part = dy.sum(dim=(0, 2, 3)).reshape(1, Cout).contiguous()  # eager path only; the engine fuses this into pool-backward
-    _ok(L.pdl_tc_conv2d_wgrad_strided(_p(x), _p(dy), _p(dw), _p(db), _p(db_part), 1 if db is not None else 0, _p(sc), N, H, W, Cin, Cout,
+    db_part, parts = None, 0
+    if db is not None:  # bias gradient: per-split column sums of dy, folded in by the weight-gradient kernel's second pass
+        M = dy.shape[0] * dy.shape[2] * dy.shape[3]
+        parts = L.pdl_colsum_splits(M, Cout)
+        db_part = torch.empty((parts, Cout), dtype=dy.dtype, device=dy.device)
+        _ok(L.pdl_colsum_partial(_p(dy), _p(db_part), M, Cout, _stream(dy)), "bias gradient partial sums")
+    _ok(L.pdl_tc_conv2d_wgrad_strided(_p(x), _p(dy), _p(dw), _p(db), _p(db_part), parts, _p(sc), N, H, W, Cin, Cout,
                                       KH, KW, stride, pad, _p(error_flag(x.device)), _stream(x)), "tensor-core conv wgrad")
     return True

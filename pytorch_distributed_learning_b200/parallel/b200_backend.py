@@ -166,6 +166,10 @@ class B200ProcessGroup(dist.ProcessGroup):
         # device-side bound on every peer wait (a dead rank must not spin a kernel for the 10-minute host timeout)
         self.timeout_s = min(float(timeout_s), float(os.environ.get("PDL_KERNEL_TIMEOUT_S", "60")))
         self.device_index = device_index
+        # staging window of the group's own collectives (broadcast / allgather / allreduce of arbitrary tensors): 2 halves.  The
+        # world group gets 64 MiB halves; a sub-group (new_group) 8 MiB, so that every extra group does not pin 128 MiB.
+        default_mb = 64 if name in ("default_pg", "", None) or "default" in str(name) else 8
+        self.STAGING_BYTES = int(os.environ.get("PDL_STAGING_MB", default_mb)) << 20
         self._staging = None
         self._segments = []
         self._comm_stream = None
@@ -304,9 +308,22 @@ class B200ProcessGroup(dist.ProcessGroup):
         if W == 1:
             return tensor
         if tensor.dtype != torch.float32 or op not in (dist.ReduceOp.SUM, dist.ReduceOp.AVG):
-            host = tensor.detach().cpu()  # rare control-plane reductions (ints, MIN/MAX): host path
-            self._ctl.allreduce(host, op)
-            tensor.copy_(host)
+            # other dtypes / MIN / MAX / PRODUCT: gather every rank's tensor over peer memory (byte-level pull kernel) and reduce
+            # the W copies locally in rank order -- stays on the device and on the stream, identical result on every rank
+            stacked = torch.stack(self.allgather(tensor.detach()))
+            if op == dist.ReduceOp.SUM:
+                red = stacked.sum(0, dtype=tensor.dtype)
+            elif op == dist.ReduceOp.AVG:
+                red = stacked.sum(0, dtype=tensor.dtype) / W if tensor.is_floating_point() else torch.div(stacked.sum(0), W, rounding_mode="floor")
+            elif op == dist.ReduceOp.MIN:
+                red = stacked.amin(0)
+            elif op == dist.ReduceOp.MAX:
+                red = stacked.amax(0)
+            elif op == dist.ReduceOp.PRODUCT:
+                red = stacked.prod(0, dtype=tensor.dtype)
+            else:
+                raise ValueError("unsupported reduce op %r" % (op,))
+            tensor.copy_(red.to(tensor.dtype))
             return tensor
         st = self._stage()
         seg, half, L = st["seg"], st["half"], _lib.cuda()
@@ -452,6 +469,43 @@ class B200ReducerBackend:
         W = pg.size()
         self._pads = _ptr_array([self.seg.ptr(r) for r in range(W)])
 
+    # -- module buffers (BatchNorm running statistics) ------------------------------------------
+    def make_buffer_sync(self, buffers):
+        """DDP broadcasts rank 0's buffers before every forward (reference stack: two ncclBroadcast per forward for a
+        ResNet).  Here the buffers are moved ONCE into a block of symmetric memory -- same offsets on every
+        rank, every dtype, 16-byte aligned -- and the per-forward sync is a single kernel in which every replica pulls
+        rank 0's block over NVLink into its own (flag round before: rank 0's values are final; flag round after: rank 0 may
+        overwrite them).  No concatenation, no staging copies, no scatter.  Returns the callable, or None without buffers."""
+        bufs = [b for b in buffers if b is not None and b.is_cuda]
+        if not bufs:
+            return None
+        W, pg, L = self.pg.size(), self.pg, self.L
+        offs, off = [], 0
+        for b in bufs:
+            offs.append(off)
+            off = (off + b.numel() * b.element_size() + 15) // 16 * 16
+        pad = (L.pdl_signal_pad_bytes() + 4095) // 4096 * 4096
+        seg = pg.new_segment(pad + off, want_multicast=False)
+        state = pg.new_comm_state()
+        with torch.no_grad():
+            for b, o in zip(bufs, offs):
+                view = seg.tensor(pad + o, b.numel(), b.dtype).view(b.shape)
+                view.copy_(b)
+                b.data = view
+        srcs = _ptr_array([seg.ptr(r, pad) for r in range(W)])
+        pads = _ptr_array([seg.ptr(r) for r in range(W)])
+        dst = ctypes.c_void_p(seg.ptr(pg.rank(), pad))
+        n16 = off // 16
+        blocks = min(32, max(1, off >> 15))
+        keep = (seg, state, srcs, pads)
+
+        def sync():
+            stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+            _check(L.pdl_pull_launch(pg.rank(), W, 0, 0, n16, keep[2], dst, keep[3], ctypes.c_void_p(keep[1].data_ptr()), blocks, pg.timeout_s, stream),
+                   "buffer broadcast kernel")
+
+        return sync
+
     # -- signal-pad channels ------------------------------------------------------------------
     # A channel is one epoch counter + one set of flag slots.  Two kernels may share a channel only if they can never be in
     # flight together, i.e. they are ordered on one stream.  DDP's own buckets all run on pg.comm_stream and share the
@@ -580,7 +634,38 @@ class B200ReducerBackend:
                                            c["mc_in"], c["mc_out"], param, mom, hyper, ctypes.c_void_p(self.state.data_ptr()), c["blocks"],
                                            1.0 / world, self.pg.timeout_s, ctypes.c_void_p(stream_handle)), "bucket allreduce kernel")
 
+    def _bucket_handle(self, bk, world, algorithm):
+        c = self.bucket_launch_args(bk, world, algorithm)
+        h = c.get("handle")
+        if h is None:
+            h = ctypes.c_void_p()
+            row4 = c["n4"]
+            _check(self.L.pdl_bucket_create(c["algo"], self.pg.rank(), world, c["channel"], c["n4"], row4, c["in"], c["out"], c["ring"], self._pads,
+                                            c["mc_in"], c["mc_out"], ctypes.c_void_p(self.state.data_ptr()), c["blocks"], 1.0 / world,
+                                            self.pg.timeout_s, ctypes.byref(h)), "bucket handle")
+            c["handle"] = h
+        return h
+
     def reduce_bucket(self, bk, world, algorithm, fused=None):
+        if fused is None:
+            fused = bk.fused_group is not None
+        if not self.collect_stats:
+            # the hot path: ONE native call records "ready", orders the communication stream behind it, launches the fused
+            # kernel there and records "done" (csrc/cuda/allreduce.cu: pdl_bucket_reduce)
+            h = self._bucket_handle(bk, world, algorithm)
+            param = mom = hyper = None
+            if fused:
+                off = bk.offset * 4
+                param = ctypes.c_void_p(self.p_flat.data_ptr() + off)
+                if bk.fused_group[0].group_by_id(bk.fused_group[1])["momentum"] != 0:
+                    mom = ctypes.c_void_p(self.m_flat.data_ptr() + off)
+                hyper = ctypes.c_void_p(self._hyper_for(bk).data_ptr())
+            _check(self.L.pdl_bucket_reduce(h, param, mom, hyper, ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream),
+                                            ctypes.c_void_p(self.pg.comm_stream.cuda_stream)), "bucket allreduce kernel")
+            self._last_done = h
+            if fused:
+                bk.fused_group[0].mark_fused_done(bk.fused_params)
+            return
         comm = self.pg.comm_stream
         cur = torch.cuda.current_stream(self.device)
         ready = torch.cuda.Event()
@@ -604,9 +689,12 @@ class B200ReducerBackend:
             self._bw_end = torch.cuda.Event(enable_timing=True)
             self._bw_end.record(cur)
         if self._last_done is not None:
-            cur.wait_event(self._last_done)
-            if self.collect_stats:
-                self._exposed_ms.append((self._bw_end, self._last_done))
+            if isinstance(self._last_done, ctypes.c_void_p):  # native handle: buckets run in order on one stream, the last "done" covers all
+                _check(self.L.pdl_bucket_wait(self._last_done, ctypes.c_void_p(cur.cuda_stream)), "bucket wait")
+            else:
+                cur.wait_event(self._last_done)
+                if self.collect_stats:
+                    self._exposed_ms.append((self._bw_end, self._last_done))
         self._last_done = None
 
     def stats(self):

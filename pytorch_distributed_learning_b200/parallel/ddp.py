@@ -160,6 +160,9 @@ class DistributedDataParallel(nn.Module):
         self._sync_module_states()
         self._backend = self.process_group.make_reducer_backend(self.device) if hasattr(self.process_group, "make_reducer_backend") else _CpuReducerBackend(self.process_group)
         self._build_buckets(list(reversed(range(len(self._params)))))
+        self._buffer_sync = None
+        if self.broadcast_buffers and self._world > 1 and hasattr(self._backend, "make_buffer_sync"):
+            self._buffer_sync = self._backend.make_buffer_sync(list(self.module.buffers()))
         self._hook_handles = [p.register_post_accumulate_grad_hook(self._make_hook(i)) for i, p in enumerate(self._params)]
 
     # ------------------------------------------------------------------ construction
@@ -243,10 +246,15 @@ class DistributedDataParallel(nn.Module):
         if torch.is_grad_enabled() and self.require_backward_grad_sync:
             self._maybe_rebuild_buckets()
             self._prepare_for_backward()
+        else:
+            self._remove_grad_sinks()  # a local (no_sync / no-grad) pass must not write into the exchange arena
         if self.broadcast_buffers and self.require_backward_grad_sync:
-            bufs = list(self.module.buffers())
-            if bufs and self._world > 1:
-                self._broadcast_coalesced(bufs)
+            if self._buffer_sync is not None:
+                self._buffer_sync()  # ONE kernel: every replica pulls rank 0's buffer block over NVLink (K14)
+            else:
+                bufs = list(self.module.buffers())
+                if bufs and self._world > 1:
+                    self._broadcast_coalesced(bufs)
         if self.device.type == "cuda":
             inputs = tuple(self._to_device(x) for x in inputs)
             kwargs = {k: self._to_device(v) for k, v in kwargs.items()}
@@ -263,6 +271,27 @@ class DistributedDataParallel(nn.Module):
             bk.grads.clear()
         self._core.prepare(record_arrival=self._iteration == 0)  # pending counts, ready flags, launch cursor (C++)
         self._callback_queued = False
+        if self.device.type == "cuda" and self._comm_hook is None:
+            if not self._fused_checked:
+                self._resolve_fused_optimizers()  # may move the parameters into the flat arena: do it before forward saves them
+            self._install_grad_sinks()
+
+    def _install_grad_sinks(self):
+        """Tell the native backward functions where each parameter's gradient belongs (its view of the symmetric arena): their
+        kernels write it there and autograd adopts the alias as ``param.grad`` -- no gradient tensor of its own, no copy
+        into the bucket (``ops.functional.grad_buffer``).  Removed again when backward ends."""
+        from ..ops import functional as NF
+
+        self._sink_keys = [p.data_ptr() for p in self._params]
+        NF.install_grad_sinks({k: v for k, v in zip(self._sink_keys, self._in_views)})
+
+    def _remove_grad_sinks(self):
+        keys = getattr(self, "_sink_keys", None)
+        if keys:
+            from ..ops import functional as NF
+
+            NF.remove_grad_sinks(keys)
+            self._sink_keys = None
 
     def _maybe_rebuild_buckets(self):
         if self._rebuilt or self._iteration != 1:
@@ -349,6 +378,7 @@ class DistributedDataParallel(nn.Module):
 
     def _finalize_backward(self):
         self._callback_queued = False
+        self._remove_grad_sinks()
         if not self.require_backward_grad_sync:
             return
         for b in self._core.finalize():  # some parameters produced no gradient this iteration: they contribute zeros

@@ -240,3 +240,45 @@ def test_tc_dgrad_with_fused_pool_backward(case):
     ref = zr.grad.permute(0, 2, 3, 1)
     _tf32_close(dz, ref, scale_ref=da)
     torch.testing.assert_close(dbpart.sum(0), dz.sum((0, 1, 2)), rtol=2e-3, atol=2e-3 * dz.abs().sum((0, 1, 2)).max().item() / 10 + 1e-4)
+
+
+def test_convnet_eager_fused_blocks_match_torch():
+    """The reference's unchanged forward (launch_dist.py:35-41) on this package's layers takes the fused conv+ReLU+pool kernels
+    (``ops.functional.conv_relu_pool``) when TF32 convolutions are allowed; loss and every gradient must match torch's
+    strict-fp32 result within TF32 tolerance, and the bias gradients (pool-backward partials) exactly as closely."""
+    import copy
+
+    import pytorch_distributed_learning_b200 as pdl
+
+    torch.manual_seed(3)
+    ours = pdl.models.ConvNet().to(DEV)
+
+    class Ref(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.conv1, self.conv2, self.conv3 = torch.nn.Conv2d(1, 32, 5, 1, 1), torch.nn.Conv2d(32, 64, 3), torch.nn.Conv2d(64, 128, 3)
+            self.fc1 = torch.nn.Linear(2048, 10)
+
+        def forward(self, x):
+            x = F.max_pool2d(torch.relu(self.conv1(x)), 2, 2)
+            x = F.max_pool2d(torch.relu(self.conv2(x)), 2, 1)
+            x = F.max_pool2d(torch.relu(self.conv3(x)), 2, 2)
+            return self.fc1(x.reshape(-1, 2048))
+
+    ref = Ref().to(DEV)
+    ref.load_state_dict(copy.deepcopy(ours.state_dict()))
+    x, y = torch.randn(20, 1, 28, 28, device=DEV), torch.randint(0, 10, (20,), device=DEV)
+    assert tc_conv.enabled()
+    before = _lib.cuda().pdl_launch_count()
+    lo = pdl.nn.CrossEntropyLoss()(ours(x), y)
+    lo.backward()
+    launched = _lib.cuda().pdl_launch_count() - before
+    tc_conv.check_errors(DEV)
+    torch.backends.cudnn.allow_tf32 = False
+    lr = F.cross_entropy(ref(x), y)
+    lr.backward()
+    torch.backends.cudnn.allow_tf32 = True
+    assert abs(lo.item() - lr.item()) < 2e-3 * max(1.0, abs(lr.item()))
+    for (n, a), (_, b) in zip(ours.named_parameters(), ref.named_parameters()):
+        _tf32_close(a.grad, b.grad)
+    assert launched <= 30, "the fused path should need ~25 launches, saw %d" % launched
