@@ -39,6 +39,8 @@ def parse_args():
     p.add_argument("--model", choices=["convnet", "resnet18", "resnet50"], default="convnet")
     p.add_argument("--batch", type=int, default=None, help="per-rank batch (default: 100 ConvNet, 128 ResNet-18, 64 ResNet-50)")
     p.add_argument("--eager", action="store_true", help="ours: run the reference-style eager loop instead of the graphed TrainStep")
+    p.add_argument("--six-call", action="store_true", help="ours: the reference's loop body verbatim (model(x); criterion; zero_grad; backward; step) "
+                   "on this package's classes -- DistributedDataParallel defers the forward and replays the whole-iteration graph in backward()")
     p.add_argument("--e2e-sync", action="store_true", help="end-to-end loop: block on loss.item() after every step (default: read it one step late)")
     p.add_argument("--algorithm", default=None, help="ours: force an allreduce variant (oneshot|twoshot|ring|nvls)")
     p.add_argument("--local-rank", "--local_rank", type=int, default=None)
@@ -275,6 +277,16 @@ def main():
         model = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[local_rank], output_device=local_rank, algorithm=args.algorithm)
         train_step = pdl.TrainStep(model, criterion, optimizer, use_graph=not args.eager)
         step_fn = train_step
+        if args.six_call:
+            def step_fn(images, labels):  # loop body of launch_dist.py:82-92, unchanged
+                images = images.cuda(non_blocking=True)
+                labels = labels.cuda(non_blocking=True)
+                outputs = model(images)
+                loss = criterion(outputs, labels)
+                optimizer.zero_grad()
+                loss.backward()
+                optimizer.step()
+                return loss
 
         def barrier():
             torch.cuda.synchronize()
@@ -291,6 +303,8 @@ def main():
             dist.destroy_process_group()
         parallelism = "dp%d (P2P NVLink allreduce fused with SGD)" % world
         mode = "cuda-graph" if train_step.graphed else "eager"
+        if args.six_call:
+            mode = "six-call loop (deferred forward, graph replayed by loss.backward())"
 
     # ---------------- synthetic data: pool larger than L2 ----------------
     per_batch = batch * (shape[0] * shape[1] * shape[2]) * 4
@@ -314,6 +328,9 @@ def main():
         step_fn(dev_x[i % dev_pool], dev_y[i % dev_pool])
     if args.impl == "ours":
         kernels_per_step = train_step.kernels_per_step() or 0
+        if args.six_call:
+            engines = [e for e, _ in getattr(model, "_graph_engines", {}).values() if e is not None]
+            kernels_per_step = engines[0].kernels_per_step() if engines else 0
     start, stop = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps)]
     barrier()
@@ -344,7 +361,7 @@ def main():
     # issued), so neither arm drains the GPU per step; the last value is fetched before the closing event.  Reference:
     # loss.item() on the previous step's tensor.  Ours: TrainStep.step_async -> PendingLoss (pinned-host ring) with the
     # batch's H2D copy on a copy stream.  --e2e-sync restores a blocking .item() after every step in both arms.
-    if args.impl == "ours" and not args.e2e_sync:
+    if args.impl == "ours" and not args.e2e_sync and not args.six_call:
         e2e_step = train_step.step_async
     else:
         e2e_step = step_fn

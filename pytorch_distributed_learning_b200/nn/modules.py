@@ -82,6 +82,15 @@ class Linear(tnn.Linear):
 
 class CrossEntropyLoss(tnn.CrossEntropyLoss):
     def forward(self, logits, target):
+        from ..parallel.lazy_step import DeferredLoss, DeferredOutput
+
+        if isinstance(logits, DeferredOutput):
+            # the model's forward pass has not run yet (parallel/lazy_step.py): keep deferring when this is the loss the graphed
+            # step computes, otherwise ask for the real logits now
+            if (logits._value is None and isinstance(target, torch.Tensor) and target.dtype == torch.int64 and target.dim() == 1
+                    and self.weight is None and self.reduction == "mean" and self.label_smoothing == 0.0 and self.ignore_index == -100):
+                return DeferredLoss(logits, target, self)
+            logits = logits._tensor()
         if (_native(logits) and logits.dim() == 2 and target.dtype == torch.int64 and self.weight is None
                 and self.reduction == "mean" and self.label_smoothing == 0.0 and self.ignore_index == -100):
             from ..ops import functional as NF

@@ -131,6 +131,9 @@ class ConvNetEngine:
             self.g_views = [ddp._in_views[index_of[id(p)]] for p in self.params]
             self.avg_views = [ddp._avg_views[index_of[id(p)]] for p in self.params]
             self.world = ddp._world
+            # resolve variant / CTA count / push inbox of the whole-bucket kernel NOW (strict-fp32 schedule): the inbox is a
+            # collective allocation and must not happen while a graph is being captured
+            self.backend.bucket_launch_args(bk, self.world, ddp.algorithm)
         else:
             self.arena = _SoloArena(self.params, self.group, optimizer, self.device)
             a = self.arena
@@ -477,6 +480,8 @@ class ConvNetEngine:
         stager.consumed(slot, main)
         self.kernel_count = entry["kernels"]
         self.last_key = key
+        self.serial = getattr(self, "serial", 0) + 1
+        self._last_loss = s["buf"]["loss"]
         if self.ddp is not None:
             self.ddp._iteration += 1
         if pending:
@@ -487,6 +492,17 @@ class ConvNetEngine:
             handle, s["read"] = self._ring.publish(s["buf"]["loss"], self._d2h, after=stager.free[slot])
             return handle
         return s["buf"]["loss"]
+
+    def last_loss(self):
+        """Device scalar holding the most recent step's loss (static buffer: the next step on the same slot overwrites it)."""
+        return self._last_loss
+
+    def grad_views(self):
+        """(parameter, view of the averaged-gradient arena) pairs."""
+        return list(zip(self.params, self.avg_views))
+
+    def updated_params(self):
+        return self.params
 
     def kernels_per_step(self):
         return self.kernel_count

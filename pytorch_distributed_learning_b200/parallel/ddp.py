@@ -103,7 +103,7 @@ def _align(n, a=_ALIGN_ELEMS):
 class DistributedDataParallel(nn.Module):
     def __init__(self, module, device_ids=None, output_device=None, dim=0, broadcast_buffers=True, process_group=None,
                  bucket_cap_mb=25, find_unused_parameters=False, check_reduction=False, gradient_as_bucket_view=True,
-                 static_graph=False, algorithm=None, first_bucket_mb=1, fused_optimizer=None):
+                 static_graph=False, algorithm=None, first_bucket_mb=1, fused_optimizer=None, graph_step=None):
         """``fused_optimizer`` (default on; ``PDL_FUSED_OPTIMIZER=0`` or ``False`` turns it off): when the parameters belong to
         this package's ``optim.SGD`` the bucket kernel applies the update itself, i.e. the weights change DURING
         ``loss.backward()`` and ``optimizer.step()`` has nothing left to do.  Anything placed between ``backward()`` and
@@ -111,6 +111,13 @@ class DistributedDataParallel(nn.Module):
         the kernel then only averages, ``.grad`` holds the averaged gradient and ``step()`` performs the whole update, exactly
         like the reference's loop (launch_dist.py:91-92)."""
         super().__init__()
+        # graph_step: run the reference's unchanged six-call loop on the whole-iteration CUDA graph (parallel/lazy_step.py).
+        # None = automatic for the model families this package ships (ConvNet, ResNet) on a GPU; True = also for any other
+        # model built from capturable ops; False (or PDL_TRANSPARENT_GRAPH=0) = every call runs when it is made.
+        from . import lazy_step as _lazy
+
+        self._graph_step = ("auto" if _lazy.enabled_by_default() else False) if graph_step is None else bool(graph_step)
+        self._graph_engines = {}
         if fused_optimizer is None:
             fused_optimizer = os.environ.get("PDL_FUSED_OPTIMIZER", "1") != "0"
         self.fused_optimizer = bool(fused_optimizer)
@@ -237,6 +244,61 @@ class DistributedDataParallel(nn.Module):
 
     # ------------------------------------------------------------------ forward
     def forward(self, *inputs, **kwargs):
+        if self._graph_step is not False and self._can_defer(inputs, kwargs):
+            from .lazy_step import DeferredOutput
+
+            return DeferredOutput(self, inputs[0])
+        return self._forward_traced(*inputs, **kwargs)
+
+    def _can_defer(self, inputs, kwargs):
+        from . import lazy_step as _lazy
+
+        if (kwargs or len(inputs) != 1 or not isinstance(inputs[0], torch.Tensor) or self.device.type != "cuda" or not self.training
+                or not torch.is_grad_enabled() or not self.require_backward_grad_sync or self._comm_hook is not None
+                or not self.fused_optimizer or not getattr(self._backend, "supports_fused_sgd", False) or _lazy.suspended()):
+            return False
+        if self._graph_step is True:
+            return True
+        from ..models.convnet import ConvNet
+        from ..models.resnet import ResNet
+
+        return isinstance(self.module, (ConvNet, ResNet))
+
+    def _forward_now(self, images):
+        """The real forward pass of a deferred call (something needed the outputs before ``loss.backward()``)."""
+        from . import lazy_step as _lazy
+
+        with _lazy.suspend():
+            return self._forward_traced(images)
+
+    def _graph_engine(self, criterion):
+        """The whole-iteration graph for (this model, ``criterion``, the optimizer that owns the parameters), or None when the
+        combination is not one the graphed step covers -- the caller then runs eagerly, and so does every later call."""
+        if self._graph_step is False:
+            return None
+        key = id(criterion)
+        if key in self._graph_engines:
+            return self._graph_engines[key][0]
+        from ..optim.sgd import lookup_optimizer
+
+        owners = {id(o[0]): o[0] for o in (lookup_optimizer(p) for p in self._params) if o is not None}
+        engine = None
+        if len(owners) == 1 and all(lookup_optimizer(p) is not None for p in self._params):
+            opt = next(iter(owners.values()))
+            from ..ops.convnet_engine import ConvNetEngine
+
+            engine = ConvNetEngine.try_create(self, criterion, opt)
+            if engine is None:
+                from .graph_engine import GenericGraphEngine
+
+                if GenericGraphEngine.supports(criterion):
+                    engine = GenericGraphEngine(self, criterion, opt)
+        self._graph_engines[key] = (engine, criterion)  # keeps the criterion alive: ids are only unique among live objects
+        if engine is None:
+            self._graph_step = False
+        return engine
+
+    def _forward_traced(self, *inputs, **kwargs):
         if _tracing.enabled():
             with _tracing.trace_range("pdl.DistributedDataParallel.forward", iteration=self._iteration):
                 return self._forward(*inputs, **kwargs)

@@ -21,6 +21,7 @@ class GenericGraphEngine:
         self.graphs = {}
         self._kernel_count = 0
         self._out = self._last = None
+        self._grad_views = []
         self._ring = None  # pinned loss ring, created by the first step(pending=True)
 
     # -- helpers ---------------------------------------------------------------------------
@@ -28,10 +29,31 @@ class GenericGraphEngine:
         keys = ("lr", "momentum", "dampening", "weight_decay", "nesterov")
         return tuple(tuple(g.get(k) for k in keys) for g in self.optimizer.param_groups)
 
+    @staticmethod
+    def supports(criterion):
+        """Losses whose scalar result the engine can hand back: any module returning a 0-dim tensor works in principle; the
+        transparent six-call mode only trusts this package's mean cross entropy."""
+        from ..nn.modules import CrossEntropyLoss
+
+        return isinstance(criterion, CrossEntropyLoss)
+
+    def last_loss(self):
+        """Device scalar holding the most recent step's loss (the graph's static buffer)."""
+        return self._last["loss"]
+
+    def grad_views(self):
+        """(parameter, tensor that holds its averaged gradient after a replay) pairs."""
+        return self._grad_views
+
+    def updated_params(self):
+        """Parameters whose update happens inside the captured iteration (all of them: the capture ends with optimizer.step())."""
+        return [p for p, _ in self._grad_views]
+
     def _eager_step(self, x, y):
         from ..ops import tc_conv
+        from . import lazy_step as _lazy
 
-        with tc_conv.prepacked(self.model):  # one launch packs every conv weight for the tensor cores (fwd + dgrad copies)
+        with _lazy.suspend(), tc_conv.prepacked(self.model):  # one launch packs every conv weight for the tensor cores (fwd + dgrad copies)
             out = self.model(x)
             self._out = out.detach()
             loss = self.criterion(out, y)
@@ -94,6 +116,7 @@ class GenericGraphEngine:
         with torch.cuda.graph(g):
             loss = self._eager_step(x, y)
         self._kernel_count = int(L.pdl_launch_count() - before)  # launcher calls of this library inside one iteration
+        self._grad_views = [(p, p.grad) for p in params if p.grad is not None]
         return {"graph": g, "x": x, "y": y, "loss": loss, "out": self._out, "hyper": self._hyper_signature()}
 
     def step(self, images, labels, pending=False):
@@ -122,6 +145,7 @@ class GenericGraphEngine:
             refresh_inputs(entry["x"], entry["y"], images, labels)
         entry["graph"].replay()
         self._last = entry
+        self.serial = getattr(self, "serial", 0) + 1
         if hasattr(self.model, "_iteration"):
             self.model._iteration += 1
         if pending:

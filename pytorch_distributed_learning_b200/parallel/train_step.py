@@ -86,16 +86,19 @@ class TrainStep:
         return self._ring.publish(loss, torch.cuda.current_stream(loss.device))[0]
 
     def _eager(self, images, labels):
+        from . import lazy_step as _lazy
+
         dev = next(self.model.parameters()).device
         if images.device != dev:
             images = images.to(dev, non_blocking=True)
             labels = labels.to(dev, non_blocking=True)
-        out = self.model(images)
-        self._out = out.detach()
-        loss = self.criterion(out, labels)
-        self.optimizer.zero_grad()
-        loss.backward()
-        self.optimizer.step()
+        with _lazy.suspend():  # use_graph=False means call by call: no transparent graph either
+            out = self.model(images)
+            self._out = out.detach()
+            loss = self.criterion(out, labels)
+            self.optimizer.zero_grad()
+            loss.backward()
+            self.optimizer.step()
         return loss.detach()
 
     def outputs(self):

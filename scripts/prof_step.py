@@ -1,6 +1,8 @@
 """In-situ kernel timeline of the graphed training step (torch.profiler / CUPTI on graph replays): per-kernel totals
 inside the CUDA graph, warm caches, real overlap -- unlike ncu's serialised cold-cache launch list.
-Usage: prof_step.py [convnet|resnet18|resnet50] [batch] [steps]"""
+Usage: prof_step.py [convnet|resnet18|resnet50] [batch] [steps]      (PDL_PROF_DDP=1: wrap the model in DistributedDataParallel,
+world size 1, so that the reducer path -- gradient sinks, bucket kernels, fused SGD -- is part of the captured iteration)"""
+import os
 import collections
 import sys
 
@@ -18,6 +20,11 @@ torch.manual_seed(0)
 model = (pdl.models.ConvNet() if name == "convnet" else getattr(pdl.models, name)(num_classes=classes)).cuda()
 kw = dict(lr=1e-4) if name == "convnet" else dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)
 opt = pdl.optim.SGD(model.parameters(), **kw)
+if os.environ.get("PDL_PROF_DDP", "0") == "1":
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    os.environ.setdefault("MASTER_PORT", "29541")
+    pdl.distributed.init_process_group("nccl", world_size=1, rank=0)
+    model = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[0])
 step = pdl.TrainStep(model, pdl.nn.CrossEntropyLoss(), opt)
 x = torch.randn((N,) + shape).cuda()
 y = torch.randint(0, classes, (N,)).cuda()

@@ -99,7 +99,7 @@ def test_ddp_world1_b200_backend(ours_optim):
         state = copy.deepcopy(model.state_dict())
         kw = dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)
         opt = (pdl.optim.SGD if ours_optim else torch.optim.SGD)(model.parameters(), **kw)  # optimizer BEFORE the wrap, like launch_dist.py
-        ddp = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[0], output_device=0)
+        ddp = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[0], output_device=0, graph_step=False)  # call by call: the hook path
         crit = pdl.nn.CrossEntropyLoss().cuda(0)
         g = torch.Generator().manual_seed(1)
         batches = [(torch.randn(12, 1, 28, 28, generator=g), torch.randint(0, 10, (12,), generator=g)) for _ in range(4)]
@@ -281,3 +281,51 @@ def test_resume_from_optimizer_state_dict_matches_uninterrupted_run(wrapped):
     finally:
         if wrapped:
             dist.destroy_process_group()
+
+
+def test_six_call_loop_runs_on_the_graphed_step():
+    """The reference's loop body, unchanged (launch_dist.py:86-92), on a wrapped ConvNet: forward is deferred, ``loss.backward()``
+    replays the whole-iteration graph, ``optimizer.step()`` finds the update done.  Must follow the same trajectory as an explicit
+    ``TrainStep`` and as torch; ``loss.item()`` and the outputs are readable afterwards; touching the outputs BEFORE backward
+    falls back to the ordinary eager pass for that iteration."""
+    from pytorch_distributed_learning_b200.parallel.lazy_step import DeferredLoss, DeferredOutput
+
+    dist = pdl.distributed
+    dist.init_process_group("nccl", init_method="tcp://127.0.0.1:%d" % free_port(), world_size=1, rank=0)
+    try:
+        torch.manual_seed(0)
+        model = pdl.models.ConvNet().cuda()
+        state = copy.deepcopy(model.state_dict())
+        kw = dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)
+        opt = pdl.optim.SGD(model.parameters(), **kw)
+        ddp = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[0], output_device=0)
+        crit = pdl.nn.CrossEntropyLoss().cuda(0)
+        g = torch.Generator().manual_seed(1)
+        batches = [(torch.randn(12, 1, 28, 28, generator=g), torch.randint(0, 10, (12,), generator=g)) for _ in range(5)]
+        losses, kinds = [], []
+        for i, (x, y) in enumerate(batches):
+            images, labels = x.cuda(non_blocking=True), y.cuda(non_blocking=True)
+            outputs = ddp(images)
+            if i == 2:
+                assert outputs.argmax(dim=1).shape == (12,)  # needs real logits now: this iteration runs eagerly
+            loss = crit(outputs, labels)
+            opt.zero_grad()
+            loss.backward()
+            opt.step()
+            kinds.append((type(outputs).__name__, type(loss).__name__, getattr(loss, "_engine", None) is not None))
+            losses.append(loss.item())
+            assert torch.max(outputs, 1)[1].shape == (12,)  # after the step: the graph's logits (or the eager tensor)
+            assert model.conv1.weight.grad is not None
+        assert kinds[0] == ("DeferredOutput", "DeferredLoss", True) and kinds[1][2] and kinds[3][2] and kinds[4][2]
+        assert kinds[2][2] is False, "an iteration whose outputs were used before backward() must not replay the graph"
+        assert isinstance(outputs, DeferredOutput) and isinstance(loss, DeferredLoss)
+        ref, ref_losses = _reference_run(state, batches, kw)
+        torch.testing.assert_close(torch.tensor(losses), torch.tensor(ref_losses), rtol=1e-4, atol=1e-5)
+        for (n, a), (_, b) in zip(model.named_parameters(), ref.named_parameters()):
+            torch.testing.assert_close(a, b, rtol=1e-4, atol=5e-5, msg=lambda m, n=n: "%s: %s" % (n, m))
+        # evaluation and no_grad calls are ordinary tensors
+        ddp.eval()
+        with torch.no_grad():
+            assert isinstance(ddp(batches[0][0].cuda()), torch.Tensor)
+    finally:
+        dist.destroy_process_group()

@@ -22,7 +22,7 @@ def _collectives_worker(rank, world, port, outdir):
     dev = torch.device("cuda", rank)
     pg = dist._default()
     res = {}
-    for name in ["oneshot", "twoshot", "ring", "nvls"]:
+    for name in ["oneshot", "twoshot", "ring", "push", "nvls"]:
         for n in (7, 1000, 113674, 3_000_001):
             g = torch.Generator().manual_seed(100 + n)
             parts = [torch.randn(n, generator=g) for _ in range(world)]
@@ -65,7 +65,7 @@ def test_peer_memory_collectives(tmp_path, world):
         for k, v in res.items():
             if k.endswith("_identical"):
                 assert v, k
-            elif k.split("_")[0] in ("oneshot", "twoshot", "ring", "nvls") and isinstance(v, float):
+            elif k.split("_")[0] in ("oneshot", "twoshot", "ring", "push", "nvls") and isinstance(v, float):
                 assert v < 1e-4, (k, v)
         assert res["bcast"] and res["soak"] and res["max"] == world - 1
         assert res["gather"] == [float(i) for i in range(world)]
@@ -95,7 +95,8 @@ def _ddp_worker(rank, world, port, outdir, mode, algorithm):
     model = pdl.models.ConvNet().to(torch.device("cuda", rank))
     kw = dict(lr=0.02, momentum=0.9, weight_decay=1e-4, nesterov=True)
     opt = pdl.optim.SGD(model.parameters(), **kw) if mode != "torch_optim" else torch.optim.SGD(model.parameters(), **kw)
-    ddp = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[rank], output_device=rank, algorithm=algorithm)
+    ddp = pdl.nn.parallel.DistributedDataParallel(model, device_ids=[rank], output_device=rank, algorithm=algorithm,
+                                                  graph_step=None if mode == "sixcall" else False)  # "eager": the call-by-call hook path
     crit = pdl.nn.CrossEntropyLoss().cuda(rank)
     start = copy.deepcopy({k: v.cpu() for k, v in model.state_dict().items()})
     step = pdl.TrainStep(ddp, crit, opt) if mode == "graph" else None
@@ -119,7 +120,8 @@ def _ddp_worker(rank, world, port, outdir, mode, algorithm):
 
 
 @needs2
-@pytest.mark.parametrize("mode,algorithm", [("graph", None), ("eager", None), ("eager", "twoshot"), ("eager", "ring"), ("torch_optim", None)])
+@pytest.mark.parametrize("mode,algorithm", [("graph", None), ("sixcall", None), ("eager", None), ("eager", "twoshot"), ("eager", "ring"),
+                                            ("eager", "push"), ("eager", "oneshot"), ("torch_optim", None)])
 def test_ddp_convnet_two_gpus(tmp_path, mode, algorithm):
     world = 2
     pdl.multiprocessing.spawn(_ddp_worker, args=(world, free_port(), str(tmp_path), mode, algorithm), nprocs=world)
@@ -143,4 +145,4 @@ def test_ddp_convnet_two_gpus(tmp_path, mode, algorithm):
     for k, v in ref.state_dict().items():
         torch.testing.assert_close(res[0]["end"][k], v.cpu(), rtol=1e-4, atol=1e-5, msg=lambda m, k=k: "%s: %s" % (k, m))
     if mode != "torch_optim":
-        assert res[0]["stats"].get("fused_buckets", 0) > 0 or mode == "graph"
+        assert res[0]["stats"].get("fused_buckets", 0) > 0 or mode in ("graph", "sixcall")

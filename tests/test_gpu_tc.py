@@ -277,8 +277,13 @@ def test_convnet_eager_fused_blocks_match_torch():
     torch.backends.cudnn.allow_tf32 = False
     lr = F.cross_entropy(ref(x), y)
     lr.backward()
-    torch.backends.cudnn.allow_tf32 = True
+    strict = [p.grad.clone() for p in ref.parameters()]
+    torch.backends.cudnn.allow_tf32 = True  # torch's own TF32 convolutions: the yardstick for "TF32 tolerance" through 3 layers
+    ref.zero_grad()
+    F.cross_entropy(ref(x), y).backward()
     assert abs(lo.item() - lr.item()) < 2e-3 * max(1.0, abs(lr.item()))
-    for (n, a), (_, b) in zip(ours.named_parameters(), ref.named_parameters()):
-        _tf32_close(a.grad, b.grad)
+    for (n, a), b, t in zip(ours.named_parameters(), strict, [p.grad for p in ref.parameters()]):
+        mag = b.abs().max().item()
+        ours_err, torch_err = (a.grad - b).abs().max().item(), (t - b).abs().max().item()
+        assert ours_err <= max(3.0 * torch_err, 4e-3 * mag), "%s: ours %.3e vs torch-TF32 %.3e (|g| max %.3e)" % (n, ours_err, torch_err, mag)
     assert launched <= 30, "the fused path should need ~25 launches, saw %d" % launched
