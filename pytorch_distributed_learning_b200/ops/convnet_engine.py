@@ -131,9 +131,6 @@ class ConvNetEngine:
             self.g_views = [ddp._in_views[index_of[id(p)]] for p in self.params]
             self.avg_views = [ddp._avg_views[index_of[id(p)]] for p in self.params]
             self.world = ddp._world
-            # resolve variant / CTA count / push inbox of the whole-bucket kernel NOW (strict-fp32 schedule): the inbox is a
-            # collective allocation and must not happen while a graph is being captured
-            self.backend.bucket_launch_args(bk, self.world, ddp.algorithm)
         else:
             self.arena = _SoloArena(self.params, self.group, optimizer, self.device)
             a = self.arena
@@ -143,6 +140,10 @@ class ConvNetEngine:
         for p, v in zip(self.params, self.avg_views):
             p.grad = v
         self._setup_split()
+        if ddp is not None:
+            # resolve variant / CTA count / push inbox of the whole-bucket kernel NOW (strict-fp32 schedule): the inbox is a
+            # collective allocation and must not happen while a graph is being captured
+            self.backend.bucket_launch_args(self.bucket, self.world, ddp.algorithm)
         optimizer.add_reload_listener(self._on_optimizer_reload)
         self.graphs = {}
         self.kernel_count = 0
