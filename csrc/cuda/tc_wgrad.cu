@@ -228,6 +228,9 @@ int act_map(CUtensorMap* m, const float* base, int N, int H, int W, int C, int b
 
 int env_int(const char* name, int dflt) { const char* v = getenv(name); return v ? atoi(v) : dflt; }
 
+// Upper bound on the CTAs of the next weight-gradient launches (0 = none); see pdl_tc_wgrad_max_ctas.
+int g_wg_cta_cap = 0;
+
 // Channel tiles: M (= Cout) tile 128 (64 when Cout == 64).  N (= Cin) tile as wide as the TMEM budget allows --
 // every operand byte comes through L2 (~42 B/clk/SM), so FLOPs per loaded byte is what bounds this kernel:
 // 1x1 filters take 256 / 128 columns, filter rows of up to 3 taps 128 (3 accumulators = 384 TMEM columns).
@@ -260,7 +263,8 @@ bool wg_geometry(int N, int P, int Q, int Cin, int Cout, int KH, int KW, int pad
   if (KH * tiles < 74) splits = 148 / (KH * tiles);  // few big tiles: one wave, each split costs a full dW of partial traffic
   if (splits > 148) splits = 148;
   {
-    static const int cta_cap = env_int("PDL_WG_MAX_CTAS", 0);  // experiment knob: bound the grid (KH * splits * tiles)
+    static const int env_cap = env_int("PDL_WG_MAX_CTAS", 0);  // experiment knob: bound the grid (KH * splits * tiles)
+    const int cta_cap = env_cap > 0 ? env_cap : g_wg_cta_cap;
     if (cta_cap > 0 && KH * tiles * splits > cta_cap) splits = cta_cap / (KH * tiles) > 0 ? cta_cap / (KH * tiles) : 1;
   }
   if (splits > g->units) splits = g->units;
@@ -291,6 +295,17 @@ int launch_wg(const CUtensorMap& a, const CUtensorMap& b, const WgGeom& g, int K
 }
 
 }  // namespace
+
+// Bound the grid of the weight-gradient launches that follow (0 lifts the bound); returns the previous value.  A caller
+// that runs a small weight gradient NEXT TO other kernels uses this: every CTA of these kernels takes a whole SM's shared
+// memory, so a one-wave grid makes concurrent kernels queue for SMs, while a third of a wave leaves room for them (and
+// leaves the second pass a third of the partial sums).  Measured on the batch-100 ConvNet step: 124.9 us with the one-wave
+// grid, 116.9 us with 48 CTAs, 123-124 us at 36 or 60.  Host-side setting, read when a launch is issued (or captured).
+PDL_API int pdl_tc_wgrad_max_ctas(int cap) {
+  const int old = g_wg_cta_cap;
+  g_wg_cta_cap = cap < 0 ? 0 : cap;
+  return old;
+}
 
 PDL_API int pdl_tc_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad) {
   if (stride != 1 && stride != 2) return 0;

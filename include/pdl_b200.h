@@ -121,6 +121,9 @@ int pdl_tc_conv2d_fwd_strided(const float* x, const float* packed_w, const float
 int pdl_tc_conv2d_dgrad(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
                         int* error_flag, cudaStream_t stream);
 int pdl_tc_wgrad_supported(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);
+/* bound the CTA count of the weight-gradient launches that follow (0 = no bound; returns the previous bound): for small
+ * weight gradients that run next to other kernels, see tc_wgrad.cu */
+int pdl_tc_wgrad_max_ctas(int cap);
 long long pdl_tc_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad);
 int pdl_tc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch, int N,
                         int H, int W, int Cin, int Cout, int KH, int KW, int pad, int* error_flag, cudaStream_t stream);

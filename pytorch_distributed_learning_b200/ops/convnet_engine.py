@@ -147,8 +147,10 @@ class ConvNetEngine:
         optimizer.add_reload_listener(self._on_optimizer_reload)
         self.graphs = {}
         self.kernel_count = 0
-        self._branch = torch.cuda.Stream(device=self.device)   # off-critical-path kernels (see _record_tc): pack, fc1 wgrad
-        self._branch2 = torch.cuda.Stream(device=self.device)  # conv3 / conv2 weight gradients
+        bprio = -1 if os.environ.get("PDL_CONVNET_PRIORITY", "0") == "2" else 0
+        self._branch = torch.cuda.Stream(device=self.device, priority=bprio)   # off-critical-path kernels (see _record_tc): pack, fc1 wgrad
+        self._branch2 = torch.cuda.Stream(device=self.device, priority=bprio)  # conv3 / conv2 weight gradients
+        self._capture_stream = torch.cuda.Stream(device=self.device, priority=-1)  # the main chain: high priority (see _build)
         self._ring = self._d2h = None  # pinned loss ring + its copy stream, created by the first step(pending=True)
 
     def _on_optimizer_reload(self, first):
@@ -278,8 +280,14 @@ class ConvNetEngine:
             self._record(b, N, side.cuda_stream, reduce=False)
         torch.cuda.current_stream(dev).wait_stream(side)
         torch.cuda.synchronize(dev)
+        # Kernel nodes inherit the priority of the stream they were captured on.  The main chain is the step's critical path
+        # and the branch streams only carry work that has slack (weight gradients, their exchange), so the chain is captured
+        # on a HIGH-priority stream: whenever CTAs of both are waiting for SMs -- the tcgen05 kernels take a whole SM's shared
+        # memory each, so concurrent kernels queue for SMs rather than share them -- the chain's go first.
+        prio = os.environ.get("PDL_CONVNET_PRIORITY", "0") == "1"
+        cap = dict(stream=self._capture_stream) if prio else {}
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        with torch.cuda.graph(g, **cap):
             entry["kernels"] = self._record(b, N, torch.cuda.current_stream(dev).cuda_stream, reduce=True)
         entry["graph"] = g
         # Slot 1: the same iteration captured over a second set of input/loss buffers (everything else is shared --
@@ -289,7 +297,7 @@ class ConvNetEngine:
         b1["x"], b1["y"], b1["loss"] = torch.zeros_like(b["x"]), torch.zeros_like(b["y"]), torch.zeros_like(b["loss"])
         torch.cuda.synchronize(dev)
         g1 = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g1):
+        with torch.cuda.graph(g1, **cap):
             self._record(b1, N, torch.cuda.current_stream(dev).cuda_stream, reduce=True)
         from ..parallel.pipeline import InputStager
 
@@ -311,6 +319,16 @@ class ConvNetEngine:
         return k
 
     def _record_tc(self, b, N, stream_handle, reduce=False):
+        # the two weight gradients run beside the main chain: a third of a wave of CTAs each (see pdl_tc_wgrad_max_ctas)
+        # -- only while the step is latency-bound; at large batches the weight gradients need the whole machine
+        cap = int(os.environ.get("PDL_CONVNET_WG_CTAS", "48")) if N <= 256 else 0
+        old_cap = self.L.pdl_tc_wgrad_max_ctas(cap)
+        try:
+            return self._record_tc_impl(b, N, stream_handle, reduce)
+        finally:
+            self.L.pdl_tc_wgrad_max_ctas(old_cap)
+
+    def _record_tc_impl(self, b, N, stream_handle, reduce=False):
         """Tensor-core path: 15 launches (tcgen05 conv2/conv3 fwd+dgrad+wgrad, fused CUDA-core kernels for the rest).
 
         At batch 100 every kernel is a fraction of one wave and latency-bound, so the step time is the length of the
