@@ -22,41 +22,53 @@ __global__ void __launch_bounds__(kThreads) pool2_bwd_dbias_kernel(const float* 
                                                                    const float* __restrict__ pooled, float* __restrict__ dz,
                                                                    float* __restrict__ dbpart, unsigned total_pix, unsigned H, unsigned W,
                                                                    unsigned pix_per_cta) {
+  // A thread owns FOUR channels of a pixel (float4 / uchar4 accesses): C/4 threads per pixel, 1024/C pixels in flight per
+  // CTA, so a CTA's pixel range takes 4x fewer serial iterations than with one channel per thread -- this kernel sits on the
+  // step's critical path and is pure latency (13.5 us -> see profiles/convnet_timeline_w1.txt).
   const int PH = (static_cast<int>(H) - 2) / stride + 1, PW = (static_cast<int>(W) - 2) / stride + 1;
-  constexpr int G = kThreads / C;
-  const int c = threadIdx.x % C, grp = threadIdx.x / C;
-  float colsum = 0.f;
+  constexpr int C4 = C / 4;            // threads per pixel
+  constexpr int G = kThreads / C4;     // pixel lanes
+  const int q = threadIdx.x % C4, grp = threadIdx.x / C4;
+  float4 colsum = make_float4(0.f, 0.f, 0.f, 0.f);
   launch_dependents();     // successor may set up while this grid drains
   grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
   const unsigned p_lo = blockIdx.x * pix_per_cta;  // 32-bit index math: 64-bit div/mod made this kernel ALU-bound
   const unsigned p_hi = min(total_pix, p_lo + pix_per_cta);
-#pragma unroll 4
+  const float4* da4 = reinterpret_cast<const float4*>(da);
+  const float4* po4 = reinterpret_cast<const float4*>(pooled);
+  const uchar4* ix4 = reinterpret_cast<const uchar4*>(idx);
+#pragma unroll 2
   for (unsigned px = p_lo + grp; px < p_hi; px += G) {
     const int w = static_cast<int>(px % W);
     const unsigned t = px / W;
     const int h = static_cast<int>(t % H);
     const int n = static_cast<int>(t / H);
-    float acc = 0.f;
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
     for (int k = 0; k < 4; ++k) {  // window whose element (r,s) = (k/2, k%2) is this pixel
-      const int r = k >> 1, s = k & 1;
-      const int ph_ = h - r, pw_ = w - s;
+      const int r = k >> 1, s2 = k & 1;
+      const int ph_ = h - r, pw_ = w - s2;
       const bool valid = ph_ >= 0 && pw_ >= 0 && (ph_ % stride) == 0 && (pw_ % stride) == 0 && (ph_ / stride) < PH && (pw_ / stride) < PW;
-      const int o = valid ? ((n * PH + ph_ / stride) * PW + pw_ / stride) * C + c : 0;  // branch-free: loads overlap
-      const float g = da[o], pv = pooled[o];
-      const int a = idx[o];
-      acc += (valid && a == k && pv > 0.f) ? g : 0.f;
+      const int o = valid ? ((n * PH + ph_ / stride) * PW + pw_ / stride) * C4 + q : 0;  // branch-free: loads overlap
+      const float4 g = da4[o], pv = po4[o];
+      const uchar4 a = ix4[o];
+      acc.x += (valid && a.x == k && pv.x > 0.f) ? g.x : 0.f;
+      acc.y += (valid && a.y == k && pv.y > 0.f) ? g.y : 0.f;
+      acc.z += (valid && a.z == k && pv.z > 0.f) ? g.z : 0.f;
+      acc.w += (valid && a.w == k && pv.w > 0.f) ? g.w : 0.f;
     }
-    colsum += acc;
-    dz[static_cast<size_t>(px) * C + c] = round_tf32(acc);  // operand of the tcgen05 dgrad / wgrad
+    colsum.x += acc.x; colsum.y += acc.y; colsum.z += acc.z; colsum.w += acc.w;
+    // operand of the tcgen05 dgrad / wgrad: rounded to TF32 by its producer
+    reinterpret_cast<float4*>(dz)[static_cast<size_t>(px) * C4 + q] = make_float4(round_tf32(acc.x), round_tf32(acc.y), round_tf32(acc.z), round_tf32(acc.w));
   }
-  __shared__ float cs[kThreads];
+  __shared__ float4 cs[kThreads];
   cs[threadIdx.x] = colsum;
   __syncthreads();
-  if (threadIdx.x < C) {
+  if (threadIdx.x < C) {  // channel c = 4 * q + j: sum the G pixel lanes in lane order (deterministic)
+    const int qq = threadIdx.x / 4, j = threadIdx.x % 4;
     float s = 0.f;
 #pragma unroll
-    for (int g = 0; g < G; ++g) s += cs[g * C + threadIdx.x];
+    for (int g = 0; g < G; ++g) s += reinterpret_cast<const float*>(&cs[g * C4 + qq])[j];
     dbpart[blockIdx.x * C + threadIdx.x] = s;
   }
 }
@@ -255,9 +267,9 @@ int c1_imgs_per_cta(int N) { int v = (N + 295) / 296; return v < 1 ? 1 : v; }
 int c1_blocks(int N) { int per = c1_imgs_per_cta(N); return (N + per - 1) / per; }
 
 int pool_pix_per_cta(long long total_pix, int C) {
-  const int G = kThreads / C;
+  const int G = kThreads / (C / 4);  // pixel lanes of pool2_bwd_dbias_kernel
   long long p = (total_pix + 511) / 512;  // at most ~512 CTAs (= rows of dbpart)
-  if (p < 8 * G) p = 8 * G;
+  if (p < 2 * G) p = 2 * G;
   return static_cast<int>((p + G - 1) / G * G);
 }
 

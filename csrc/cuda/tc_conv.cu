@@ -497,8 +497,13 @@ inline bool use_tma_store() {
 
 // CTAs of a launch over num_tiles (= m_tiles * n_tiles) tiles: balanced waves; with fused BatchNorm statistics also a
 // multiple of n_tiles, so that all tiles of a CTA share one column block (grid / n_tiles = rows of the partial buffer).
+// Upper bound on the CTAs of the forward / dgrad launches that follow (0 = the whole chip); see pdl_tc_conv_max_ctas.
+int g_tc_cta_cap = 0;
 int tc_grid(int num_tiles, int n_tiles, bool bn_stats) {
-  const int waves = (num_tiles + 147) / 148;
+  static const int env_cap = getenv("PDL_TC_MAX_CTAS") ? atoi(getenv("PDL_TC_MAX_CTAS")) : 0;
+  const int cap = env_cap > 0 ? env_cap : g_tc_cta_cap;
+  const int sms = (cap > 0 && cap < 148) ? cap : 148;
+  const int waves = (num_tiles + sms - 1) / sms;
   int grid = (num_tiles + waves - 1) / waves;
   if (bn_stats) {
     grid = grid / n_tiles * n_tiles;
@@ -583,6 +588,14 @@ static int n_gemm_for(int channels, bool wide = false, int m_tiles = 0) {  // co
 }
 // M tiles of a launch whose box was chosen by choose_box
 static int m_tiles_of(const TcGeom& g, int N) { return g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img; }
+
+// Bound the grid of the forward / dgrad launches that follow (0 lifts the bound); returns the previous value.  Same reason as
+// pdl_tc_wgrad_max_ctas: a caller that wants another kernel to run BESIDE this one leaves it some SMs.
+PDL_API int pdl_tc_conv_max_ctas(int cap) {
+  const int old = g_tc_cta_cap;
+  g_tc_cta_cap = cap < 0 ? 0 : cap;
+  return old;
+}
 
 PDL_API int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool) {
   if ((stride != 1 && stride != 2) || (stride == 2 && pool) || Cin % 32 || !n_gemm_for(Cout) || (pool && Cout > 128)) return 0;

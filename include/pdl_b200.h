@@ -107,6 +107,7 @@ int pdl_conv2d_wgrad_simt_noalloc(const float* x, const float* dy, float* dw, fl
 
 /* ---- convolution, tcgen05 tensor cores (TF32 in, fp32 accumulate in TMEM), TMA-fed (same reference lines) ---- */
 int pdl_tc_conv_supported(int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad, int pool);
+int pdl_tc_conv_max_ctas(int cap); /* bound the CTA count of the forward / dgrad launches that follow (0 = none); returns the old bound */
 int pdl_tc_pack_weights(const float* w, float* packed_fwd, float* packed_bwd, int Cout, int Cin, int taps, cudaStream_t stream);
 /* every convolution weight of a model in one launch (shared-memory tile transpose, both operand layouts): table
  * [num][6] int64 {w, fwd, bwd, Cout, Cin, taps} (device; channels % 32 == 0, taps <= pdl_tc_pack_max_taps()),

@@ -55,6 +55,7 @@ def declare(L):
     sig("pdl_conv2d_wgrad_simt", [P, P, P, P, P, I, I, I, I, I, I, I, I, I, P])
     # convolution (tcgen05 / TMA tensor-core path)
     sig("pdl_tc_conv_supported", [I, I, I, I, I, I, I, I, I])
+    sig("pdl_tc_conv_max_ctas", [I])
     sig("pdl_tc_pack_weights", [P, P, P, I, I, I, P])
     sig("pdl_tc_pack_max_taps", [])
     sig("pdl_tc_pack_weights_multi", [P, P, I, I, P])

@@ -400,7 +400,10 @@ class ConvNetEngine:
             # conv3's and conv2's gradients are final on this branch: exchange + SGD here, hidden behind the two kernels the
             # main chain still has to run
             self._launch_part("c32", branch2.cuda_stream); k += 1
+        d2cap = int(os.environ.get("PDL_CONVNET_DGRAD2_CTAS", "0")) if N <= 256 else 0
+        old = L.pdl_tc_conv_max_ctas(d2cap)  # conv2's dgrad and wgrad become ready together: leave the wgrad some SMs
         ok(L.pdl_tc_conv2d_dgrad(_p(b["dz2"]), _p(b["p2b"]), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 dgrad"); k += 1
+        L.pdl_tc_conv_max_ctas(old)
         if reduce and self.split is not None:
             self._launch_conv1_wgrad_comm(b, N, st); k += 1
         else:
