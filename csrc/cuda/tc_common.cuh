@@ -59,6 +59,15 @@ __device__ __forceinline__ void tma_load_4d(void* smem, const CUtensorMap* m, ui
                "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                : "memory");
 }
+// The same load delivered to the same shared-memory offset of every CTA in `mask` (bit i = cluster rank i), each signalling
+// its own copy of the mbarrier.  TMA multicast loads here read only this GPU's memory (packed weights / activations that
+// this process allocated on its own device); peer buffers are never given to a multicast tensor map.
+__device__ __forceinline__ void tma_load_2d_multicast(void* smem, const CUtensorMap* m, uint64_t* bar, int c0, int c1, uint16_t mask) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%4, %5}], [%2], %3;" ::"r"(
+                   smem_u32(smem)),
+               "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "h"(mask), "r"(c0), "r"(c1)
+               : "memory");
+}
 // Tile store smem -> global through the tensor map (bulk async group; out-of-range parts of the box are clipped).
 __device__ __forceinline__ void tma_store_4d(const CUtensorMap* m, const void* smem, int c0, int c1, int c2, int c3) {
   asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];" ::"l"(reinterpret_cast<uint64_t>(m)),
@@ -93,6 +102,21 @@ __device__ __forceinline__ void mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint6
 // mbarrier arrives once every MMA issued so far by this thread has completed.
 __device__ __forceinline__ void mma_commit(uint64_t* bar) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+// The same arrival on the mbarrier at this offset in every CTA of `mask`: "this stage's MMAs have retired" for a stage that
+// a cluster fills cooperatively (each CTA multicasts its share of the operand into everyone's stage).
+__device__ __forceinline__ void mma_commit_multicast(uint64_t* bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(smem_u32(bar)), "h"(mask)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// Barrier over all threads of all CTAs of the cluster (every thread must call it, converged).
+__device__ __forceinline__ void cluster_sync() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 // 32 lanes x 32 columns of fp32: thread t of the warp receives lane (warp%4)*32+t, columns [col, col+32)
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float* v) {

@@ -34,6 +34,8 @@ struct TcGeom {
   int tap_r0, tap_s0, tap_step, S_full;  // taps visited: (tap_r0 + r*tap_step, tap_s0 + s*tap_step) of an S_full-wide filter
   int out_stride, out_oh, out_ow, Hc;    // output pixel = (tile row * out_stride + out_oh, col * out_stride + out_ow); Hc tile-grid rows
   int n_tiles, ldc;      // N_GEMM-wide column tiles; ldc = total output channels (tile index = m_tile * n_tiles + n_tile)
+  const float* w_base;   // the packed weights behind tmB ([w_rows][w_K]): lets the launcher re-encode the map for CTA pairs
+  int w_rows, w_K;
 };
 
 struct EpiArgs {
@@ -65,7 +67,18 @@ struct Smem {
   static constexpr int TOTAL = BAR_OFFSET + 256 + 512 + 512 + 1024;  // + barriers + bias row + pool table + alignment slack
 };
 
-template <int N_GEMM, int EPI>
+// CL = 2: the kernel runs as clusters of two CTAs that work on two M tiles of the SAME column block in lock step and share
+// the weight tile: each CTA fetches half of it and TMA-multicasts that half into both CTAs' stage, so every weight byte
+// crosses L2 -> SM once per pair instead of once per CTA (these kernels are bound by exactly that traffic).  A stage may be
+// refilled only when BOTH CTAs' MMAs have retired, hence the multicast commit on the `empty` barriers (count 2).
+// Tiles are paired as (v, v ^ 1): virtual tile v -> pair p = v >> 1 -> (m tile 2 * (p / n_tiles) + (v & 1), n tile p % n_tiles).
+template <int CL>
+__device__ __forceinline__ void decode_tile(int tile, int n_tiles, int& mt, int& nt) {
+  if (CL == 1) { mt = tile / n_tiles; nt = tile % n_tiles; }
+  else { const int p = tile >> 1; mt = 2 * (p / n_tiles) + (tile & 1); nt = p % n_tiles; }
+}
+
+template <int N_GEMM, int EPI, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const __grid_constant__ CUtensorMap tmOut,
                const TcGeom g, const EpiArgs e) {
@@ -92,7 +105,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     tc::prefetch_tmap(&tmA);
     tc::prefetch_tmap(&tmB);
     if (EPI == EPI_STORE && e.tma_store) tc::prefetch_tmap(&tmOut);
-    for (int i = 0; i < kStages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], 1); }
+    for (int i = 0; i < kStages; ++i) { tc::mbar_init(&full[i], 1); tc::mbar_init(&empty[i], CL); }
     for (int i = 0; i < 2; ++i) { tc::mbar_init(&tfull[i], 1); tc::mbar_init(&tempty[i], kEpiWarps); }
     *failed = 0;
     tc::fence_barrier_init();
@@ -115,8 +128,10 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   }
   tc::tc_fence_before();
   __syncthreads();
+  if (CL > 1) tc::cluster_sync();  // the peer's barriers exist before anything is multicast at them
   tc::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  const uint32_t crank = CL > 1 ? tc::cluster_ctarank() : 0;
   if (threadIdx.x == 0) PDL_TRACE(1);
 
   const int ksteps = g.R * g.S * g.kchunks;
@@ -130,7 +145,8 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       uint32_t phase = 0;
       bool ok = true;
       for (int tile = blockIdx.x; tile < g.num_tiles && ok; tile += gridDim.x) {
-        const int mt = tile / g.n_tiles, nt = tile % g.n_tiles;
+        int mt, nt;
+        decode_tile<CL>(tile, g.n_tiles, mt, nt);
         const int n0 = g.BN > 1 ? mt * g.BN : mt / g.tiles_per_img;
         const int h0 = g.BN > 1 ? 0 : (mt % g.tiles_per_img) * g.BH;
         int tap = 0;
@@ -142,7 +158,11 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
               tc::mbar_expect_tx(&full[stage], stage_tx);
               tc::tma_load_4d(a_dst, &tmA, &full[stage], kc * 32, g.a_w0 + g.tap_sign * s, h0 * g.in_stride + g.a_h0 + g.tap_sign * r, n0);
               const int wtap = (g.tap_r0 + r * g.tap_step) * g.S_full + g.tap_s0 + s * g.tap_step;  // row block of the packed weights
-              tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, wtap * g.ldc + nt * N_GEMM);
+              if (CL == 1)
+                tc::tma_load_2d(a_dst + A_BYTES, &tmB, &full[stage], kc * 32, wtap * g.ldc + nt * N_GEMM);
+              else  // my half of the weight tile, into both CTAs' stage (tmB's box is N_GEMM / 2 rows here)
+                tc::tma_load_2d_multicast(a_dst + A_BYTES + crank * (SM::B_BYTES / 2), &tmB, &full[stage], kc * 32,
+                                          wtap * g.ldc + nt * N_GEMM + static_cast<int>(crank) * (N_GEMM / 2), static_cast<uint16_t>(0x3));
               if (tile == blockIdx.x && tap == 0 && kc == 0) PDL_TRACE(2);
               if (++stage == kStages) { stage = 0; phase ^= 1; }
             }
@@ -171,7 +191,8 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tc::mma_tf32(d_tmem, tc::smem_desc_sw128(a_addr + k * 32, 0, 1024), tc::smem_desc_sw128(b_addr + k * 32, 0, 1024), idesc,
                          (ks | k) != 0);
           }
-          tc::mma_commit(&empty[stage]);                      // frees the smem slot when these MMAs retire
+          if (CL == 1) tc::mma_commit(&empty[stage]);         // frees the smem slot when these MMAs retire
+          else tc::mma_commit_multicast(&empty[stage], static_cast<uint16_t>(0x3));  // ... in both CTAs: the slot is filled by both
           if (ks == ksteps - 1) tc::mma_commit(&tfull[acc]);  // accumulator complete -> epilogue
         }
         __syncwarp();
@@ -197,7 +218,8 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       if (*failed || !tc::mbar_wait(&tfull[acc], acc_phase)) { *failed = 1; break; }
       tc::tc_fence_after();
       if (tile == blockIdx.x && et == 0) PDL_TRACE(6);
-      const int mt = tile / g.n_tiles, nt = tile % g.n_tiles;
+      int mt, nt;
+      decode_tile<CL>(tile, g.n_tiles, mt, nt);
       const int n0 = g.BN > 1 ? mt * g.BN : mt / g.tiles_per_img;
       const int h0 = g.BN > 1 ? 0 : (mt % g.tiles_per_img) * g.BH;
       const uint32_t t_row = tmem_base + acc * N_GEMM + half * HALF + (static_cast<uint32_t>(quarter * 32) << 16);
@@ -426,8 +448,12 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
           for (int p = 0; p < PARTS; ++p) { s += staging[(p * 2) * PN + et]; q += staging[(p * 2 + 1) * PN + et]; }  // fixed order
           const float n = static_cast<float>(bn_count);
           const float mean = n > 0.f ? s / n : 0.f;
-          const int nt_mine = blockIdx.x % g.n_tiles;
-          float* o = e.bn_partial + (static_cast<long long>(blockIdx.x / g.n_tiles) * g.ldc + nt_mine * N_GEMM + pass * PN + et) * 3;
+          // every tile of this CTA has the same column block (the grid is a multiple of CL * n_tiles): its index, and this
+          // CTA's row among the grid / n_tiles CTAs that share it
+          const int cta = CL == 1 ? blockIdx.x : blockIdx.x >> 1;
+          const int nt_mine = cta % g.n_tiles;
+          const int split = CL == 1 ? cta / g.n_tiles : (cta / g.n_tiles) * 2 + (blockIdx.x & 1);
+          float* o = e.bn_partial + (static_cast<long long>(split) * g.ldc + nt_mine * N_GEMM + pass * PN + et) * 3;
           o[0] = n; o[1] = mean; o[2] = fmaxf(q - s * mean, 0.f);
         }
       }
@@ -436,6 +462,7 @@ tc_conv_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 
   tc::tc_fence_before();
   __syncthreads();
+  if (CL > 1) tc::cluster_sync();  // the peer may still multicast into this CTA's stages / arrive on its barriers until it is done
   if (threadIdx.x == 0) PDL_TRACE(8);
   if (warp == 2) tc::tmem_dealloc(tmem_base, kTmemCols);
   if (threadIdx.x == 0 && *failed && e.error) *e.error = 1;
@@ -512,18 +539,68 @@ int tc_grid(int num_tiles, int n_tiles, bool bn_stats) {
   return grid;
 }
 
+inline bool cta_pairs_allowed(int num_tiles, int n_tiles, int n_gemm);
+// CTAs of a launch, and whether it runs as CTA pairs (tc_conv_kernel<.., CL = 2>): the one place that decides both, shared by
+// the launcher and by the functions that size the BatchNorm-statistics buffer (rows = grid / n_tiles).
+inline int planned_grid(int num_tiles, int n_tiles, int n_gemm, bool bn_stats, bool* pairs_out) {
+  const bool pairs = cta_pairs_allowed(num_tiles, n_tiles, n_gemm);
+  if (pairs_out) *pairs_out = pairs;
+  if (!pairs) return tc_grid(num_tiles, n_tiles, bn_stats);
+  // pairs of CTAs step through pairs of tiles: balanced waves over 74 pairs; with fused statistics the pair count is a
+  // multiple of n_tiles so that every CTA keeps one column block
+  const int num_pairs = num_tiles / 2;
+  const int waves = (num_pairs + 73) / 74;
+  int pairs_n = (num_pairs + waves - 1) / waves;
+  if (bn_stats) {
+    pairs_n = pairs_n / n_tiles * n_tiles;
+    if (pairs_n < n_tiles) pairs_n = n_tiles;
+  }
+  return 2 * pairs_n;
+}
+
+// Whether a launch runs as CTA pairs sharing the weight tile (tc_conv_kernel<.., CL = 2>): an even number of M tiles (pairs
+// never straddle a column block), at least a wave of work (below that the kernels are latency-bound, and a pair must be
+// co-scheduled on one TPC), and a weight tile whose halves are whole swizzle atoms.
+inline bool cta_pairs_allowed(int num_tiles, int n_tiles, int n_gemm) {
+  static const int mode = getenv("PDL_TC_CLUSTER") ? atoi(getenv("PDL_TC_CLUSTER")) : 1;
+  if (mode == 0 || n_gemm < 64 || n_tiles > 74) return false;
+  const int m_tiles = num_tiles / n_tiles;
+  return (m_tiles % 2 == 0) && (mode == 2 || num_tiles >= 148);
+}
+
 template <int N_GEMM, int EPI>
 int launch_tc(const CUtensorMap& a, const CUtensorMap& b, const CUtensorMap& o, const TcGeom& g, const EpiArgs& e, cudaStream_t stream) {
   static bool configured = false;
-  auto kernel = tc_conv_kernel<N_GEMM, EPI>;
   if (!configured) {
-    PDL_CUDA_CHECK(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<N_GEMM>::TOTAL));
+    PDL_CUDA_CHECK(cudaFuncSetAttribute(tc_conv_kernel<N_GEMM, EPI, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<N_GEMM>::TOTAL));
+    PDL_CUDA_CHECK(cudaFuncSetAttribute(tc_conv_kernel<N_GEMM, EPI, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<N_GEMM>::TOTAL));
     configured = true;
   }
   // balanced waves: 200 tiles run as 100 CTAs x 2 tiles, not 148 CTAs of which 52 take two -- same makespan, and the
   // SMs left over go to whatever runs beside this kernel (the wgrad branch of the ConvNet graph)
-  const int grid = tc_grid(g.num_tiles, g.n_tiles, e.bn_partial != nullptr);
-  PDL_CUDA_CHECK(launch_dependent(kernel, dim3(grid), dim3(kThreads), Smem<N_GEMM>::TOTAL, stream, a, b, o, g, e));
+  bool pairs = false;
+  const int grid = planned_grid(g.num_tiles, g.n_tiles, N_GEMM, e.bn_partial != nullptr, &pairs);
+  if (pairs && g.w_base != nullptr) {
+    CUtensorMap bh;  // the same packed weights, box = half a column tile: each CTA of a pair fetches (and multicasts) one half
+    if (int rc = make_weight_map(&bh, g.w_base, g.w_rows, g.w_K, N_GEMM / 2)) return rc;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = Smem<N_GEMM>::TOTAL;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[2];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl_dependent_launch_enabled() ? 2 : 1;
+    PDL_CUDA_CHECK(cudaLaunchKernelEx(&cfg, tc_conv_kernel<N_GEMM, EPI, 2>, a, bh, o, g, e));
+    PDL_LAUNCH_CHECK();
+    return 0;
+  }
+  if (pairs) { pdl_set_error("tc_conv: a paired launch needs the weight description in its geometry"); return -3; }
+  PDL_CUDA_CHECK(launch_dependent(tc_conv_kernel<N_GEMM, EPI, 1>, dim3(grid), dim3(kThreads), Smem<N_GEMM>::TOTAL, stream, a, b, o, g, e));
   PDL_LAUNCH_CHECK();
   return 0;
 }
@@ -678,6 +755,7 @@ static int tc_fwd_impl(const float* x, const float* packed_w, const float* bias,
   CUtensorMap ta, tb;
   if (int rc = make_act_map(&ta, x, N, H, W, Cin, g.BW, g.BH, g.BN, stride)) return rc;
   if (int rc = make_weight_map(&tb, packed_w, KH * KW * Cout, Cin, ng)) return rc;
+  g.w_base = packed_w; g.w_rows = KH * KW * Cout; g.w_K = Cin;
   const int tma_store = pool_stride == 0 && use_tma_store();
   CUtensorMap to = ta;
   if (tma_store) { if (int rc = make_out_map(&to, y, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc; }
@@ -693,9 +771,10 @@ PDL_API int pdl_tc_conv_bn_splits(int N, int H, int W, int Cin, int Cout, int KH
   TcGeom g{};
   const int P = (H + 2 * pad - KH) / stride + 1, Q = (W + 2 * pad - KW) / stride + 1;
   if (!choose_box(P, Q, 0, &g)) return 0;
-  const int n_tiles = Cout / n_gemm_for(Cout, true, m_tiles_of(g, N));
+  const int ng = n_gemm_for(Cout, true, m_tiles_of(g, N));
+  const int n_tiles = Cout / ng;
   const int num_tiles = m_tiles_of(g, N) * n_tiles;
-  return tc_grid(num_tiles, n_tiles, true) / n_tiles;
+  return planned_grid(num_tiles, n_tiles, ng, true, nullptr) / n_tiles;
 }
 
 // Bias-free forward (stride 1|2) that also leaves the per-channel BatchNorm statistics of its output in bn_partial, in
@@ -771,6 +850,7 @@ static int dgrad_impl(const float* dy, const float* packed_w_bwd, float* dx, int
       g.a_h0 = (ph + pad - r0) / stride; g.a_w0 = (pw + pad - s0) / stride; g.tap_sign = -1;
       g.out_stride = stride; g.out_oh = ph; g.out_ow = pw; g.Hc = Hc;
       g.Nimg = N; g.Hout = H; g.Wout = W;
+      g.w_base = packed_w_bwd; g.w_rows = KH * KW * Cin; g.w_K = Cout;
       CUtensorMap ta;
       if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
       const int tma_store = stride == 1 && use_tma_store();  // parity classes scatter with a stride: direct stores
@@ -810,6 +890,7 @@ PDL_API int pdl_tc_conv2d_dgrad_poolbwd(const float* dy, const float* packed_w_b
   g.Nimg = N; g.Hout = H; g.Wout = W;
   CUtensorMap ta, tb;
   if (int rc = make_weight_map(&tb, packed_w_bwd, KH * KW * Cin, Cout, ng)) return rc;
+  g.w_base = packed_w_bwd; g.w_rows = KH * KW * Cin; g.w_K = Cout;
   if (int rc = make_act_map(&ta, dy, N, P, Q, Cout, g.BW, g.BH, g.BN)) return rc;
   EpiArgs e{dz, const_cast<uint8_t*>(idx), nullptr, 0, pool_stride, 0, error_flag, g_trace, pooled, dbpart};
   return dispatch_n<EPI_POOL_BWD>(ng, ta, tb, ta, g, e, stream);
@@ -917,6 +998,7 @@ static int stem_fwd_impl(const float* xp, const float* packed_w, const float* bi
     if (r != CUDA_SUCCESS) { pdl_set_error("cuTensorMapEncodeTiled(stem input, overlapping windows) failed: %d", (int)r); return -2; }
   }
   if (int rc = make_weight_map(&tb, packed_w, KH * Cout, 32, ng)) return rc;
+  g.w_base = packed_w; g.w_rows = KH * Cout; g.w_K = 32;
   const int tma_store = use_tma_store();
   CUtensorMap to = ta;
   if (tma_store) { if (int rc = make_out_map(&to, y, N, d.P, d.Q, Cout, g.BW, g.BH, g.BN)) return rc; }
@@ -934,9 +1016,10 @@ PDL_API int pdl_tc_stem_bn_splits(int N, int H, int W, int Cin, int Cout, int KH
   const tc::StemDims d = tc::stem_dims(H, W, KH, KW, stride, pad);
   TcGeom g{};
   if (!choose_box(d.P, d.Q, 0, &g)) return 0;
-  const int n_tiles = Cout / n_gemm_for(Cout);
+  const int ng = n_gemm_for(Cout);
+  const int n_tiles = Cout / ng;
   const int num_tiles = (g.BN > 1 ? (N + g.BN - 1) / g.BN : N * g.tiles_per_img) * n_tiles;
-  return tc_grid(num_tiles, n_tiles, true) / n_tiles;
+  return planned_grid(num_tiles, n_tiles, ng, true, nullptr) / n_tiles;
 }
 PDL_API int pdl_tc_stem_fwd_bnstats(const float* xp, const float* packed_w, float* y, float* bn_partial, int N, int H, int W, int Cout, int KH,
                                     int KW, int stride, int pad, int* error_flag, cudaStream_t stream) {

@@ -353,6 +353,7 @@ PDL_API int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* 
   else if (mt == 64 && nt == 32) rc = launch_wg<64, 32>(ta, tb, g, KH, scratch, error_flag, stream);
   else if (mt == 64 && nt == 64) rc = launch_wg<64, 64>(ta, tb, g, KH, scratch, error_flag, stream);
   if (rc) return rc;
+  if (dw == nullptr) return 0;  // GEMM pass only (pdl_tc_conv2d_wgrad_gemm); the second pass is launched separately
   const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
   PDL_CUDA_CHECK(launch_dependent(wgrad_finish_kernel, dim3(pdl_ceil_div(total, 256)), dim3(256), 0, stream, scratch, wg_splits(g), KH * KW, Cout, Cin, dw,
                                   db_partial, db_blocks, db));
@@ -438,6 +439,23 @@ PDL_API int pdl_tc_stem_wgrad(const float* xp, const float* dy, float* dw, float
   if (rc) return rc;
   const int total = Cout * Cin * KH * KW;
   stem_wgrad_finish_kernel<<<pdl_ceil_div(total, 256), 256, 0, stream>>>(scratch, wg_splits(g), Cout, Cin, KH, KW, dw);
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// The two passes of pdl_tc_conv2d_wgrad as separate launches (stride 1), so that a caller can put the split-K GEMM and its
+// deterministic second pass on different streams.  Both must see the same pdl_tc_wgrad_max_ctas setting.
+PDL_API int pdl_tc_conv2d_wgrad_gemm(const float* x, const float* dy, float* scratch, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
+                                     int* error_flag, cudaStream_t stream) {
+  return pdl_tc_conv2d_wgrad_strided(x, dy, nullptr, nullptr, nullptr, 0, scratch, N, H, W, Cin, Cout, KH, KW, 1, pad, error_flag, stream);
+}
+PDL_API int pdl_tc_conv2d_wgrad_finish(float* dw, float* db, const float* db_partial, int db_blocks, const float* scratch, int N, int H, int W, int Cin,
+                                       int Cout, int KH, int KW, int pad, cudaStream_t stream) {
+  WgGeom g{};
+  if (!wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KH, KW, pad, &g)) { pdl_set_error("tc wgrad: unsupported shape"); return -3; }
+  const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
+  PDL_CUDA_CHECK(launch_dependent(wgrad_finish_kernel, dim3(pdl_ceil_div(total, 256)), dim3(256), 0, stream, scratch, wg_splits(g), KH * KW, Cout, Cin, dw,
+                                  db_partial, db_blocks, db));
   PDL_LAUNCH_CHECK();
   return 0;
 }

@@ -128,6 +128,12 @@ int pdl_tc_wgrad_max_ctas(int cap);
 long long pdl_tc_wgrad_scratch_bytes(int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad);
 int pdl_tc_conv2d_wgrad(const float* x, const float* dy, float* dw, float* db, const float* db_partial, int db_blocks, float* scratch, int N,
                         int H, int W, int Cin, int Cout, int KH, int KW, int pad, int* error_flag, cudaStream_t stream);
+/* the two passes of pdl_tc_conv2d_wgrad (split-K GEMM into `scratch`; deterministic reduction of the partials + bias gradient)
+ * as separate launches, for callers that schedule them on different streams */
+int pdl_tc_conv2d_wgrad_gemm(const float* x, const float* dy, float* scratch, int N, int H, int W, int Cin, int Cout, int KH, int KW, int pad,
+                             int* error_flag, cudaStream_t stream);
+int pdl_tc_conv2d_wgrad_finish(float* dw, float* db, const float* db_partial, int db_blocks, const float* scratch, int N, int H, int W, int Cin,
+                               int Cout, int KH, int KW, int pad, cudaStream_t stream);
 int pdl_tc_conv2d_dgrad_strided(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                                 int stride, int pad, int* error_flag, cudaStream_t stream); /* stride 2 = four parity-class launches */
 long long pdl_tc_wgrad_scratch_bytes_strided(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);

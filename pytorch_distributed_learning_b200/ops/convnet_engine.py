@@ -393,9 +393,19 @@ class ConvNetEngine:
         else:
             ok(L.pdl_tc_conv2d_dgrad(_p(b["dz3"]), _p(b["p3b"]), _p(b["da2"]), N, 10, 10, 64, 128, 3, 3, 0, err, st), "conv3 dgrad"); k += 1
             ok(L.pdl_pool2_bwd_dbias(_p(b["da2"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 11, 11, 64, 1, st), "pool2 backward"); k += 1
-        branch2.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
-        ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
-                                 3, 3, 0, err, sb2), "conv2 wgrad"); k += 2
+        wg2_main = os.environ.get("PDL_CONVNET_WG2_MAIN", "0") == "1" and fork
+        if wg2_main:
+            # experiment: conv2's weight-gradient GEMM in the main chain (before the dgrad), only its second pass + the
+            # exchange on the branch -- the exchange then has the dgrad and conv1's wgrad to hide behind
+            main.wait_stream(branch2)  # wg_scratch: conv3's second pass must be done
+            ok(L.pdl_tc_conv2d_wgrad_gemm(_p(b["a1"]), _p(b["dz2"]), _p(b["wg_scratch"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 wgrad gemm"); k += 1
+            branch2.wait_stream(main)
+            ok(L.pdl_tc_conv2d_wgrad_finish(_p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64, 3, 3, 0, sb2),
+               "conv2 wgrad second pass"); k += 1
+        else:
+            branch2.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
+            ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
+                                     3, 3, 0, err, sb2), "conv2 wgrad"); k += 2
         if exchange:
             # conv3's and conv2's gradients are final on this branch: exchange + SGD here, hidden behind the two kernels the
             # main chain still has to run
