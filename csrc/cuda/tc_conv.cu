@@ -561,8 +561,12 @@ inline int planned_grid(int num_tiles, int n_tiles, int n_gemm, bool bn_stats, b
 // Whether a launch runs as CTA pairs sharing the weight tile (tc_conv_kernel<.., CL = 2>): an even number of M tiles (pairs
 // never straddle a column block), at least a wave of work (below that the kernels are latency-bound, and a pair must be
 // co-scheduled on one TPC), and a weight tile whose halves are whole swizzle atoms.
+// OPT-IN (PDL_TC_CLUSTER=1; 2 forces pairs on small launches too, which the tests use).  Measured on B200, ResNet-50 batch 64
+// (profiles/tc_conv_cta_pairs.md): every layer within +-2 % of the single-CTA kernel, the step 13.15 vs 13.09 ms.  Halving the
+// L2 READS of the weight tile does not help because what bounds these kernels is the bytes that LAND in each SM's shared
+// memory per MAC -- a multicast tile still arrives in full in both SMs.
 inline bool cta_pairs_allowed(int num_tiles, int n_tiles, int n_gemm) {
-  static const int mode = getenv("PDL_TC_CLUSTER") ? atoi(getenv("PDL_TC_CLUSTER")) : 1;
+  static const int mode = getenv("PDL_TC_CLUSTER") ? atoi(getenv("PDL_TC_CLUSTER")) : 0;
   if (mode == 0 || n_gemm < 64 || n_tiles > 74) return false;
   const int m_tiles = num_tiles / n_tiles;
   return (m_tiles % 2 == 0) && (mode == 2 || num_tiles >= 148);

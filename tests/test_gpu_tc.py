@@ -287,3 +287,41 @@ def test_convnet_eager_fused_blocks_match_torch():
         ours_err, torch_err = (a.grad - b).abs().max().item(), (t - b).abs().max().item()
         assert ours_err <= max(3.0 * torch_err, 4e-3 * mag), "%s: ours %.3e vs torch-TF32 %.3e (|g| max %.3e)" % (n, ours_err, torch_err, mag)
     assert launched <= 30, "the fused path should need ~25 launches, saw %d" % launched
+
+
+def test_cta_pair_variant_matches_single_cta():
+    """The opt-in CTA-pair kernel (cluster of 2, weight tile TMA-multicast to both CTAs, multicast commit on the stage barriers)
+    must give bit-identical results to the single-CTA kernel: same tiles, same MMAs, only the way the weight tile arrives in
+    shared memory differs.  Runs in a child process because the choice is read from PDL_TC_CLUSTER once per process."""
+    import os
+    import subprocess
+    import sys
+
+    code = r'''
+import torch, sys
+sys.path.insert(0, ".")
+from pytorch_distributed_learning_b200.ops import tc_conv
+torch.manual_seed(0)
+res = []
+for (N, Cin, H, Cout, k, pad) in [(8, 128, 28, 128, 3, 1), (4, 64, 56, 256, 1, 0), (6, 256, 14, 512, 1, 0)]:
+    x = torch.randn(N, Cin, H, H, device="cuda").contiguous(memory_format=torch.channels_last)
+    w = torch.randn(Cout, Cin, k, k, device="cuda") * 0.1
+    y = torch.empty((N, Cout, H, H), device="cuda").contiguous(memory_format=torch.channels_last)
+    handled, _, _ = tc_conv.conv2d_fwd(x, w, None, y, 1, pad, relu=False, want_bwd_pack=False, bn_stats=False)
+    assert handled
+    dx = torch.empty_like(x)
+    assert tc_conv.conv2d_dgrad(y, w, dx, 1, pad)
+    tc_conv.check_errors(x.device)
+    res += [y.cpu(), dx.cpu()]
+torch.save(res, sys.argv[1])
+'''
+    import tempfile
+
+    outs = []
+    for mode in ("0", "2"):
+        with tempfile.NamedTemporaryFile(suffix=".pt") as f:
+            env = dict(os.environ, PDL_TC_CLUSTER=mode)
+            subprocess.run([sys.executable, "-c", code, f.name], check=True, env=env, cwd=os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+            outs.append(torch.load(f.name))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
