@@ -133,7 +133,7 @@ __device__ void allreduce_body(const ARParams& p, int blk, int nblocks) {
   const int W = p.world, r = p.rank, tid = threadIdx.x;
   const uint32_t e = p.state->epoch[p.channel];
   const float inv = p.scale;
-  if (p.state->error != 0) {  // a previous collective of this communicator lost a peer: leave gradients and parameters untouched
+  if (__syncthreads_or(p.state->error != 0)) {  // a previous collective of this communicator lost a peer: leave gradients and parameters untouched
     retire(p, nblocks, 0, false);
     return;
   }
@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(kThreads) pull_kernel(CopyParams c) {
   p.state = c.state; p.rank = c.rank; p.world = c.world; p.channel = c.channel; p.timeout_ns = c.timeout_ns;
   const int blk = blockIdx.x, nblocks = gridDim.x;
   const uint32_t e = c.state->epoch[c.channel];
-  bool alive = c.state->error == 0;
+  bool alive = __syncthreads_or(c.state->error != 0) == 0;
   if (c.world > 1 && alive) { signal_peers(p, blk, e + 1); alive = wait_peers(p, blk, e + 1); }
   if (!alive) { retire(p, nblocks, 0, false); return; }
   long long per = (c.n16 + nblocks - 1) / nblocks, lo = per * blk, hi = min(c.n16, lo + per);

@@ -197,7 +197,8 @@ __global__ void __launch_bounds__(kC1Threads) conv1_wgrad_fused_kernel(const flo
     using namespace pdl_comm;
     const int W = tc.world, r = tc.rank;
     const uint32_t e = W > 1 ? tc.state->epoch[0] : 0u;  // no communicator state without peers
-    const bool dead = W > 1 && tc.state->error != 0;     // sticky: an earlier step lost a peer -> leave everything as it is
+    // sticky: an earlier step lost a peer -> leave everything as it is (decided once for the whole CTA)
+    const bool dead = __syncthreads_or(W > 1 && tc.state->error != 0) != 0;
     float* row = red + 2 * 832;              // this rank's finished gradient (also the W == 1 "sum")
     for (int i = threadIdx.x; i < 832; i += kC1Threads) {
       const float s = red[i] + red[832 + i];

@@ -13,7 +13,7 @@
 // filter row, K is split over CTAs, each CTA writes partial sums to a scratch buffer, and a second
 // kernel reduces the splits in fixed order (deterministic) into the gradient bucket and finishes the
 // bias gradient.  Replaces cuDNN wgrad + ATen bias reductions.
-#include "common.cuh"
+#include "comm.cuh"
 #include "tc_common.cuh"
 
 #include <cstdlib>
@@ -456,6 +456,154 @@ PDL_API int pdl_tc_conv2d_wgrad_finish(float* dw, float* db, const float* db_par
   const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
   PDL_CUDA_CHECK(launch_dependent(wgrad_finish_kernel, dim3(pdl_ceil_div(total, 256)), dim3(256), 0, stream, scratch, wg_splits(g), KH * KW, Cout, Cin, dw,
                                   db_partial, db_blocks, db));
+  PDL_LAUNCH_CHECK();
+  return 0;
+}
+
+// ------------------------------------------------------------------------------------------------------------------
+// Second pass of a split-K weight gradient FUSED with the cross-GPU exchange of that gradient and the SGD update: the
+// reference's "gradient ready -> bucket allreduce -> optimizer.step()" (launch_dist.py:91-92) for one layer in one kernel.
+// Output index space (= the layer's slice of the gradient arena): [db (Cout) | dw (Cout*Cin*taps)].  CTA 0 reduces the bias
+// partials, the other CTAs 256 weight outputs each (fixed split order: deterministic).  Then each CTA pushes its 256 values
+// into every peer's inbox ([2 parities][world][total] floats of symmetric memory), raises ONE flag per peer for its block,
+// waits for its peers' flags, sums the `world` inbox rows in rank order, and updates the parameters.  Same protocol and the
+// same parity argument as the push allreduce (allreduce.cu) -- the difference is that the value pushed never exists as a
+// separate tensor pass: the kernel that produces the gradient is the kernel that exchanges it.
+// ------------------------------------------------------------------------------------------------------------------
+namespace {
+struct FinishComm {
+  float* inbox[pdl_comm::kMaxWorld];
+  uint32_t* pad[pdl_comm::kMaxWorld];
+  pdl_comm::CommState* state;
+  float* raw;    // local gradient out (arena `in` slice), [db | dw]
+  float* avg;    // averaged gradient out
+  float* param;  // parameters / momentum in the same order (nullptr: average only)
+  float* mom;
+  SgdHyper* hyper;
+  int rank, world, channel;
+  float scale;
+  unsigned long long timeout_ns;
+};
+
+__global__ void __launch_bounds__(256) wgrad_finish_comm_kernel(const float* __restrict__ partial, int splits, int taps, int Cout, int Cin,
+                                                                const float* __restrict__ db_partial, int db_blocks, FinishComm fc) {
+  using namespace pdl_comm;
+  launch_dependents();
+  grid_dependency_wait();
+  const int per_split = taps * Cout * Cin;
+  const int total = Cout + per_split;
+  // ---- second pass: this thread's output ----
+  int i = -1;          // index in [db | dw]
+  float mine = 0.f;
+  if (blockIdx.x == 0) {  // bias gradient: 256 / Cout... threads per channel stride over the partial rows, fixed shuffle tree
+    const int tpc = 256 / Cout > 0 ? 256 / Cout : 1;  // Cout <= 256
+    const int co = threadIdx.x / tpc, sub = threadIdx.x % tpc;
+    float acc = 0.f;
+    if (co < Cout)
+      for (int b = sub; b < db_blocks; b += tpc) acc += db_partial[b * Cout + co];
+    for (int o = tpc >> 1; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (co < Cout && sub == 0) { i = co; mine = acc; }
+  } else {
+    const int e = (blockIdx.x - 1) * 256 + threadIdx.x;  // output layout [co][ci][tap]: coalesced writes
+    if (e < per_split) {
+      const int tap = e % taps, ci = (e / taps) % Cin, co = e / (taps * Cin);
+      const float* src = partial + (static_cast<long long>(tap) * Cout + co) * Cin + ci;
+      float acc = 0.f;
+#pragma unroll 8
+      for (int s = 0; s < splits; ++s) acc += __ldg(src + static_cast<long long>(s) * per_split);
+      i = Cout + e;
+      mine = acc;
+    }
+  }
+  if (i >= 0) fc.raw[i] = mine;
+  // ---- exchange ----
+  const int W = fc.world, r = fc.rank, blk = blockIdx.x;
+  float sum = mine;
+  if (W > 1) {
+    if (__syncthreads_or(fc.state->error != 0)) return;  // an earlier step lost a peer: leave parameters untouched
+    const uint32_t ep = fc.state->epoch[fc.channel];
+    const size_t row = (static_cast<size_t>(ep & 1u) * W + r) * total;
+    if (i >= 0) {
+#pragma unroll
+      for (int q = 0; q < kMaxWorld; ++q)
+        if (q < W && q != r) asm volatile("st.global.relaxed.sys.f32 [%0], %1;" ::"l"(fc.inbox[q] + row + i), "f"(mine) : "memory");
+    }
+    __syncthreads();
+    int failed = 0;
+    if (threadIdx.x < W && threadIdx.x != r) {
+      st_release_sys(fc.pad[threadIdx.x] + flag_index(fc.channel, blk, r), ep + 1);
+      failed = poll_flag(fc.pad[r] + flag_index(fc.channel, blk, threadIdx.x), ep + 1, fc.timeout_ns, fc.state) ? 0 : 1;
+    }
+    if (__syncthreads_or(failed)) return;
+    if (i >= 0) {
+      const float* base = fc.inbox[r] + static_cast<size_t>(ep & 1u) * W * total + i;
+      float v[kMaxWorld];
+#pragma unroll
+      for (int q = 0; q < kMaxWorld; ++q)
+        if (q < W && q != r) asm volatile("ld.global.relaxed.sys.f32 %0, [%1];" : "=f"(v[q]) : "l"(base + static_cast<size_t>(q) * total) : "memory");
+      sum = r == 0 ? mine : v[0];
+#pragma unroll
+      for (int q = 1; q < kMaxWorld; ++q)  // fixed rank order: every rank computes the same bits
+        if (q < W) sum += (q == r ? mine : v[q]);
+    }
+  }
+  if (i >= 0) {
+    const float avg = sum * fc.scale;
+    fc.avg[i] = avg;
+    if (fc.param != nullptr) {
+      const SgdHyper h = *fc.hyper;
+      const bool has_mom = fc.mom != nullptr && h.momentum != 0.0f;
+      float m = has_mom ? fc.mom[i] : 0.f;
+      fc.param[i] = sgd_update(fc.param[i], avg, &m, h, has_mom);
+      if (has_mom) fc.mom[i] = m;
+    }
+  }
+  // the last CTA to finish advances the epoch (all CTAs have read it by then) and clears the first-step flag
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t done = atomicAdd(&fc.state->finished[fc.channel], 1u);
+    if (done == gridDim.x - 1) {
+      fc.state->finished[fc.channel] = 0;
+      if (W > 1) fc.state->epoch[fc.channel] += 1;
+      if (fc.param != nullptr) fc.hyper->first_step = 0;
+      __threadfence();
+    }
+  }
+}
+}  // namespace
+
+// Floats of symmetric memory per rank the exchange needs: [2][world][Cout + Cout*Cin*KH*KW].
+PDL_API long long pdl_wgrad_finish_comm_inbox_floats(int world, int Cin, int Cout, int KH, int KW) {
+  return 2ll * world * (static_cast<long long>(Cout) + static_cast<long long>(Cout) * Cin * KH * KW);
+}
+PDL_API int pdl_wgrad_finish_comm_blocks(int Cin, int Cout, int KH, int KW) { return 1 + pdl_ceil_div(static_cast<long long>(Cout) * Cin * KH * KW, 256); }
+
+// Second pass of pdl_tc_conv2d_wgrad_gemm + exchange + SGD.  raw/avg/param/mom point at the layer's [db | dw] slice (bias first,
+// contiguous); inbox/pad: `world` peer-mapped pointers (pad: a signal pad; `channel` of it is used with one flag block per
+// CTA, so pdl_wgrad_finish_comm_blocks() must not exceed pdl_comm_max_blocks()); state: communicator state whose `channel` is
+// used by nothing else in flight.  world == 1: no exchange.  Must see the same pdl_tc_wgrad_max_ctas setting as the GEMM pass.
+PDL_API int pdl_tc_conv2d_wgrad_finish_comm(const float* scratch, const float* db_partial, int db_blocks, int N, int H, int W, int Cin, int Cout,
+                                            int KH, int KW, int pad_, float* raw, float* avg, float* param, float* mom, void* hyper, int rank,
+                                            int world, int channel, float* const* inbox, uint32_t* const* pad, void* state, double scale,
+                                            double timeout_s, cudaStream_t stream) {
+  WgGeom g{};
+  if (!wg_geometry(N, H + 2 * pad_ - KH + 1, W + 2 * pad_ - KW + 1, Cin, Cout, KH, KW, pad_, &g)) { pdl_set_error("tc wgrad: unsupported shape"); return -3; }
+  if (Cout > 256 || (256 % Cout) != 0) { pdl_set_error("wgrad finish+exchange: Cout must divide 256"); return -3; }
+  const int blocks = pdl_wgrad_finish_comm_blocks(Cin, Cout, KH, KW);
+  if (world < 1 || world > pdl_comm::kMaxWorld || channel < 0 || channel >= pdl_comm::kMaxChannels || !state) {
+    pdl_set_error("wgrad finish+exchange: bad world / channel / state");
+    return -1;
+  }
+  if (world > 1 && (blocks > pdl_comm::kMaxBlocks || !inbox || !pad)) { pdl_set_error("wgrad finish+exchange: too many blocks or peer pointers missing"); return -1; }
+  FinishComm fc{};
+  for (int q = 0; q < world && world > 1; ++q) { fc.inbox[q] = inbox[q]; fc.pad[q] = pad[q]; }
+  fc.state = static_cast<pdl_comm::CommState*>(state);
+  fc.raw = raw; fc.avg = avg; fc.param = param; fc.mom = mom; fc.hyper = static_cast<SgdHyper*>(hyper);
+  fc.rank = rank; fc.world = world; fc.channel = channel; fc.scale = static_cast<float>(scale);
+  fc.timeout_ns = static_cast<unsigned long long>(timeout_s * 1e9);
+  PDL_CUDA_CHECK(launch_dependent(wgrad_finish_comm_kernel, dim3(blocks), dim3(256), 0, stream, scratch, wg_splits(g), KH * KW, Cout, Cin, db_partial,
+                                  db_blocks, fc));
   PDL_LAUNCH_CHECK();
   return 0;
 }

@@ -134,6 +134,17 @@ int pdl_tc_conv2d_wgrad_gemm(const float* x, const float* dy, float* scratch, in
                              int* error_flag, cudaStream_t stream);
 int pdl_tc_conv2d_wgrad_finish(float* dw, float* db, const float* db_partial, int db_blocks, const float* scratch, int N, int H, int W, int Cin,
                                int Cout, int KH, int KW, int pad, cudaStream_t stream);
+/* second pass of pdl_tc_conv2d_wgrad_gemm FUSED with the cross-GPU exchange of the layer's gradient and its SGD update (reference:
+ * gradient -> bucket allreduce -> optimizer.step(), launch_dist.py:91-92, for one layer in one kernel): every CTA reduces its
+ * split-K partials, pushes the result into the peers' inboxes (symmetric memory, [2][world][Cout + Cout*Cin*KH*KW] floats),
+ * raises one flag per peer, sums the rows it received in rank order and updates the parameters.  raw/avg/param/mom: the
+ * layer's [db | dw] slice of the gradient / averaged-gradient / parameter / momentum arenas. */
+long long pdl_wgrad_finish_comm_inbox_floats(int world, int Cin, int Cout, int KH, int KW);
+int pdl_wgrad_finish_comm_blocks(int Cin, int Cout, int KH, int KW);
+int pdl_tc_conv2d_wgrad_finish_comm(const float* scratch, const float* db_partial, int db_blocks, int N, int H, int W, int Cin, int Cout, int KH,
+                                    int KW, int pad, float* raw, float* avg, float* param, float* mom, void* hyper, int rank, int world,
+                                    int channel, float* const* inbox, uint32_t* const* sigpad, void* state, double scale, double timeout_s,
+                                    cudaStream_t stream);
 int pdl_tc_conv2d_dgrad_strided(const float* dy, const float* packed_w_bwd, float* dx, int N, int H, int W, int Cin, int Cout, int KH, int KW,
                                 int stride, int pad, int* error_flag, cudaStream_t stream); /* stride 2 = four parity-class launches */
 long long pdl_tc_wgrad_scratch_bytes_strided(int N, int H, int W, int Cin, int Cout, int KH, int KW, int stride, int pad);

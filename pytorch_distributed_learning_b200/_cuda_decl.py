@@ -64,6 +64,9 @@ def declare(L):
     sig("pdl_tc_conv2d_dgrad", [P, P, P, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_wgrad_supported", [I, I, I, I, I, I, I, I, I])
     sig("pdl_tc_wgrad_max_ctas", [I])
+    sig("pdl_wgrad_finish_comm_inbox_floats", [I, I, I, I, I], LL)
+    sig("pdl_wgrad_finish_comm_blocks", [I, I, I, I])
+    sig("pdl_tc_conv2d_wgrad_finish_comm", [P, P, I, I, I, I, I, I, I, I, I, P, P, P, P, P, I, I, I, P, P, P, c_double, c_double, P])
     sig("pdl_tc_conv2d_wgrad_gemm", [P, P, P, I, I, I, I, I, I, I, I, P, P])
     sig("pdl_tc_conv2d_wgrad_finish", [P, P, P, I, P, I, I, I, I, I, I, I, I, P])
     sig("pdl_tc_wgrad_scratch_bytes", [I, I, I, I, I, I, I, I], LL)

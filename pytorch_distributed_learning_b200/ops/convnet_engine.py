@@ -35,11 +35,11 @@ class _SoloArena:
         self.g_avg = torch.zeros(off, dtype=torch.float32, device=device)
         self.p_flat = torch.zeros(off, dtype=torch.float32, device=device)
         self.m_flat = torch.zeros(off, dtype=torch.float32, device=device) if opt_group["momentum"] != 0 else None
-        self.states = [torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device=device) for _ in range(4)]
+        self.states = [torch.zeros(_lib.cuda().pdl_comm_state_bytes(), dtype=torch.uint8, device=device) for _ in range(5)]
         self.state = self.states[0]
         # one device-resident SgdHyper per kernel that applies an update (each clears its own first_step flag):
-        # [whole arena, fc1 part, conv3+conv2 part, conv1 tail]
-        self.hypers = [torch.zeros(8, dtype=torch.float32, device=device) for _ in range(4)]
+        # [whole arena, fc1 part, conv3 part, conv1 tail, conv2 part]
+        self.hypers = [torch.zeros(8, dtype=torch.float32, device=device) for _ in range(5)]
         self.hyper = self.hypers[0]
         self.hyper_vals = None
         self.first = 1
@@ -151,6 +151,8 @@ class ConvNetEngine:
         self._branch = torch.cuda.Stream(device=self.device, priority=bprio)   # off-critical-path kernels (see _record_tc): pack, fc1 wgrad
         self._branch2 = torch.cuda.Stream(device=self.device, priority=bprio)  # conv3 / conv2 weight gradients
         self._capture_stream = torch.cuda.Stream(device=self.device, priority=-1)  # the main chain: high priority (see _build)
+        self._branch3 = torch.cuda.Stream(device=self.device, priority=-1)  # conv2's wgrad chain: high priority (see _record_tc_impl)
+        self._branch4 = torch.cuda.Stream(device=self.device)               # conv3's gradient exchange
         self._ring = self._d2h = None  # pinned loss ring + its copy stream, created by the first step(pending=True)
 
     def _on_optimizer_reload(self, first):
@@ -162,15 +164,18 @@ class ConvNetEngine:
 
     # ------------------------------------------------------------------ two-part gradient exchange
     def _setup_split(self):
-        """The arena is laid out in gradient-arrival order -- fc1 | conv3 | conv2 | conv1 -- so each layer group is a contiguous
-        range.  Instead of ONE exchange after the last gradient (fully exposed: nothing is left to overlap it with), the step
-        exchanges three parts, each the moment it is final, each fused with its SGD update:
-          * fc1            on branch stream A, right behind fc1's weight-gradient kernel;
-          * conv3 + conv2  on branch stream B, behind conv2's weight gradient -- hidden under conv2's dgrad and conv1's wgrad;
-          * conv1 (832 floats, the LAST gradient) inside the conv1-wgrad kernel itself: push one-shot over peer memory
-            (csrc/cuda/convnet_bwd.cu), one NVLink store latency instead of a kernel + two flag rounds.
-        Kernels on different streams can be in flight together, so each part owns a signal-pad channel (and, for the push
-        variant, an inbox)."""
+        """The arena is laid out in gradient-arrival order -- fc1 | conv3 | conv2 | conv1 -- so each layer is a contiguous range.
+        Instead of ONE exchange after the last gradient (fully exposed: nothing is left to overlap it with), the step
+        exchanges four parts, each the moment it is final, each fused with its SGD update:
+          * fc1    an allreduce+SGD kernel on branch stream A, right behind fc1's weight-gradient kernel;
+          * conv3  an allreduce+SGD kernel on a stream of its own behind conv3's weight gradient (hidden: half the backward
+                   pass is still to come);
+          * conv2  INSIDE the second pass of its split-K weight gradient (csrc/cuda/tc_wgrad.cu: every CTA reduces its partial
+                   sums, pushes the result to the peers, one flag round, reduce, SGD) -- no separate collective kernel on the
+                   branch that ends the step;
+          * conv1  (832 floats, the LAST gradient) inside the conv1-wgrad kernel (csrc/cuda/convnet_bwd.cu).
+        Kernels on different streams can be in flight together, so every part owns its flags: a reserved signal-pad channel
+        of the arena's segment (fc1, conv3) or a small segment of its own with inbox + pad + state (conv2, conv1)."""
         from ..parallel.ddp import _Bucket
 
         self.split = None
@@ -181,48 +186,82 @@ class ConvNetEngine:
         off = lambda i: (self.g_views[i].data_ptr() - flat_in.data_ptr()) // esz  # noqa: E731
         base = self.bucket.offset if self.ddp is not None else 0
         total = (self.bucket.offset + self.bucket.numel) if self.ddp is not None else self.arena.total
-        off_fcb, off_c3b, off_c1b, off_c1w = off(7), off(5), off(1), off(0)
-        ok = off_fcb == base and base < off_c3b < off_c1b and off_c1b + 32 == off_c1w and off_c1w + 800 == total \
-            and off_c3b % 4 == 0 and off_c1b % 4 == 0 and off(6) < off_c3b and off_c3b <= off(4) < off_c1b and off_c3b <= off(2) < off_c1b
+        off_fcb, off_c3b, off_c2b, off_c2w, off_c1b, off_c1w = off(7), off(5), off(3), off(2), off(1), off(0)
+        ok = off_fcb == base and base < off_c3b < off_c2b and off_c2b + 64 == off_c2w and off_c2w + 18432 == off_c1b \
+            and off_c1b + 32 == off_c1w and off_c1w + 800 == total and off_c3b % 4 == 0 and off_c2b % 4 == 0 and off_c1b % 4 == 0 \
+            and off(6) < off_c3b and off_c3b <= off(4) < off_c2b
         if not ok:
             return  # unexpected layout (e.g. a user-forced bucket order): keep the single whole-bucket kernel
-        split = {"fc": (base, off_c3b - base), "c32": (off_c3b, off_c1b - off_c3b), "inbox": None, "pads": None, "state": None}
+        fuse_c2 = os.environ.get("PDL_CONVNET_FUSE_C2", "1") != "0"
+        split = {"fc": (base, off_c3b - base), "c3": (off_c3b, (off_c2b if fuse_c2 else off_c1b) - off_c3b), "c2": (off_c2b, off_c1b - off_c2b),
+                 "fuse_c2": fuse_c2, "tail": {"inbox": None, "pads": None, "state": None}, "c2x": {"inbox": None, "pads": None, "state": None}}
+        L = self.L
         if self.ddp is not None:
             parts = {}
-            for name, index, (o, n) in (("fc", 1000, split["fc"]), ("c32", 1002, split["c32"]), ("tail", 1001, (off_c1b, 832))):
+            for name, index, (o, n) in (("fc", 1000, split["fc"]), ("c3", 1002, split["c3"]), ("tail", 1001, (off_c1b, 832)), ("c2", 1003, split["c2"])):
                 bk = _Bucket(index, [], o, n)
                 bk.fused_group, bk.first_flag = self.bucket.fused_group, self.bucket.first_flag
                 parts[name] = bk
-            parts["fc"].channel = self.backend.reserve_channel()   # launched from branch streams: never share flags with the
-            parts["c32"].channel = self.backend.reserve_channel()  # communication stream's buckets or with each other
+            parts["fc"].channel = self.backend.reserve_channel()  # launched from branch streams: never share flags with the
+            parts["c3"].channel = self.backend.reserve_channel()  # communication stream's buckets or with each other
             split["parts"] = parts
+            pg = self.backend.pg
+            split["c2x"]["state"] = pg.new_comm_state()  # also at world size 1: the fused second pass counts its CTAs in it
             if self.world > 1:
-                pg, L = self.backend.pg, self.L
                 pad = (L.pdl_signal_pad_bytes() + 4095) // 4096 * 4096
-                seg = pg.new_segment(pad + int(L.pdl_conv1_tail_inbox_bytes(self.world)), want_multicast=False)
-                split["seg"], split["state"] = seg, pg.new_comm_state()
-                split["pads"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r) for r in range(self.world)])
-                split["inbox"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r, pad) for r in range(self.world)])
-                for name in ("fc", "c32"):  # resolve variant / CTAs / inbox now: collective allocations stay out of graph capture
+                for key, nbytes in (("tail", int(L.pdl_conv1_tail_inbox_bytes(self.world))),
+                                    ("c2x", 4 * int(L.pdl_wgrad_finish_comm_inbox_floats(self.world, 32, 64, 3, 3)))):
+                    seg = pg.new_segment(pad + nbytes, want_multicast=False)
+                    d = split[key]
+                    d["seg"] = seg
+                    if d["state"] is None:
+                        d["state"] = pg.new_comm_state()
+                    d["pads"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r) for r in range(self.world)])
+                    d["inbox"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r, pad) for r in range(self.world)])
+                for name in ("fc", "c3"):  # resolve variant / CTAs / inbox now: collective allocations stay out of graph capture
                     self.backend.bucket_launch_args(parts[name], self.world, self.ddp.algorithm)
+        else:
+            split["c2x"]["state"] = self.arena.states[4]
         self.split = split
 
-    def _tail_hyper(self):
+    def _part_hyper(self, name):
         if self.ddp is not None:
-            return self.backend._hyper_for(self.split["parts"]["tail"])
-        return self.arena.hypers[3]
+            return self.backend._hyper_for(self.split["parts"][name])
+        return self.arena.hypers[{"fc": 1, "c3": 2, "tail": 3, "c2": 4}[name]]
+
+    def _tail_hyper(self):
+        return self._part_hyper("tail")
 
     def _launch_part(self, name, stream_handle):
-        """Exchange + SGD of one contiguous part of the arena ("fc" or "c32") on the given stream."""
+        """Exchange + SGD of one contiguous part of the arena ("fc" or "c3") on the given stream."""
         if self.ddp is not None:
             self.backend.launch_bucket_kernel(self.split["parts"][name], self.world, self.ddp.algorithm, stream_handle, fused=True)
         else:
             o, n = self.split[name]
-            self.arena.launch(stream_handle, offset=o, numel=n, which={"fc": 1, "c32": 2}[name])
+            self.arena.launch(stream_handle, offset=o, numel=n, which={"fc": 1, "c3": 2}[name])
+
+    def _launch_conv2_finish_comm(self, b, N, st):
+        """Second pass of conv2's weight gradient + cross-GPU average + SGD in one kernel (the conv2 slice of the arena)."""
+        sp, x = self.split, self.split["c2x"]
+        o, n = sp["c2"]
+        flat = (lambda t: ctypes.c_void_p(t.data_ptr() + 4 * o))
+        if self.ddp is not None:
+            bk = self.backend
+            g_in, g_avg, p_flat, m_flat = bk.g_in, bk.g_avg, bk.p_flat, bk.m_flat
+            rank, timeout = bk.pg.rank(), bk.pg.timeout_s
+        else:
+            a = self.arena
+            g_in, g_avg, p_flat, m_flat = a.g_in, a.g_avg, a.p_flat, a.m_flat
+            rank, timeout = 0, 30.0
+        mom = flat(m_flat) if (self.group["momentum"] != 0 and m_flat is not None) else None
+        NF._ok(self.L.pdl_tc_conv2d_wgrad_finish_comm(_p(b["wg_scratch"]), _p(b["db2part"]), self.db2_blocks, N, 13, 13, 32, 64, 3, 3, 0,
+                                                      flat(g_in), flat(g_avg), flat(p_flat), mom, _p(self._part_hyper("c2")), rank, self.world, 0,
+                                                      x["inbox"], x["pads"], _p(x["state"]), 1.0 / self.world, timeout, st),
+               "conv2 wgrad second pass + gradient exchange + SGD")
 
     def _launch_conv1_wgrad_comm(self, b, N, st):
         """conv1 weight gradient + cross-GPU average + SGD in one kernel (the tail of the arena)."""
-        sp = self.split
+        sp = self.split["tail"]
         w1, b1 = self.params[0], self.params[1]
         gw1, gb1 = self.g_views[0], self.g_views[1]
         aw1, ab1 = self.avg_views[0], self.avg_views[1]
@@ -349,6 +388,7 @@ class ConvNetEngine:
         sb = ctypes.c_void_p(branch.cuda_stream)
         sb2 = ctypes.c_void_p(branch2.cuda_stream)
         exchange = reduce and self.split is not None
+        joined = [branch2]
         branch.wait_stream(main)
         ok(L.pdl_convnet_pack(_p(w2), _p(w3), _p(wf), _p(b["p2f"]), _p(b["p2b"]), _p(b["p3f"]), _p(b["p3b"]), _p(b["wfp"]), sb), "weight pack"); k += 1
         # forward: conv+bias+ReLU+pool fused per layer
@@ -387,30 +427,39 @@ class ConvNetEngine:
         branch2.wait_stream(main)  # dz3 / db3part are ready
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a2"]), _p(b["dz3"]), _p(gw3), _p(gb3), _p(b["db3part"]), N, _p(b["wg_scratch"]), N, 10, 10, 64, 128, 3, 3, 0,
                                  err, sb2), "conv3 wgrad"); k += 2
+        fuse_c2 = exchange and self.split["fuse_c2"] and fork
+        if exchange and fuse_c2:
+            # conv3's gradient is final: its exchange + SGD goes to a stream of its own (half of the backward pass is still to
+            # come, so it is hidden), leaving this branch free for conv2's weight gradient the moment dz2 exists
+            self._branch4.wait_stream(branch2)
+            joined.append(self._branch4)
+            self._launch_part("c3", self._branch4.cuda_stream); k += 1
         if self.fuse_pool2:  # conv3 dgrad with pool2's backward + ReLU mask + bias partials in its epilogue
             ok(L.pdl_tc_conv2d_dgrad_poolbwd(_p(b["dz3"]), _p(b["p3b"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 10, 10, 64, 128,
                                              3, 3, 0, 1, err, st), "conv3 dgrad + pool2 backward"); k += 1
         else:
             ok(L.pdl_tc_conv2d_dgrad(_p(b["dz3"]), _p(b["p3b"]), _p(b["da2"]), N, 10, 10, 64, 128, 3, 3, 0, err, st), "conv3 dgrad"); k += 1
             ok(L.pdl_pool2_bwd_dbias(_p(b["da2"]), _p(b["i2"]), _p(b["a2"]), _p(b["dz2"]), _p(b["db2part"]), N, 11, 11, 64, 1, st), "pool2 backward"); k += 1
-        wg2_main = os.environ.get("PDL_CONVNET_WG2_MAIN", "0") == "1" and fork
-        if wg2_main:
-            # experiment: conv2's weight-gradient GEMM in the main chain (before the dgrad), only its second pass + the
-            # exchange on the branch -- the exchange then has the dgrad and conv1's wgrad to hide behind
-            main.wait_stream(branch2)  # wg_scratch: conv3's second pass must be done
-            ok(L.pdl_tc_conv2d_wgrad_gemm(_p(b["a1"]), _p(b["dz2"]), _p(b["wg_scratch"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 wgrad gemm"); k += 1
-            branch2.wait_stream(main)
-            ok(L.pdl_tc_conv2d_wgrad_finish(_p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64, 3, 3, 0, sb2),
-               "conv2 wgrad second pass"); k += 1
+        if fork and N <= 256 and os.environ.get("PDL_CONVNET_WG2_PRIO", "1") == "1":
+            # conv2's weight gradient and its dgrad become ready together; on a HIGH-priority stream the (48-CTA) weight gradient
+            # takes its SMs at once instead of queueing behind the dgrad's 133 CTAs -- it is what the end of the step waits
+            # for (measured: 108.8 -> 104.5 us/step, 103.8 with the dgrad bounded to two tiles per CTA)
+            self._branch3.wait_stream(branch2)
+            branch2 = self._branch3
+            joined.append(branch2)
+            sb2 = ctypes.c_void_p(branch2.cuda_stream)
+        branch2.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
+        if fuse_c2:
+            ok(L.pdl_tc_conv2d_wgrad_gemm(_p(b["a1"]), _p(b["dz2"]), _p(b["wg_scratch"]), N, 13, 13, 32, 64, 3, 3, 0, err, sb2), "conv2 wgrad gemm"); k += 1
+            self._launch_conv2_finish_comm(b, N, sb2); k += 1  # second pass + gradient exchange + SGD: one kernel
         else:
-            branch2.wait_stream(main)  # dz2 / db2part are ready (the branch is also past conv3's wgrad: wg_scratch is free again)
             ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
                                      3, 3, 0, err, sb2), "conv2 wgrad"); k += 2
-        if exchange:
-            # conv3's and conv2's gradients are final on this branch: exchange + SGD here, hidden behind the two kernels the
-            # main chain still has to run
-            self._launch_part("c32", branch2.cuda_stream); k += 1
-        d2cap = int(os.environ.get("PDL_CONVNET_DGRAD2_CTAS", "0")) if N <= 256 else 0
+            if exchange:
+                # conv3's and conv2's gradients are final on this branch: exchange + SGD here, hidden behind the two kernels
+                # the main chain still has to run
+                self._launch_part("c3", branch2.cuda_stream); k += 1
+        d2cap = int(os.environ.get("PDL_CONVNET_DGRAD2_CTAS", "100")) if N <= 256 else 0
         old = L.pdl_tc_conv_max_ctas(d2cap)  # conv2's dgrad and wgrad become ready together: leave the wgrad some SMs
         ok(L.pdl_tc_conv2d_dgrad(_p(b["dz2"]), _p(b["p2b"]), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 dgrad"); k += 1
         L.pdl_tc_conv_max_ctas(old)
@@ -419,8 +468,9 @@ class ConvNetEngine:
         else:
             ok(L.pdl_conv1_wgrad_fused(_p(b["x"]), _p(b["da1"]), _p(b["i1"]), _p(b["a1"]), _p(gw1), _p(gb1), _p(b["c1part"]), N, st), "conv1 wgrad"); k += 1
         main.wait_stream(branch)  # join: every gradient is in the bucket before the allreduce / the step ends
-        if branch2 is not branch:
-            main.wait_stream(branch2)
+        for other in joined:  # every stream that received work in this capture joins the main chain
+            if other is not branch and other is not main:
+                main.wait_stream(other)
         return k
 
     def _record_simt(self, b, N, stream_handle):
