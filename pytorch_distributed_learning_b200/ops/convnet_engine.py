@@ -192,7 +192,9 @@ class ConvNetEngine:
             and off(6) < off_c3b and off_c3b <= off(4) < off_c2b
         if not ok:
             return  # unexpected layout (e.g. a user-forced bucket order): keep the single whole-bucket kernel
-        fuse_c2 = os.environ.get("PDL_CONVNET_FUSE_C2", "1") != "0"
+        # conv2's exchange inside its second pass is OPT-IN: measured on B200 at batch 100 it is 3 us/step slower on one GPU
+        # (104.4 vs 101.4 us: one output per thread against the float4 allreduce kernel) and within noise on two (116.2 vs 117.0)
+        fuse_c2 = os.environ.get("PDL_CONVNET_FUSE_C2", "0") == "1"
         split = {"fc": (base, off_c3b - base), "c3": (off_c3b, (off_c2b if fuse_c2 else off_c1b) - off_c3b), "c2": (off_c2b, off_c1b - off_c2b),
                  "fuse_c2": fuse_c2, "tail": {"inbox": None, "pads": None, "state": None}, "c2x": {"inbox": None, "pads": None, "state": None}}
         L = self.L
