@@ -171,68 +171,39 @@ tc_wgrad_kernel(const __grid_constant__ CUtensorMap tmDy, const __grid_constant_
 }
 
 // dw[co][ci][tap] = sum_split partial[split][tap][co][ci];  db[co] = sum_blk db_partial[blk][co]
-// One CTA per output channel block: READS follow the partial layout (rows of Cin contiguous floats per (tap, co): coalesced,
-// `splits` independent loads in flight per thread), the [tap][ci] -> [ci][tap] transpose happens in shared memory, WRITES
-// follow the output layout (Cin*taps contiguous floats per co).  The first version indexed the output and gathered the
-// partials with a stride of Cout*Cin floats between neighbouring threads: 7-10 us for 1-4 MB (ncu: 2-6 % of DRAM
-// throughput), i.e. pure load latency -- and it runs 52 times per ResNet-50 step.
-constexpr int kFinThreads = 256;
-__global__ void __launch_bounds__(kFinThreads) wgrad_finish_kernel(const float* __restrict__ partial, int splits, int taps, int Cout, int Cin,
-                                                                   float* __restrict__ dw, const float* __restrict__ db_partial, int db_blocks,
-                                                                   float* __restrict__ db, int co_per_cta) {
-  extern __shared__ float fin_tile[];  // [co_per_cta][Cin * taps (+1)]
+// One thread per OUTPUT element, gathering its `splits` partials (stride Cout*Cin floats between neighbouring threads).  Two
+// "coalesced" rewrites -- a CTA per output-channel block, and a CTA per (channels x 32 input channels x taps) tile, each
+// reading 128-byte rows and transposing through shared memory -- were measured SLOWER in round 2 (ResNet-50 step 14.25 and
+// 13.38 ms against 13.08 ms; ConvNet 111-115 against 101 us): the kernel is bound by load latency, not by sectors, and the
+// gather keeps one independent chain per output with no barrier in it.
+__global__ void wgrad_finish_kernel(const float* __restrict__ partial, int splits, int taps, int Cout, int Cin, float* __restrict__ dw,
+                                    const float* __restrict__ db_partial, int db_blocks, float* __restrict__ db) {
   launch_dependents();     // successor may set up while this grid drains
   grid_dependency_wait();  // predecessor's outputs are complete and visible from here on
-  const long long per_split = static_cast<long long>(taps) * Cout * Cin;
-  const int co0 = blockIdx.x * co_per_cta;
-  const int row_len = Cin * taps, ld = row_len + 1;
-  const int items = co_per_cta * row_len;  // (co, tap, ci) with ci fastest: the partial's order
-  for (int e = threadIdx.x; e < items; e += kFinThreads) {
-    const int ci = e % Cin, t2 = e / Cin, tap = t2 % taps, cl = t2 / taps;
-    const int co = co0 + cl;
-    if (co < Cout) {
-      const float* src = partial + (static_cast<long long>(tap) * Cout + co) * Cin + ci;
-      float acc = 0.f;
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int per_split = taps * Cout * Cin;
+  if (i < per_split) {
+    // i indexes the OUTPUT layout so writes are coalesced
+    const int tap = i % taps, ci = (i / taps) % Cin, co = i / (taps * Cin);
+    const float* src = partial + (static_cast<long long>(tap) * Cout + co) * Cin + ci;
+    float acc = 0.f;
 #pragma unroll 8
-      for (int s2 = 0; s2 < splits; ++s2) acc += __ldg(src + s2 * per_split);  // independent loads, fixed order
-      fin_tile[cl * ld + ci * taps + tap] = acc;
-    }
+    for (int s = 0; s < splits; ++s) acc += __ldg(src + static_cast<long long>(s) * per_split);  // independent loads, fixed order
+    dw[i] = acc;
   }
-  __syncthreads();
-  for (int e = threadIdx.x; e < items; e += kFinThreads) {
-    const int cl = e / row_len, j = e % row_len;
-    if (co0 + cl < Cout) dw[static_cast<long long>(co0 + cl) * row_len + j] = fin_tile[cl * ld + j];
-  }
-  // bias gradient: one warp per channel of this CTA, lanes stride over the partial rows, fixed shuffle tree (deterministic)
+  // bias gradient: one warp per channel, lanes stride over the partial rows, fixed shuffle tree (deterministic)
   if (db) {
-    const int warp = threadIdx.x / 32, lane = threadIdx.x % 32;
-    for (int cl = warp; cl < co_per_cta; cl += kFinThreads / 32) {
-      const int co = co0 + cl;
-      if (co >= Cout) break;
+    const int warp_global = (blockIdx.x * blockDim.x + threadIdx.x) / 32, lane = threadIdx.x % 32;
+    const int first = (per_split + 31) / 32;  // warps past the weight outputs
+    const int co = warp_global - first;
+    if (co >= 0 && co < Cout) {
       float acc = 0.f;
-      for (int b2 = lane; b2 < db_blocks; b2 += 32) acc += db_partial[b2 * Cout + co];
+      for (int b = lane; b < db_blocks; b += 32) acc += db_partial[b * Cout + co];
 #pragma unroll
       for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
       if (lane == 0) db[co] = acc;
     }
   }
-}
-
-// Launch geometry of the second pass: output channels per CTA such that the transposing tile fits in 48 KB and the grid has
-// a few hundred CTAs.
-inline int fin_co_per_cta(int Cout, int Cin, int taps) {
-  const int row = Cin * taps + 1;
-  int c = 48 * 1024 / 4 / row;          // shared-memory bound
-  if (c > 8) c = 8;
-  while (c > 1 && (Cout + c - 1) / c < 128) --c;  // keep the grid wide
-  return c < 1 ? 1 : c;
-}
-inline cudaError_t launch_finish(const float* scratch, int splits, int taps, int Cout, int Cin, float* dw, const float* db_partial, int db_blocks,
-                                 float* db, cudaStream_t stream) {
-  const int c = fin_co_per_cta(Cout, Cin, taps);
-  const size_t smem = static_cast<size_t>(c) * (Cin * taps + 1) * sizeof(float);
-  return launch_dependent(wgrad_finish_kernel, dim3((Cout + c - 1) / c), dim3(kFinThreads), smem, stream, scratch, splits, taps, Cout, Cin, dw,
-                          db_partial, db_blocks, db, c);
 }
 
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
@@ -388,8 +359,9 @@ PDL_API int pdl_tc_conv2d_wgrad_strided(const float* x, const float* dy, float* 
   else if (mt == 64 && nt == 64) rc = launch_wg<64, 64>(ta, tb, g, KH, scratch, error_flag, stream);
   if (rc) return rc;
   if (dw == nullptr) return 0;  // GEMM pass only (pdl_tc_conv2d_wgrad_gemm); the second pass is launched separately
-  if (static_cast<size_t>(Cin) * KH * KW + 1 > 48 * 1024 / 4) { pdl_set_error("tc wgrad: filter row of %d floats does not fit the second pass", Cin * KH * KW); return -3; }
-  PDL_CUDA_CHECK(launch_finish(scratch, wg_splits(g), KH * KW, Cout, Cin, dw, db_partial, db_blocks, db, stream));
+  const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
+  PDL_CUDA_CHECK(launch_dependent(wgrad_finish_kernel, dim3(pdl_ceil_div(total, 256)), dim3(256), 0, stream, scratch, wg_splits(g), KH * KW, Cout, Cin, dw,
+                                  db_partial, db_blocks, db));
   PDL_LAUNCH_CHECK();
   return 0;
 }
@@ -486,8 +458,9 @@ PDL_API int pdl_tc_conv2d_wgrad_finish(float* dw, float* db, const float* db_par
                                        int Cout, int KH, int KW, int pad, cudaStream_t stream) {
   WgGeom g{};
   if (!wg_geometry(N, H + 2 * pad - KH + 1, W + 2 * pad - KW + 1, Cin, Cout, KH, KW, pad, &g)) { pdl_set_error("tc wgrad: unsupported shape"); return -3; }
-  if (static_cast<size_t>(Cin) * KH * KW + 1 > 48 * 1024 / 4) { pdl_set_error("tc wgrad: filter row of %d floats does not fit the second pass", Cin * KH * KW); return -3; }
-  PDL_CUDA_CHECK(launch_finish(scratch, wg_splits(g), KH * KW, Cout, Cin, dw, db_partial, db_blocks, db, stream));
+  const int total = (KH * KW * Cout * Cin + 31) / 32 * 32 + (db ? Cout * 32 : 0);
+  PDL_CUDA_CHECK(launch_dependent(wgrad_finish_kernel, dim3(pdl_ceil_div(total, 256)), dim3(256), 0, stream, scratch, wg_splits(g), KH * KW, Cout, Cin, dw,
+                                  db_partial, db_blocks, db));
   PDL_LAUNCH_CHECK();
   return 0;
 }
