@@ -195,7 +195,12 @@ class ConvNetEngine:
         # conv2's exchange inside its second pass is OPT-IN: measured on B200 at batch 100 it is 3 us/step slower on one GPU
         # (104.4 vs 101.4 us: one output per thread against the float4 allreduce kernel) and within noise on two (116.2 vs 117.0)
         fuse_c2 = os.environ.get("PDL_CONVNET_FUSE_C2", "0") == "1"
-        split = {"fc": (base, off_c3b - base), "c3": (off_c3b, (off_c2b if fuse_c2 else off_c1b) - off_c3b), "c2": (off_c2b, off_c1b - off_c2b),
+        # conv3 and conv2 are exchanged separately (PDL_CONVNET_JOIN_C32=1 restores one kernel over both): conv3's part leaves
+        # from a stream of its own as soon as its weight gradient is final, so what is left for the end of the step is conv2's
+        # 74 KB instead of 369 KB
+        join_c32 = os.environ.get("PDL_CONVNET_JOIN_C32", "0") == "1" and not fuse_c2
+        split = {"fc": (base, off_c3b - base), "c3": (off_c3b, (off_c1b if join_c32 else off_c2b) - off_c3b), "c2": (off_c2b, off_c1b - off_c2b),
+                 "join_c32": join_c32,
                  "fuse_c2": fuse_c2, "tail": {"inbox": None, "pads": None, "state": None}, "c2x": {"inbox": None, "pads": None, "state": None}}
         L = self.L
         if self.ddp is not None:
@@ -206,6 +211,7 @@ class ConvNetEngine:
                 parts[name] = bk
             parts["fc"].channel = self.backend.reserve_channel()  # launched from branch streams: never share flags with the
             parts["c3"].channel = self.backend.reserve_channel()  # communication stream's buckets or with each other
+            parts["c2"].channel = self.backend.reserve_channel()
             split["parts"] = parts
             pg = self.backend.pg
             split["c2x"]["state"] = pg.new_comm_state()  # also at world size 1: the fused second pass counts its CTAs in it
@@ -220,7 +226,7 @@ class ConvNetEngine:
                         d["state"] = pg.new_comm_state()
                     d["pads"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r) for r in range(self.world)])
                     d["inbox"] = (ctypes.c_void_p * self.world)(*[seg.ptr(r, pad) for r in range(self.world)])
-                for name in ("fc", "c3"):  # resolve variant / CTAs / inbox now: collective allocations stay out of graph capture
+                for name in ("fc", "c3", "c2"):  # resolve variant / CTAs / inbox now: collective allocations stay out of graph capture
                     self.backend.bucket_launch_args(parts[name], self.world, self.ddp.algorithm)
         else:
             split["c2x"]["state"] = self.arena.states[4]
@@ -235,12 +241,12 @@ class ConvNetEngine:
         return self._part_hyper("tail")
 
     def _launch_part(self, name, stream_handle):
-        """Exchange + SGD of one contiguous part of the arena ("fc" or "c3") on the given stream."""
+        """Exchange + SGD of one contiguous part of the arena ("fc", "c3" or "c2") on the given stream."""
         if self.ddp is not None:
             self.backend.launch_bucket_kernel(self.split["parts"][name], self.world, self.ddp.algorithm, stream_handle, fused=True)
         else:
             o, n = self.split[name]
-            self.arena.launch(stream_handle, offset=o, numel=n, which={"fc": 1, "c3": 2}[name])
+            self.arena.launch(stream_handle, offset=o, numel=n, which={"fc": 1, "c3": 2, "c2": 4}[name])
 
     def _launch_conv2_finish_comm(self, b, N, st):
         """Second pass of conv2's weight gradient + cross-GPU average + SGD in one kernel (the conv2 slice of the arena)."""
@@ -430,7 +436,8 @@ class ConvNetEngine:
         ok(L.pdl_tc_conv2d_wgrad(_p(b["a2"]), _p(b["dz3"]), _p(gw3), _p(gb3), _p(b["db3part"]), N, _p(b["wg_scratch"]), N, 10, 10, 64, 128, 3, 3, 0,
                                  err, sb2), "conv3 wgrad"); k += 2
         fuse_c2 = exchange and self.split["fuse_c2"] and fork
-        if exchange and fuse_c2:
+        own_c3 = exchange and fork and not self.split["join_c32"]
+        if own_c3:
             # conv3's gradient is final: its exchange + SGD goes to a stream of its own (half of the backward pass is still to
             # come, so it is hidden), leaving this branch free for conv2's weight gradient the moment dz2 exists
             self._branch4.wait_stream(branch2)
@@ -458,9 +465,12 @@ class ConvNetEngine:
             ok(L.pdl_tc_conv2d_wgrad(_p(b["a1"]), _p(b["dz2"]), _p(gw2), _p(gb2), _p(b["db2part"]), self.db2_blocks, _p(b["wg_scratch"]), N, 13, 13, 32, 64,
                                      3, 3, 0, err, sb2), "conv2 wgrad"); k += 2
             if exchange:
-                # conv3's and conv2's gradients are final on this branch: exchange + SGD here, hidden behind the two kernels
-                # the main chain still has to run
-                self._launch_part("c3", branch2.cuda_stream); k += 1
+                # conv2's gradient (and conv3's, when the two are joined or there is no fork) is final on this branch:
+                # exchange + SGD here, behind the two kernels the main chain still has to run
+                if not own_c3:
+                    self._launch_part("c3", branch2.cuda_stream); k += 1
+                if not self.split["join_c32"]:
+                    self._launch_part("c2", branch2.cuda_stream); k += 1
         d2cap = int(os.environ.get("PDL_CONVNET_DGRAD2_CTAS", "100")) if N <= 256 else 0
         old = L.pdl_tc_conv_max_ctas(d2cap)  # conv2's dgrad and wgrad become ready together: leave the wgrad some SMs
         ok(L.pdl_tc_conv2d_dgrad(_p(b["dz2"]), _p(b["p2b"]), _p(b["da1"]), N, 13, 13, 32, 64, 3, 3, 0, err, st), "conv2 dgrad"); k += 1
