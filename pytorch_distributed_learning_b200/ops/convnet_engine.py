@@ -112,7 +112,15 @@ class ConvNetEngine:
             return None
         if ddp is not None and (len(ddp._buckets) != 1 or not getattr(ddp._backend, "supports_fused_sgd", False) or not ddp.fused_optimizer):
             return None
-        return cls(module, ddp, optimizer)
+        if ddp is None:
+            return cls(module, ddp, optimizer)
+        # one engine per (wrapped model, optimizer): an explicit TrainStep and the transparent six-call path share graphs,
+        # buffers and the reserved signal-pad channels instead of claiming them twice
+        cache = ddp.__dict__.setdefault("_convnet_engines", {})
+        engine = cache.get(id(optimizer))
+        if engine is None or engine.optimizer is not optimizer:
+            engine = cache[id(optimizer)] = cls(module, ddp, optimizer)
+        return engine
 
     def __init__(self, module, ddp, optimizer):
         self.module, self.ddp, self.optimizer = module, ddp, optimizer
