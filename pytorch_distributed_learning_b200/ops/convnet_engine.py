@@ -560,6 +560,8 @@ class ConvNetEngine:
         self._refresh_hyper()
         if self.ddp is not None:
             self.backend.pg.poll_errors()  # a lost peer reported by an earlier replay's allreduce kernel raises here (one host load)
+        if entry["tc"]:
+            tc_conv.check_errors(self.device)  # ... and so does a tensor-core kernel of an earlier replay that gave up on its pipeline
         main = torch.cuda.current_stream(self.device)
         stager = entry["stager"]
         if not images.is_cuda and not labels.is_cuda:

@@ -31,16 +31,19 @@ def _stream(t):
 
 
 def error_flag(device):
-    """Device int set by a kernel whose pipeline wait timed out (checked by tests / check_errors)."""
+    """Word that a tensor-core kernel sets when one of its (bounded) pipeline waits timed out.  It lives in PINNED HOST memory,
+    which the device can address directly: the failing kernel writes it itself, and ``check_errors`` is a plain host load --
+    cheap enough for the step path of the graphed engines, no synchronisation, no copy."""
     f = _err.get(device.index)
     if f is None:
-        f = _err[device.index] = torch.zeros(1, dtype=torch.int32, device=device)
+        f = _err[device.index] = torch.zeros(1, dtype=torch.int32).pin_memory()
     return f
 
 
 def check_errors(device):
+    """Raise if a tensor-core convolution kernel gave up on its TMA/MMA pipeline since the last check (its output is garbage)."""
     f = _err.get(device.index)
-    if f is not None and int(f.item()) != 0:
+    if f is not None and int(f[0]) != 0:
         f.zero_()
         raise RuntimeError("a tensor-core convolution kernel timed out waiting on its TMA/MMA pipeline")
 

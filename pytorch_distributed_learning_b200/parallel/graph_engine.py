@@ -130,7 +130,13 @@ class GenericGraphEngine:
         if entry is None:
             entry = self.graphs[key] = self._build(images, labels)
         self._refresh_fused_hyper()
+        from ..ops import tc_conv
         from .pipeline import InputStager, refresh_inputs
+
+        tc_conv.check_errors(self.device)  # a tensor-core kernel of an earlier replay gave up on its pipeline: raise (host load)
+        pg = getattr(getattr(self.model, "_backend", None), "pg", None)
+        if pg is not None and hasattr(pg, "poll_errors"):
+            pg.poll_errors()               # a collective kernel of an earlier replay lost a peer
 
         if not images.is_cuda and not labels.is_cuda:
             stager = entry.get("stager")
