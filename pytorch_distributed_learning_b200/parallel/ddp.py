@@ -287,12 +287,19 @@ class DistributedDataParallel(nn.Module):
             opt = next(iter(owners.values()))
             from ..ops.convnet_engine import ConvNetEngine
 
-            engine = ConvNetEngine.try_create(self, criterion, opt)
-            if engine is None:
-                from .graph_engine import GenericGraphEngine
+            try:
+                engine = ConvNetEngine.try_create(self, criterion, opt)
+                if engine is None:
+                    from .graph_engine import GenericGraphEngine
 
-                if GenericGraphEngine.supports(criterion):
-                    engine = GenericGraphEngine(self, criterion, opt)
+                    if GenericGraphEngine.supports(criterion):
+                        engine = GenericGraphEngine(self, criterion, opt)
+            except (RuntimeError, ValueError, NotImplementedError) as e:
+                # e.g. an optimizer group the fused update does not cover: the loop simply runs call by call
+                from ..utils.logging import debug
+
+                debug("transparent graph step disabled: %s" % e)
+                engine = None
         self._graph_engines[key] = (engine, criterion)  # keeps the criterion alive: ids are only unique among live objects
         if engine is None:
             self._graph_step = False
