@@ -48,6 +48,19 @@ class SGD(torch.optim.SGD):
         self._momentum_views = {}  # id(param) -> view of a flat momentum arena that fused kernels update in place
         self._reload_listeners = []  # weak callables(first_step) run after load_state_dict (device-resident hyper-parameters)
 
+    def __setstate__(self, state):
+        """Unpickling / ``copy.deepcopy`` restores torch's three fields only (``Optimizer.__getstate__``): the copy starts with
+        empty fusion bookkeeping -- it owns different parameter objects, so nothing of the original's arenas applies to it."""
+        super().__setstate__(state)
+        self.__dict__.setdefault("_fused_done", set())
+        self.__dict__.setdefault("_attached", [])
+        self.__dict__.setdefault("_native_tables", {})
+        self.__dict__.setdefault("_momentum_views", {})
+        self.__dict__.setdefault("_reload_listeners", [])
+        for group in self.param_groups:
+            for p in group["params"]:
+                _registry[id(p)] = self
+
     def add_param_group(self, param_group):
         super().add_param_group(param_group)
         for p in self.param_groups[-1]["params"]:

@@ -82,3 +82,19 @@ def test_load_state_dict_refills_flat_momentum_views_and_notifies_mirrors():
     fresh = pdl.optim.SGD([torch.nn.Parameter(torch.randn(*s)) for s in shapes], lr=0.1, momentum=0.9).state_dict()
     ob.load_state_dict(fresh)
     assert mirror.calls == [0, 1] and flat_b.abs().sum() == 0
+
+
+def test_deepcopy_and_pickle_give_a_working_optimizer():
+    import copy
+    import pickle
+
+    w = torch.nn.Parameter(torch.ones(3))
+    opt = pdl.optim.SGD([w], lr=0.1, momentum=0.9)
+    w.grad = torch.ones(3)
+    opt.step()
+    for clone in (copy.deepcopy(opt), pickle.loads(pickle.dumps(opt))):
+        p = clone.param_groups[0]["params"][0]
+        assert p is not w and pdl.optim.lookup_optimizer(p)[0] is clone
+        p.grad = torch.ones(3)
+        clone.step()
+        torch.testing.assert_close(p.detach(), torch.full((3,), 1 - 0.1 - 0.1 * 1.9))
